@@ -1,0 +1,332 @@
+"""ORACLE (test infrastructure, NOT product code) — float64 CPU restatement of the reference's
+bundle-adjustment hot path.  PARITY UNPINNED: the arithmetic of the path lives in the
+un-vendored dependency `jaxopt==0.7` (`/root/reference/requirements.txt:30`, on `jax==0.4.8`,
+`:81-82`), which is absent from this image, and the reference has no test that pins the path
+(SURVEY.md §4).  What IS pinned: the projection against COLMAP's four known-answer vectors
+(`colmap/src/base/cost_functions_test.cc:41-69`), the analytic Jacobian against autodiff of a
+literal restatement of the reference's `get_residuals` (`oracle/ref_literal.py`), and the pose
+log/exp maps against scipy and the reference's `test_pose.txt` fixture.
+
+Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s cpu_baseline / `--impl reference`
+legs may import this module.
+
+Follows (all paths relative to /root/reference/src/reconstruction/bundle_adjustment/):
+  rot_mat_from_vec        utils.py:21-28      -> rot_mat_from_vec
+  pose_mat_to_vec         utils.py:31-44      -> pose_mat_to_vec
+  parse_intrinsics        utils.py:47-57      -> folded into project()
+  reproject_point(s)      bundle_adjustment.py:17-29
+  get_residuals           bundle_adjustment.py:52-74   -> ba_residuals (sparse rows, mask==1 only)
+  prepare_params          bundle_adjustment.py:93-102  -> pack_params / unpack_params
+  jaxopt LevenbergMarquardt 0.7 (init_state / update / run) -> lm_solve
+  jax.scipy.sparse.linalg.cg (tol=1e-5, atol=0, maxiter=10n, x0=0, no preconditioner) -> _cg_jaxopt
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+import scipy.linalg
+import scipy.sparse as sp
+
+
+# ----------------------------------------------------------------------------- camera algebra
+def rot_mat_from_vec(w):
+    """utils.py:21-28: R = cos I + (1-cos) k k^T + sin [k]x, theta=|w|, k=w/theta (NaN at 0)."""
+    w = np.asarray(w, dtype=np.float64)
+    theta = np.linalg.norm(w, axis=-1)[..., None, None]
+    with np.errstate(invalid="ignore", divide="ignore"):
+        k = w / theta[..., 0]
+    K = np.zeros(w.shape[:-1] + (3, 3))
+    K[..., 0, 1] = -k[..., 2]
+    K[..., 0, 2] = k[..., 1]
+    K[..., 1, 0] = k[..., 2]
+    K[..., 1, 2] = -k[..., 0]
+    K[..., 2, 0] = -k[..., 1]
+    K[..., 2, 1] = k[..., 0]
+    kk = k[..., :, None] * k[..., None, :]
+    eye = np.broadcast_to(np.eye(3), K.shape)
+    return np.cos(theta) * eye + (1.0 - np.cos(theta)) * kk + np.sin(theta) * K
+
+
+def pose_mat_to_vec(pose):
+    """utils.py:31-44: SO(3) log via the antisymmetric part; returns [w, t] (...,6)."""
+    pose = np.asarray(pose, dtype=np.float64)
+    R = pose[..., :3, :3]
+    n = np.zeros(R.shape[:-2] + (3,))
+    angle = np.arccos(np.clip((R[..., 0, 0] + R[..., 1, 1] + R[..., 2, 2] - 1) / 2, -1, 1))
+    n[..., 0] = R[..., 2, 1] - R[..., 1, 2]
+    n[..., 1] = R[..., 0, 2] - R[..., 2, 0]
+    n[..., 2] = R[..., 1, 0] - R[..., 0, 1]
+    norms = np.linalg.norm(n, axis=-1)
+    nz = norms != 0
+    n[nz] *= (angle[nz] / norms[nz])[..., None]
+    return np.concatenate([n, pose[..., :3, 3]], axis=-1)
+
+
+def pack_params(poses0, intrinsics0, points0):
+    """bundle_adjustment.py:93-102: opt_params = [C*6 (w,t) | C*2 (fx,fy) | P*3], cx_cy_skew."""
+    intrinsics0 = np.asarray(intrinsics0, dtype=np.float64)
+    cam = pose_mat_to_vec(np.asarray(poses0)).reshape(-1)
+    return (np.concatenate([cam, intrinsics0[:, :2].reshape(-1), np.asarray(points0).reshape(-1)]),
+            intrinsics0[:, 2:].copy())
+
+
+def unpack_params(x, C):
+    cam6 = x[:6 * C].reshape(C, 6)
+    f = x[6 * C:8 * C].reshape(C, 2)
+    pts = x[8 * C:].reshape(-1, 3)
+    return cam6, f, pts
+
+
+def _skew(v):
+    S = np.zeros(v.shape[:-1] + (3, 3))
+    S[..., 0, 1] = -v[..., 2]
+    S[..., 0, 2] = v[..., 1]
+    S[..., 1, 0] = v[..., 2]
+    S[..., 1, 2] = -v[..., 0]
+    S[..., 2, 0] = -v[..., 1]
+    S[..., 2, 1] = v[..., 0]
+    return S
+
+
+def rot_jac_factor(w, R):
+    """M with d(R X)/dw = -R [X]x M,  M = (w w^T + (R^T - I)[w]x)/|w|^2  (Gallego & Yezzi 2015)."""
+    th2 = (w * w).sum(-1)[..., None, None]
+    eye = np.eye(3)
+    return (w[..., :, None] * w[..., None, :] + (np.swapaxes(R, -1, -2) - eye) @ _skew(w)) / th2
+
+
+# ----------------------------------------------------------------------------- residual + Jacobian
+def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True):
+    """Residual r_i = ((u-x)^2+(v-y)^2)/w^2 per valid observation (bundle_adjustment.py:17-21,74)
+    and the 8 camera + 3 point non-zeros of each Jacobian row (analytic).
+
+    Returns r (N,), dxdy (N,2), a (N,8) cols [w(3), t(3), fx, fy], b (N,3)."""
+    cam6, f, pts = unpack_params(x, C)
+    w = cam6[:, :3]
+    R = rot_mat_from_vec(w)
+    Rc = R[cam_idx]
+    X = pts[pt_idx]
+    q = (Rc @ X[..., None])[..., 0] + cam6[cam_idx, 3:6]
+    fx = f[cam_idx, 0]
+    fy = f[cam_idx, 1]
+    cx = cx_cy_skew[cam_idx, 0]
+    cy = cx_cy_skew[cam_idx, 1]
+    s = cx_cy_skew[cam_idx, 2]
+    iz = 1.0 / q[:, 2]
+    u = (fx * q[:, 0] + s * q[:, 1]) * iz + cx
+    v = fy * q[:, 1] * iz + cy
+    dx = u - obs[:, 0]
+    dy = v - obs[:, 1]
+    r = (dx * dx + dy * dy) / w2
+    dxdy = np.stack([dx, dy], axis=1)
+    if not want_jac:
+        return r, dxdy, None, None
+    N = len(r)
+    # d(u,v)/dq
+    dpi = np.zeros((N, 2, 3))
+    dpi[:, 0, 0] = fx * iz
+    dpi[:, 0, 1] = s * iz
+    dpi[:, 0, 2] = -(fx * q[:, 0] + s * q[:, 1]) * iz * iz
+    dpi[:, 1, 1] = fy * iz
+    dpi[:, 1, 2] = -fy * q[:, 1] * iz * iz
+    e = (2.0 / w2) * dxdy                     # dr/d(u,v)
+    eq = np.einsum("ni,nij->nj", e, dpi)      # dr/dq   (N,3)
+    M = rot_jac_factor(w, R)
+    dq_dw = -Rc @ _skew(X) @ M[cam_idx]       # (N,3,3)
+    a = np.empty((N, 8))
+    a[:, 0:3] = np.einsum("nj,njk->nk", eq, dq_dw)
+    a[:, 3:6] = eq
+    a[:, 6] = e[:, 0] * q[:, 0] * iz
+    a[:, 7] = e[:, 1] * q[:, 1] * iz
+    b = np.einsum("nj,njk->nk", eq, Rc)
+    return r, dxdy, a, b
+
+
+def ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx):
+    """Scatter rows into the reference's column order [C*6 | C*2 | P*3] -> CSR (N, 8C+3P)."""
+    N = a.shape[0]
+    rows = np.repeat(np.arange(N), 11)
+    cols = np.empty((N, 11), dtype=np.int64)
+    cols[:, 0:6] = 6 * cam_idx[:, None] + np.arange(6)
+    cols[:, 6:8] = 6 * C + 2 * cam_idx[:, None] + np.arange(2)
+    cols[:, 8:11] = 8 * C + 3 * pt_idx[:, None] + np.arange(3)
+    vals = np.concatenate([a, b], axis=1)
+    return sp.csr_matrix((vals.reshape(-1), (rows, cols.reshape(-1))), shape=(N, 8 * C + 3 * P))
+
+
+def rms_reprojection_px(x, C, cam_idx, pt_idx, obs, cx_cy_skew):
+    """sqrt(mean(dx^2+dy^2)) in pixels — the gauge-invariant quality figure (camera.py:78-85)."""
+    _, dxdy, _, _ = ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, 1.0, want_jac=False)
+    return float(np.sqrt((dxdy ** 2).sum(1).mean()))
+
+
+# ----------------------------------------------------------------------------- linear solvers
+def _cg_jaxopt(matvec, b, tol=1e-5, maxiter=None):
+    """jax.scipy.sparse.linalg.cg as jaxopt.linear_solve.solve_cg calls it: x0=0, M=I,
+    stop when r.r <= max(tol^2 b.b, atol^2) with atol=0, maxiter = 10*n."""
+    n = b.shape[0]
+    maxiter = 10 * n if maxiter is None else maxiter
+    atol2 = tol * tol * float(b @ b)
+    x = np.zeros_like(b)
+    r = b.copy()
+    p = r.copy()
+    gamma = float(r @ r)
+    k = 0
+    while gamma > atol2 and k < maxiter:
+        Ap = matvec(p)
+        alpha = gamma / float(p @ Ap)
+        x += alpha * p
+        r -= alpha * Ap
+        gamma_new = float(r @ r)
+        p = r + (gamma_new / gamma) * p
+        gamma = gamma_new
+        k += 1
+    return x, k
+
+
+def _solve_schur_exact(a, b, g, mu, C, P, cam_idx, pt_idx):
+    """Exact solve of (J^T J + mu I) v = g through the Schur complement on the camera block
+     with a dense Cholesky of S — arithmetic-equivalent to a direct solve."""
+    N = a.shape[0]
+    # internal ordering: camera-major 8-blocks then points
+    U = np.zeros((C, 8, 8))
+    np.add.at(U, cam_idx, a[:, :, None] * a[:, None, :])
+    V = np.zeros((P, 3, 3))
+    np.add.at(V, pt_idx, b[:, :, None] * b[:, None, :])
+    V += mu * np.eye(3)
+    Vinv = np.linalg.inv(V)
+    gc = np.empty((C, 8))
+    gc[:, :6] = g[:6 * C].reshape(C, 6)
+    gc[:, 6:] = g[6 * C:8 * C].reshape(C, 2)
+    gp = g[8 * C:].reshape(P, 3)
+    # W as sparse (8C x 3P)
+    rows = (8 * cam_idx[:, None, None] + np.arange(8)[None, :, None]) + np.zeros((1, 1, 3), dtype=np.int64)
+    cols = (3 * pt_idx[:, None, None] + np.arange(3)[None, None, :]) + np.zeros((1, 8, 1), dtype=np.int64)
+    vals = a[:, :, None] * b[:, None, :]
+    W = sp.csr_matrix((vals.reshape(-1), (rows.reshape(-1), cols.reshape(-1))), shape=(8 * C, 3 * P))
+    Vinv_bd = sp.block_diag([sp.csr_matrix(Vinv[p]) for p in range(P)], format="csr") if P <= 2000 else \
+        _block_diag3(Vinv)
+    WVi = W @ Vinv_bd
+    S = -(WVi @ W.T).toarray()
+    for c in range(C):
+        S[8 * c:8 * c + 8, 8 * c:8 * c + 8] += U[c] + mu * np.eye(8)
+    rhs = gc.reshape(-1) - WVi @ gp.reshape(-1)
+    cho = scipy.linalg.cho_factor(S, lower=True, check_finite=False)
+    vc = scipy.linalg.cho_solve(cho, rhs, check_finite=False)
+    vp = np.einsum("pij,pj->pi", Vinv, gp - (W.T @ vc).reshape(P, 3))
+    v = np.empty_like(g)
+    vc8 = vc.reshape(C, 8)
+    v[:6 * C] = vc8[:, :6].reshape(-1)
+    v[6 * C:8 * C] = vc8[:, 6:].reshape(-1)
+    v[8 * C:] = vp.reshape(-1)
+    return v
+
+
+def _block_diag3(B):
+    P = B.shape[0]
+    rows = (3 * np.arange(P)[:, None, None] + np.arange(3)[None, :, None]) + np.zeros((1, 1, 3), dtype=np.int64)
+    cols = (3 * np.arange(P)[:, None, None] + np.arange(3)[None, None, :]) + np.zeros((1, 3, 1), dtype=np.int64)
+    return sp.csr_matrix((B.reshape(-1), (rows.reshape(-1), cols.reshape(-1))), shape=(3 * P, 3 * P))
+
+
+# ----------------------------------------------------------------------------- LM state machine
+@dataclass
+class LMTrace:
+    loss: list = field(default_factory=list)        # loss after each update (index 0 = init)
+    grad_l2: list = field(default_factory=list)
+    mu: list = field(default_factory=list)
+    rho: list = field(default_factory=list)
+    accepted: list = field(default_factory=list)
+    inner_iters: list = field(default_factory=list)
+    n_eval_jac: int = 0
+    n_eval_res: int = 0
+
+
+@dataclass
+class LMResult:
+    params: np.ndarray
+    iter_num: int
+    loss: float
+    grad_l2: float
+    damping_factor: float
+    increase_factor: float
+    trace: LMTrace
+
+
+def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6, maxiter=100,
+             damping_parameter=1e-6, solver="exact", round_jac_f32=False, cg_tol=1e-5) -> LMResult:
+    """jaxopt 0.7 LevenbergMarquardt.run as the reference configures it
+    (bundle_adjustment.py:83-91: tol=1e-6, maxiter=100, default solver, 'grad-l2-norm' stop).
+
+    solver: 'exact'     — Schur + dense Cholesky (the parity target)
+            'jaxopt_cg' — the reference's actual inner solver: unpreconditioned CG on the full
+                          normal equations, rel. tol 1e-5, maxiter 10n (`cg_tol` to tighten it)
+    round_jac_f32: emulate fp32 storage of Jacobian rows (design study; gradient stays exact).
+    Accept/reject uses a select instead of jaxopt's arithmetic blend."""
+    cam_idx = np.asarray(cam_idx, dtype=np.int64)
+    pt_idx = np.asarray(pt_idx, dtype=np.int64)
+    w2 = float(avg_cam_width) ** 2
+    x = np.array(x0, dtype=np.float64)
+    tr = LMTrace()
+
+    def evaluate(xx):
+        r, _, a, b = ba_eval(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2)
+        J = ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx)
+        g = J.T @ r
+        if round_jac_f32:
+            a = a.astype(np.float32).astype(np.float64)
+            b = b.astype(np.float32).astype(np.float64)
+            J = ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx)
+        tr.n_eval_jac += 1
+        return r, a, b, J, g
+
+    # init_state
+    r, a, b, J, g = evaluate(x)
+    diag = np.asarray(J.multiply(J).sum(axis=0)).reshape(-1)
+    mu = damping_parameter * float(diag.max())
+    nu = 2.0
+    loss = 0.5 * float(r @ r)
+    err = float(np.linalg.norm(g))
+    it = 0
+    tr.loss.append(loss)
+    tr.grad_l2.append(err)
+    tr.mu.append(mu)
+
+    while True:
+        # ---- update()
+        if solver == "exact":
+            v = _solve_schur_exact(a, b, g, mu, C, P, cam_idx, pt_idx)
+            inner = 0
+        elif solver == "jaxopt_cg":
+            v, inner = _cg_jaxopt(lambda p: J.T @ (J @ p) + mu * p, g, tol=cg_tol)
+        else:
+            raise ValueError(solver)
+        delta = -v
+        x_next = x + delta
+        r_next, _, _, _ = ba_eval(x_next, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=False)
+        tr.n_eval_res += 1
+        loss_next = 0.5 * float(r_next @ r_next)
+        rho = (loss - loss_next) / (0.5 * float(delta @ (mu * delta - g)))
+        ok = bool(rho > 0.0)
+        if ok:
+            x = x_next
+            r, a, b, J, g = evaluate(x)
+            mu = mu * max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)
+            nu = 2.0
+        else:
+            mu = mu * nu
+            nu = 2.0 * nu
+        it += 1
+        loss = 0.5 * float(r @ r)
+        err = float(np.linalg.norm(g))
+        tr.loss.append(loss)
+        tr.grad_l2.append(err)
+        tr.mu.append(mu)
+        tr.rho.append(rho)
+        tr.accepted.append(ok)
+        tr.inner_iters.append(inner)
+        # ---- run(): first update unconditional, then while iter_num < maxiter and error > tol
+        if not (it < maxiter and err > tol):
+            break
+    return LMResult(x, it, loss, err, mu, nu, tr)
