@@ -1,0 +1,119 @@
+/* b200ba — C-ABI of the B200-native Levenberg–Marquardt bundle-adjustment / batched single-pose
+ * hot path.  Plain pointers and sizes only; every array pointer is a DEVICE pointer owned by the
+ * caller unless the name ends in `_host`; `stream` is a cudaStream_t passed as void*.
+ * Every function returns 0 on success, non-zero otherwise (b200ba_last_error() has the text);
+ * nothing throws.  There is no CPU fallback behind any entry point.
+ *
+ * The reference has no FFI layer: its boundary is two Python classes that hand arrays to
+ * jaxopt.  Each entry point names the reference interface it stands in for (paths relative to
+ * /root/reference/src/reconstruction/bundle_adjustment/).
+ */
+#ifndef B200BA_H
+#define B200BA_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200ba_plan b200ba_plan;
+
+enum { B200BA_OK = 0, B200BA_EINVAL = 1, B200BA_ECUDA = 2, B200BA_ENCCL = 3 };
+/* per-solve status bits (b200ba_lm_result.status / pose status[]) */
+enum { B200BA_ST_CONVERGED = 0, B200BA_ST_MAXITER = 1, B200BA_ST_NAN = 2, B200BA_ST_PCG_MAXITER = 4 };
+enum { B200BA_LOSS_L2 = 0, B200BA_LOSS_CAUCHY = 1 }; /* loss.py:7-14 */
+
+const char* b200ba_last_error(void);
+int b200ba_version(void);
+
+/* ---- problem structure (replaces the dense-padded builder the caller feeds to
+ * JaxBundleAdjustment.optimize: benchmark_bundle_adjustment.py:45-106; here one row per VALID
+ * observation, any order, duplicates allowed).  Sorts rows by (point, camera), builds the
+ * camera-major permutation and CSR offsets, sizes all workspaces.  C is the GLOBAL camera
+ * count; P/N are this rank's points / observations (multi-GPU: shard by point). */
+int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_idx, const int32_t* pt_idx,
+                       int jac_f32 /*0: fp64 Jacobian rows (parity default), 1: fp32 rows*/,
+                       void* stream, b200ba_plan** out);
+int b200ba_plan_destroy(b200ba_plan* plan);
+/* obs: N x 2 pixels in the SAME row order as cam_idx/pt_idx given to plan_create
+ * (points_2d_all of bundle_adjustment.py:104-111 with mask==1 rows only). */
+int b200ba_plan_set_observations(b200ba_plan* plan, const double* obs_xy, void* stream);
+/* Optional: sum camera blocks / gradients / PCG dots across ranks (NCCL over NVLink).
+ * unique_id_host: 128 bytes from b200ba_nccl_unique_id on rank 0, broadcast by the caller. */
+int b200ba_nccl_unique_id(char* unique_id_host /*128 B*/);
+int b200ba_plan_set_comm(b200ba_plan* plan, int rank, int nranks, const char* unique_id_host);
+
+/* ---- K1: residual + analytic Jacobian rows (BundleAdjustment.get_residuals,
+ * bundle_adjustment.py:52-74 with reproject_point :17-21, plus the Jacobian jaxopt obtains by
+ * jvp/vjp).  Outputs in the caller's ORIGINAL row order.  cam8: C x 8 = [w(3), t(3), fx, fy];
+ * cam_const3: C x 3 = [cx, cy, skew] (prepare_params :93-102).  Any output may be NULL. */
+int b200ba_residual_jacobian(b200ba_plan* plan, const double* cam8, const double* cam_const3,
+                             const double* pts, double inv_w2, double* r /*N*/,
+                             double* Jc /*N x 8*/, double* Jp /*N x 3*/,
+                             double* cost_host /*0.5*sum r^2*/, void* stream);
+
+/* ---- full LM solve (JaxBundleAdjustment.optimize, bundle_adjustment.py:104-120 =
+ * jaxopt.LevenbergMarquardt(tol=1e-6, maxiter=100).run with its inner linear solve replaced by
+ * Schur elimination of the points + block-Jacobi PCG on the reduced camera system). */
+typedef struct {
+  int maxiter;              /* 100  (bundle_adjustment.py:88) */
+  double tol;               /* 1e-6 (bundle_adjustment.py:86), stop on ||J^T r||_2 <= tol */
+  double damping_parameter; /* 1e-6 (jaxopt default) */
+  double pcg_rtol;          /* ||res||_2 <= pcg_rtol * ||rhs||_2 */
+  int pcg_maxiter;
+  int fixed_pcg_iters;      /* >0: run exactly this many PCG iterations (benchmarking) */
+  int verbose;
+} b200ba_lm_opts;
+
+typedef struct {
+  int iter_num;
+  int status;
+  double loss, grad_l2, damping_factor, increase_factor;
+  int64_t n_jac_evals, n_res_evals, n_pcg_iters_total;
+  /* optional host arrays (may be NULL); capacity maxiter+1 / maxiter */
+  double* loss_trajectory_host; /* [0]=initial loss, [k]=loss after update k */
+  double* grad_trajectory_host;
+  double* mu_trajectory_host;
+  int* pcg_iters_host;
+  int* accepted_host;
+} b200ba_lm_result;
+
+void b200ba_lm_default_opts(b200ba_lm_opts* opts);
+int b200ba_lm_solve(b200ba_plan* plan, double* cam8_inout, const double* cam_const3,
+                    double* pts_inout, double inv_w2, const b200ba_lm_opts* opts,
+                    b200ba_lm_result* result, void* stream);
+
+/* ---- building blocks exposed for parity tests and per-kernel benchmarks.  All operate on the
+ * plan's internal state as left by b200ba_linearize. */
+/* K1+K2: residual, Jacobian rows, U_c (C x 64 row-major, symmetric), g_c (C x 8),
+ * V_p (P x 6: xx,xy,xz,yy,yz,zz), g_p (P x 3).  Output pointers may be NULL. */
+int b200ba_linearize(b200ba_plan* plan, const double* cam8, const double* cam_const3,
+                     const double* pts, double inv_w2, double* U, double* gc, double* V,
+                     double* gp, double* scalars_host /*[loss, |g|^2, max diag]*/, void* stream);
+/* (V+mu I)^-1, reduced rhs, block-Jacobi blocks; then y = S x for a caller vector (C x 8). */
+int b200ba_schur_prepare(b200ba_plan* plan, double mu, double* rhs /*C x 8 or NULL*/, void* stream);
+int b200ba_schur_matvec(b200ba_plan* plan, const double* x, double* y, void* stream);
+/* Solve S v_c = rhs by PCG and back-substitute; v = [v_c (C x 8) | v_p (P x 3)]. */
+int b200ba_schur_solve(b200ba_plan* plan, double rtol, int maxiter, double* vc, double* vp,
+                       int* iters_host, void* stream);
+/* trial cost 0.5*sum r^2 at given parameters (no Jacobian) */
+int b200ba_cost(b200ba_plan* plan, const double* cam8, const double* cam_const3,
+                const double* pts, double inv_w2, double* cost_host, void* stream);
+
+/* ---- K4: batched single-pose LM (JaxPoseOptimizer.optimize, pose_optimization.py:86-89 =
+ * jit(vmap(LevenbergMarquardt(tol=1e-7, maxiter=100, solver="cholesky").run)) over
+ * PoseOptimization.get_residuals :33-52).  One CTA per pose, early exit per pose.
+ * params8: B x 8 in/out; const3: B x 3; points: B x Npts x 3; obs: B x Npts x 2; mask: B x Npts. */
+int b200ba_pose_lm_batched(int B, int Npts, double* params8_inout, const double* const3,
+                           const double* points, const double* obs, const double* mask,
+                           double inv_w2, int loss, int maxiter, double tol,
+                           double damping_parameter, int32_t* iter_num /*B*/,
+                           double* loss_out /*B*/, double* grad_l2 /*B*/,
+                           double* damping_out /*B or NULL*/, int32_t* status /*B*/, void* stream);
+
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+int64_t b200ba_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,311 @@
+// Bundle-adjustment kernels (K0-K3 of SURVEY.md §7.2b), hand-written for sm_100a.
+// Observation rows live in two orders: "ps" = sorted by (point, camera), "cs" = sorted by
+// (camera, point).  JT is the storage type of Jacobian rows (double: parity default; float).
+// All reductions are ordered (no floating-point atomics) so results are bit-reproducible.
+#pragma once
+#include "common.cuh"
+
+template <typename JT>
+__device__ __forceinline__ void load8(const JT* __restrict__ p, double* a);
+template <>
+__device__ __forceinline__ void load8<double>(const double* __restrict__ p, double* a) {
+  const double2* q = reinterpret_cast<const double2*>(p);
+  double2 v0 = __ldg(q), v1 = __ldg(q + 1), v2 = __ldg(q + 2), v3 = __ldg(q + 3);
+  a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y; a[6] = v3.x; a[7] = v3.y;
+}
+template <>
+__device__ __forceinline__ void load8<float>(const float* __restrict__ p, double* a) {
+  const float4* q = reinterpret_cast<const float4*>(p);
+  float4 v0 = __ldg(q), v1 = __ldg(q + 1);
+  a[0] = v0.x; a[1] = v0.y; a[2] = v0.z; a[3] = v0.w; a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
+}
+template <typename JT>
+__device__ __forceinline__ void store8(JT* __restrict__ p, const double* a);
+template <>
+__device__ __forceinline__ void store8<double>(double* __restrict__ p, const double* a) {
+  double2* q = reinterpret_cast<double2*>(p);
+  q[0] = make_double2(a[0], a[1]); q[1] = make_double2(a[2], a[3]);
+  q[2] = make_double2(a[4], a[5]); q[3] = make_double2(a[6], a[7]);
+}
+template <>
+__device__ __forceinline__ void store8<float>(float* __restrict__ p, const double* a) {
+  float4* q = reinterpret_cast<float4*>(p);
+  q[0] = make_float4((float)a[0], (float)a[1], (float)a[2], (float)a[3]);
+  q[1] = make_float4((float)a[4], (float)a[5], (float)a[6], (float)a[7]);
+}
+// point part: 4 JT per row (b0,b1,b2,pad) so a row is one aligned vector load
+template <typename JT>
+__device__ __forceinline__ void load3(const JT* __restrict__ p, double* b);
+template <>
+__device__ __forceinline__ void load3<double>(const double* __restrict__ p, double* b) {
+  const double2* q = reinterpret_cast<const double2*>(p);
+  double2 v0 = __ldg(q), v1 = __ldg(q + 1);
+  b[0] = v0.x; b[1] = v0.y; b[2] = v1.x;
+}
+template <>
+__device__ __forceinline__ void load3<float>(const float* __restrict__ p, double* b) {
+  float4 v = __ldg(reinterpret_cast<const float4*>(p));
+  b[0] = v.x; b[1] = v.y; b[2] = v.z;
+}
+template <typename JT>
+__device__ __forceinline__ void store3(JT* __restrict__ p, const double* b);
+template <>
+__device__ __forceinline__ void store3<double>(double* __restrict__ p, const double* b) {
+  double2* q = reinterpret_cast<double2*>(p);
+  q[0] = make_double2(b[0], b[1]); q[1] = make_double2(b[2], 0.0);
+}
+template <>
+__device__ __forceinline__ void store3<float>(float* __restrict__ p, const double* b) {
+  *reinterpret_cast<float4*>(p) = make_float4((float)b[0], (float)b[1], (float)b[2], 0.f);
+}
+
+// ---------------------------------------------------------------- K0: camera tables
+__global__ void k_cam_table(int C, const double* __restrict__ cam8, const double* __restrict__ k3,
+                            double* __restrict__ tab) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) build_cam_table(cam8 + 8 * c, k3 + 3 * c, tab + (size_t)TAB_STRIDE * c);
+}
+
+// ---------------------------------------------------------------- K1: residual + Jacobian rows
+// One thread per observation in ps order.  Writes r and the Jacobian row in ps order and the
+// camera part again at the row's cs position (64/32 B aligned scatter = whole sectors), which
+// the camera-side reductions then stream.  cost_part[block] = sum r^2 of the block.
+template <typename JT, bool WITH_JAC>
+__global__ void __launch_bounds__(256)
+k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
+         const double2* __restrict__ obs_ps, const double* __restrict__ tab,
+         const double* __restrict__ pts, double inv_w2, const int32_t* __restrict__ inv_cs,
+         double* __restrict__ r_ps, JT* __restrict__ Jc_ps, JT* __restrict__ Jp_ps,
+         JT* __restrict__ Jc_cs, double* __restrict__ r_cs, double* __restrict__ cost_part) {
+  __shared__ double sm[32];
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double v[1] = {0.0};
+  if (i < N) {
+    const int c = __ldg(cam_ps + i), p = __ldg(pt_ps + i);
+    const double* T = tab + (size_t)TAB_STRIDE * c;
+    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1),
+                 Z = __ldg(pts + 3 * (size_t)p + 2);
+    const double2 o = __ldg(obs_ps + i);
+    const Proj pr = project(T, X, Y, Z);
+    const double dx = pr.u - o.x, dy = pr.v - o.y;
+    const double r = (dx * dx + dy * dy) * inv_w2;
+    v[0] = r * r;
+    if (WITH_JAC) {
+      double a[8], b[3];
+      jac_row(T, pr, X, Y, Z, 2.0 * dx * inv_w2, 2.0 * dy * inv_w2, a, b);
+      r_ps[i] = r;
+      store8<JT>(Jc_ps + 8 * i, a);
+      store3<JT>(Jp_ps + 4 * i, b);
+      const int64_t j = __ldg(inv_cs + i);
+      store8<JT>(Jc_cs + 8 * j, a);
+      r_cs[j] = r;
+    } else if (r_ps) {
+      r_ps[i] = r;
+    }
+  }
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) cost_part[blockIdx.x] = v[0];
+}
+
+// ---------------------------------------------------------------- K2a: 3x3 point blocks
+// One thread per point walks its (short) ps run.  V_p = sum b b^T (6 unique), g_p = sum b r.
+// part[2*block+0] = sum |g_p|^2, part[2*block+1] = max diag V.
+template <typename JT>
+__global__ void __launch_bounds__(256)
+k_point_blocks(int P, const int32_t* __restrict__ pt_ptr, const JT* __restrict__ Jp_ps,
+               const double* __restrict__ r_ps, double* __restrict__ V, double* __restrict__ gp,
+               double* __restrict__ part) {
+  __shared__ double sm[32];
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  double g2[1] = {0.0};
+  double md = 0.0;
+  if (p < P) {
+    double v[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+    const int e = pt_ptr[p + 1];
+    for (int i = pt_ptr[p]; i < e; ++i) {
+      double b[3];
+      load3<JT>(Jp_ps + 4 * (size_t)i, b);
+      const double r = __ldg(r_ps + i);
+      v[0] += b[0] * b[0]; v[1] += b[0] * b[1]; v[2] += b[0] * b[2];
+      v[3] += b[1] * b[1]; v[4] += b[1] * b[2]; v[5] += b[2] * b[2];
+      g[0] += b[0] * r; g[1] += b[1] * r; g[2] += b[2] * r;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) V[6 * (size_t)p + k] = v[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gp[3 * (size_t)p + k] = g[k];
+    g2[0] = g[0] * g[0] + g[1] * g[1] + g[2] * g[2];
+    md = fmax(v[0], fmax(v[3], v[5]));
+  }
+  block_sum<1>(g2, sm);
+  const double m = block_max1(md, sm);
+  if (threadIdx.x == 0) {
+    part[2 * blockIdx.x] = g2[0];
+    part[2 * blockIdx.x + 1] = m;
+  }
+}
+
+// ---------------------------------------------------------------- K2b: 8x8 camera blocks
+// One CTA per camera streams its cs rows.  Each thread keeps 36 + 8 fp64 accumulators; ordered
+// CTA reduction.  If beta != nullptr the rows are weighted: out = -sum beta_i a a^T and
+// -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs); otherwise
+// U_c = sum a a^T and g_c = sum a r.
+template <typename JT>
+__global__ void __launch_bounds__(256)
+k_cam_blocks(const int32_t* __restrict__ cam_ptr, const JT* __restrict__ Jc_cs,
+             const double* __restrict__ s_cs, const int32_t* __restrict__ perm_cs,
+             const double* __restrict__ w_ps, const double* __restrict__ beta_ps,
+             double* __restrict__ U, double* __restrict__ gc) {
+  __shared__ double sm[44 * 32];
+  const int c = blockIdx.x;
+  const int beg = cam_ptr[c], end = cam_ptr[c + 1];
+  double acc[44];
+#pragma unroll
+  for (int k = 0; k < 44; ++k) acc[k] = 0.0;
+  for (int j = beg + threadIdx.x; j < end; j += blockDim.x) {
+    double a[8];
+    load8<JT>(Jc_cs + 8 * (size_t)j, a);
+    double s, wgt;
+    if (beta_ps) {
+      const int i = __ldg(perm_cs + j);
+      s = -__ldg(w_ps + i);
+      wgt = -__ldg(beta_ps + i);
+    } else {
+      s = __ldg(s_cs + j);
+      wgt = 1.0;
+    }
+    int t = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const double ak = a[k] * wgt;
+#pragma unroll
+      for (int l = k; l < 8; ++l) acc[t++] += ak * a[l];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[36 + k] += a[k] * s;
+  }
+  block_sum<44>(acc, sm);
+  if (threadIdx.x == 0) {
+    int t = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+#pragma unroll
+      for (int l = k; l < 8; ++l) {
+        U[64 * (size_t)c + 8 * k + l] = acc[t];
+        U[64 * (size_t)c + 8 * l + k] = acc[t];
+        ++t;
+      }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) gc[8 * (size_t)c + k] = acc[36 + k];
+  }
+}
+
+// per-camera scalars after the (all-reduced) blocks: part[2c] = |g_c|^2, part[2c+1] = max diag U_c
+__global__ void k_cam_scalars(int C, const double* __restrict__ U, const double* __restrict__ gc,
+                              double* __restrict__ part) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double g2 = 0.0, md = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const double g = gc[8 * (size_t)c + k];
+    g2 += g * g;
+    md = fmax(md, U[64 * (size_t)c + 9 * k]);
+  }
+  part[2 * c] = g2;
+  part[2 * c + 1] = md;
+}
+
+__device__ __forceinline__ void inv3_sym(const double* v, double mu, double* o) {
+  const double a = v[0] + mu, b = v[1], c = v[2], d = v[3] + mu, e = v[4], f = v[5] + mu;
+  const double c00 = d * f - e * e, c01 = c * e - b * f, c02 = b * e - c * d;
+  const double det = a * c00 + b * c01 + c * c02;
+  const double id = 1.0 / det;
+  o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id;
+  o[3] = (a * f - c * c) * id; o[4] = (b * c - a * e) * id; o[5] = (a * d - b * b) * id;
+}
+
+// ---------------------------------------------------------------- K3a: point-block inverses
+// Vinv_p = (V_p + mu I)^-1; per row w_i = b_i . (Vinv g_p) and beta_i = b_i^T Vinv b_i.
+template <typename JT>
+__global__ void __launch_bounds__(256)
+k_point_prepare(int P, const double* __restrict__ mu_ptr, const int32_t* __restrict__ pt_ptr,
+                const JT* __restrict__ Jp_ps, const double* __restrict__ V,
+                const double* __restrict__ gp, double* __restrict__ Vinv, double* __restrict__ w_ps,
+                double* __restrict__ beta_ps) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const double mu = *mu_ptr;
+  double v[6], vi[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) v[k] = V[6 * (size_t)p + k];
+  inv3_sym(v, mu, vi);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) Vinv[6 * (size_t)p + k] = vi[k];
+  const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
+  const double z0 = vi[0] * g0 + vi[1] * g1 + vi[2] * g2;
+  const double z1 = vi[1] * g0 + vi[3] * g1 + vi[4] * g2;
+  const double z2 = vi[2] * g0 + vi[4] * g1 + vi[5] * g2;
+  const int e = pt_ptr[p + 1];
+  for (int i = pt_ptr[p]; i < e; ++i) {
+    double b[3];
+    load3<JT>(Jp_ps + 4 * (size_t)i, b);
+    w_ps[i] = b[0] * z0 + b[1] * z1 + b[2] * z2;
+    const double t0 = vi[0] * b[0] + vi[1] * b[1] + vi[2] * b[2];
+    const double t1 = vi[1] * b[0] + vi[3] * b[1] + vi[4] * b[2];
+    const double t2 = vi[2] * b[0] + vi[4] * b[1] + vi[5] * b[2];
+    beta_ps[i] = b[0] * t0 + b[1] * t1 + b[2] * t2;
+  }
+}
+
+// rhs = g_c + rhs_part; Minv_c = (U_c + mu I + Sd_part)^-1 (8x8, Cholesky, one thread per camera);
+// PCG start: x = 0, r = rhs, z = Minv r, p = z; part[2c] = r.z, part[2c+1] = r.r
+__global__ void __launch_bounds__(64)
+k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __restrict__ U,
+                     const double* __restrict__ gc, const double* __restrict__ Sd_part,
+                     const double* __restrict__ rhs_part, double* __restrict__ Minv,
+                     double* __restrict__ rhs, double* __restrict__ x, double* __restrict__ r,
+                     double* __restrict__ z, double* __restrict__ pv, double* __restrict__ part) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mu = *mu_ptr;
+  double A[64], L[64], e[8], Mi[64];
+#pragma unroll
+  for (int k = 0; k < 64; ++k) A[k] = U[64 * (size_t)c + k] + Sd_part[64 * (size_t)c + k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) A[9 * k] += mu;
+#pragma unroll
+  for (int col = 0; col < 8; ++col) {
+#pragma unroll
+    for (int k = 0; k < 64; ++k) L[k] = A[k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) e[k] = (k == col) ? 1.0 : 0.0;
+    chol8_solve(L, e);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) Mi[8 * k + col] = e[k];
+  }
+  double rr[8], zz[8];
+  double rz = 0.0, r2 = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) rr[k] = gc[8 * (size_t)c + k] + rhs_part[8 * (size_t)c + k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    double s = 0.0;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) s += 0.5 * (Mi[8 * k + l] + Mi[8 * l + k]) * rr[l];
+    zz[k] = s;
+    rz += s * rr[k];
+    r2 += rr[k] * rr[k];
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+#pragma unroll
+    for (int l = 0; l < 8; ++l) Minv[64 * (size_t)c + 8 * k + l] = 0.5 * (Mi[8 * k + l] + Mi[8 * l + k]);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const size_t o = 8 * (size_t)c + k;
+    rhs[o] = rr[k]; x[o] = 0.0; r[o] = rr[k]; z[o] = zz[k]; pv[o] = zz[k];
+  }
+  part[2 * c] = rz;
+  part[2 * c + 1] = r2;
+}

@@ -1,0 +1,182 @@
+// Shared device helpers for the b200ba kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define TAB_STRIDE 32  // doubles per camera-table row (256 B, sector aligned)
+// table layout: R[0..8] row-major, t[9..11], M[12..20] row-major, fx 21, fy 22, cx 23, cy 24, skew 25
+
+// Device-side solver state, shared by all LM / PCG kernels (one per plan).
+struct SolverState {
+  double mu, nu, loss, loss_trial, grad2, maxdiag, rho, denom;
+  double rz, rz_new, pAp, rr, rhs2, alpha, beta, vg, vv;
+  int accepted, pcg_done, pcg_iters, status;
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Deterministic CTA-wide sum of NV values per thread. Result valid in thread 0 (all threads of
+// warp 0 hold it). `sm` needs NV * 32 doubles. All threads must call.
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* sm) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) v[k] = warp_sum(v[k]);
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) sm[k * 32 + wid] = v[k];
+  }
+  __syncthreads();
+  if (wid == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      double x = (lane < nw) ? sm[k * 32 + lane] : 0.0;
+      v[k] = warp_sum(x);
+    }
+  }
+}
+
+__device__ __forceinline__ double block_max1(double v, double* sm) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_max(v);
+  __syncthreads();
+  if (lane == 0) sm[wid] = v;
+  __syncthreads();
+  double x = -1.0;
+  if (wid == 0) {
+    x = (lane < nw) ? sm[lane] : -1.0;
+    x = warp_max(x);
+  }
+  return x;
+}
+
+// Projection chain shared by the BA and pose kernels.
+struct Proj {
+  double q0, q1, q2, iz, u, v;
+};
+__device__ __forceinline__ Proj project(const double* __restrict__ T, double X, double Y, double Z) {
+  Proj p;
+  p.q0 = fma(T[0], X, fma(T[1], Y, fma(T[2], Z, T[9])));
+  p.q1 = fma(T[3], X, fma(T[4], Y, fma(T[5], Z, T[10])));
+  p.q2 = fma(T[6], X, fma(T[7], Y, fma(T[8], Z, T[11])));
+  p.iz = 1.0 / p.q2;
+  p.u = (T[21] * p.q0 + T[25] * p.q1) * p.iz + T[23];
+  p.v = T[22] * p.q1 * p.iz + T[24];
+  return p;
+}
+
+// Jacobian row from d r/d(u,v) = (ex, ey): a[8] = camera part [w, t, fx, fy], b[3] = point part.
+__device__ __forceinline__ void jac_row(const double* __restrict__ T, const Proj& p, double X, double Y,
+                                        double Z, double ex, double ey, double* a, double* b) {
+  const double fx = T[21], fy = T[22], s = T[25];
+  const double e0 = ex * fx * p.iz;
+  const double e1 = (ex * s + ey * fy) * p.iz;
+  const double e2 = -(ex * (fx * p.q0 + s * p.q1) + ey * fy * p.q1) * p.iz * p.iz;
+  b[0] = T[0] * e0 + T[3] * e1 + T[6] * e2;  // R^T eq
+  b[1] = T[1] * e0 + T[4] * e1 + T[7] * e2;
+  b[2] = T[2] * e0 + T[5] * e1 + T[8] * e2;
+  const double c0 = Y * b[2] - Z * b[1];  // X x b
+  const double c1 = Z * b[0] - X * b[2];
+  const double c2 = X * b[1] - Y * b[0];
+  a[0] = c0 * T[12] + c1 * T[15] + c2 * T[18];  // (X x b)^T M
+  a[1] = c0 * T[13] + c1 * T[16] + c2 * T[19];
+  a[2] = c0 * T[14] + c1 * T[17] + c2 * T[20];
+  a[3] = e0;
+  a[4] = e1;
+  a[5] = e2;
+  a[6] = ex * p.q0 * p.iz;
+  a[7] = ey * p.q1 * p.iz;
+}
+
+// Camera table row from [w,t,fx,fy] + [cx,cy,skew]: Rodrigues as utils.py:21-28 (no small-angle
+// guard: NaN at w=0 like the reference) and M = (w w^T + (R^T - I)[w]x)/|w|^2.
+__device__ __forceinline__ void build_cam_table(const double* __restrict__ c8, const double* __restrict__ k3,
+                                                double* __restrict__ T) {
+  const double w0 = c8[0], w1 = c8[1], w2 = c8[2];
+  const double th2 = w0 * w0 + w1 * w1 + w2 * w2;
+  const double th = sqrt(th2);
+  const double k0 = w0 / th, k1 = w1 / th, k2 = w2 / th;
+  double sn, cs;
+  sincos(th, &sn, &cs);
+  const double oc = 1.0 - cs;
+  double R[9];
+  R[0] = cs + oc * k0 * k0;
+  R[1] = oc * k0 * k1 - sn * k2;
+  R[2] = oc * k0 * k2 + sn * k1;
+  R[3] = oc * k1 * k0 + sn * k2;
+  R[4] = cs + oc * k1 * k1;
+  R[5] = oc * k1 * k2 - sn * k0;
+  R[6] = oc * k2 * k0 - sn * k1;
+  R[7] = oc * k2 * k1 + sn * k0;
+  R[8] = cs + oc * k2 * k2;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) T[i] = R[i];
+  T[9] = c8[3];
+  T[10] = c8[4];
+  T[11] = c8[5];
+  // A = R^T - I ; [w]x = [[0,-w2,w1],[w2,0,-w0],[-w1,w0,0]]
+  const double A[9] = {R[0] - 1.0, R[3], R[6], R[1], R[4] - 1.0, R[7], R[2], R[5], R[8] - 1.0};
+  const double w[3] = {w0, w1, w2};
+  const double Wx[9] = {0.0, -w2, w1, w2, 0.0, -w0, -w1, w0, 0.0};
+  const double inv = 1.0 / th2;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double m = w[i] * w[j];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) m += A[i * 3 + k] * Wx[k * 3 + j];
+      T[12 + i * 3 + j] = m * inv;
+    }
+  T[21] = c8[6];
+  T[22] = c8[7];
+  T[23] = k3[0];
+  T[24] = k3[1];
+  T[25] = k3[2];
+}
+
+// In-place Cholesky solve of the 8x8 SPD system A x = b held in registers/local arrays by ONE
+// thread.  A is full row-major (only the lower triangle is read). NaN on a non-positive pivot,
+// like LAPACK posv through jax (sqrt of a negative).
+__device__ __forceinline__ void chol8_solve(double* A, double* b) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    double d = A[j * 8 + j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= A[j * 8 + k] * A[j * 8 + k];
+    d = sqrt(d);
+    A[j * 8 + j] = d;
+    const double id = 1.0 / d;
+#pragma unroll
+    for (int i = j + 1; i < 8; ++i) {
+      double s = A[i * 8 + j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) s -= A[i * 8 + k] * A[j * 8 + k];
+      A[i * 8 + j] = s * id;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    double s = b[i];
+#pragma unroll
+    for (int k = 0; k < i; ++k) s -= A[i * 8 + k] * b[k];
+    b[i] = s / A[i * 8 + i];
+  }
+#pragma unroll
+  for (int i = 7; i >= 0; --i) {
+    double s = b[i];
+#pragma unroll
+    for (int k = i + 1; k < 8; ++k) s -= A[k * 8 + i] * b[k];
+    b[i] = s / A[i * 8 + i];
+  }
+}
