@@ -1,0 +1,628 @@
+// b200ba — C-ABI + host-side driver of the B200-native LM bundle-adjustment / pose hot path.
+// See include/b200ba.h for the contract.  Host code only sequences kernels on the caller's
+// stream; all arithmetic and all accept/reject/convergence decisions happen on the device.
+#include "../../include/b200ba.h"
+
+#include <cub/cub.cuh>
+#include <nccl.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ba_pcg.cuh"
+#include "pose_kernels.cuh"
+
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_) + " @" + __FILE__ + ":" + \
+              std::to_string(__LINE__);                                                  \
+      return B200BA_ECUDA;                                                               \
+    }                                                                                    \
+  } while (0)
+#define CKN(call)                                                                        \
+  do {                                                                                   \
+    ncclResult_t e_ = (call);                                                            \
+    if (e_ != ncclSuccess) {                                                             \
+      g_err = std::string(#call) + ": " + ncclGetErrorString(e_);                        \
+      return B200BA_ENCCL;                                                               \
+    }                                                                                    \
+  } while (0)
+#define LAUNCH(kern, grid, block, smem, st, ...)                                         \
+  do {                                                                                   \
+    kern<<<(grid), (block), (smem), (st)>>>(__VA_ARGS__);                                \
+    ++g_launches;                                                                        \
+  } while (0)
+#define FAIL(code, msg) \
+  do {                  \
+    g_err = (msg);      \
+    return (code);      \
+  } while (0)
+
+static inline unsigned cdiv(int64_t a, int64_t b) { return (unsigned)((a + b - 1) / b); }
+
+struct b200ba_plan {
+  int C = 0, P = 0;
+  int64_t N = 0;
+  int jac_f32 = 0;
+  size_t jsz = 8;
+  // structure (device)
+  int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // ps rows
+  int32_t *perm_cs = nullptr, *inv_cs = nullptr;                     // cs<->ps
+  int32_t *pt_ptr = nullptr, *cam_ptr = nullptr;
+  double2* obs_ps = nullptr;
+  // linearisation
+  void *Jc_ps = nullptr, *Jp_ps = nullptr, *Jc_cs = nullptr;
+  double *r_ps = nullptr, *r_cs = nullptr, *w_ps = nullptr, *beta_ps = nullptr;
+  double *tab = nullptr, *tab_trial = nullptr;
+  double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
+  double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
+  double *x = nullptr, *r = nullptr, *z = nullptr, *pv = nullptr, *y = nullptr, *vp = nullptr;
+  double *cam_trial = nullptr, *pts_trial = nullptr;
+  double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
+  SolverState* st = nullptr;
+  SolverState* st_host = nullptr;  // pinned
+  double* scal_host = nullptr;     // pinned, 16 doubles
+  int nblkN = 0, nblkP = 0;
+  // comm
+  ncclComm_t comm = nullptr;
+  int rank = 0, nranks = 1;
+  std::vector<void*> allocs;
+};
+
+template <typename T>
+static int dalloc(b200ba_plan* p, T** ptr, size_t n) {
+  void* q = nullptr;
+  CK(cudaMalloc(&q, (n ? n : 1) * sizeof(T)));
+  p->allocs.push_back(q);
+  *ptr = (T*)q;
+  return 0;
+}
+
+extern "C" const char* b200ba_last_error(void) { return g_err.c_str(); }
+extern "C" int b200ba_version(void) { return 100; }
+extern "C" int64_t b200ba_launch_count(void) { return g_launches.load(); }
+
+// ---------------------------------------------------------------- plan construction kernels
+__global__ void k_make_keys(int64_t N, const int32_t* __restrict__ cam, const int32_t* __restrict__ pt,
+                            int64_t mul_a, int which, int64_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  keys[i] = which == 0 ? (int64_t)pt[i] * mul_a + cam[i] : (int64_t)cam[i] * mul_a + pt[i];
+  vals[i] = (int32_t)i;
+}
+__global__ void k_gather_i32(int64_t N, const int32_t* __restrict__ idx, const int32_t* __restrict__ src,
+                             int32_t* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) dst[i] = src[idx[i]];
+}
+__global__ void k_invert_perm(int64_t N, const int32_t* __restrict__ perm, int32_t* __restrict__ inv) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) inv[perm[i]] = (int32_t)i;
+}
+// ptr[s] = first row whose (sorted) segment id >= s  (binary search; handles empty segments)
+__global__ void k_segment_ptr(int nseg, int64_t N, const int32_t* __restrict__ seg_sorted,
+                              int32_t* __restrict__ ptr) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s > nseg) return;
+  int64_t lo = 0, hi = N;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (seg_sorted[mid] < s) lo = mid + 1; else hi = mid;
+  }
+  ptr[s] = (int32_t)lo;
+}
+__global__ void k_check_range(int64_t N, const int32_t* __restrict__ a, int hi, int* __restrict__ bad) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N && (a[i] < 0 || a[i] >= hi)) *bad = 1;
+}
+__global__ void k_permute_obs(int64_t N, const int32_t* __restrict__ order_ps, const double* __restrict__ obs,
+                              double2* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) {
+    const int64_t o = order_ps[i];
+    out[i] = make_double2(obs[2 * o], obs[2 * o + 1]);
+  }
+}
+
+static int bits_for(int64_t v) {
+  int b = 1;
+  while ((1LL << b) <= v && b < 63) ++b;
+  return b;
+}
+
+extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_idx, const int32_t* pt_idx,
+                                  int jac_f32, void* stream_, b200ba_plan** out) {
+  if (!out || C <= 0 || P < 0 || N < 0 || N >= (1LL << 31)) FAIL(B200BA_EINVAL, "plan_create: bad sizes");
+  if (N > 0 && (!cam_idx || !pt_idx)) FAIL(B200BA_EINVAL, "plan_create: null index arrays");
+  cudaStream_t s = (cudaStream_t)stream_;
+  b200ba_plan* p = new b200ba_plan();
+  p->C = C; p->P = P; p->N = N; p->jac_f32 = jac_f32 ? 1 : 0; p->jsz = jac_f32 ? 4 : 8;
+  int rc = 0;
+#define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
+  A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(perm_cs, N) A(inv_cs, N)
+  A(pt_ptr, P + 1) A(cam_ptr, C + 1) A(obs_ps, N)
+  A(r_ps, N) A(r_cs, N) A(w_ps, N) A(beta_ps, N)
+  A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
+  A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
+  A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
+  A(x, (size_t)C * 8) A(r, (size_t)C * 8) A(z, (size_t)C * 8) A(pv, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
+  A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts_trial, (size_t)P * 3)
+  p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
+  p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
+  p->lin_scal = p->gc + (size_t)C * 8;
+  p->nblkN = (int)cdiv(N, 256); p->nblkP = (int)cdiv(P, 256);
+  A(part, 2 * (size_t)C + 16) A(part2, 2 * (size_t)C + 16)
+  A(partN, 2 * (size_t)(p->nblkN > p->nblkP ? p->nblkN : p->nblkP) + 16) A(scal, 32) A(st, 1)
+#undef A
+  {
+    void* q = nullptr;
+    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_ps"); }
+    p->allocs.push_back(q); p->Jc_ps = q;
+    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_cs"); }
+    p->allocs.push_back(q); p->Jc_cs = q;
+    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 4 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
+    p->allocs.push_back(q); p->Jp_ps = q;
+  }
+  if (cudaMallocHost((void**)&p->st_host, sizeof(SolverState)) != cudaSuccess ||
+      cudaMallocHost((void**)&p->scal_host, 32 * sizeof(double)) != cudaSuccess) {
+    b200ba_plan_destroy(p);
+    FAIL(B200BA_ECUDA, "cudaMallocHost failed");
+  }
+  cudaMemsetAsync(p->st, 0, sizeof(SolverState), s);
+
+  if (N > 0) {
+    // validate, then sort rows by (point, camera) and by (camera, point) with CUB radix sort
+    int* bad = nullptr;
+    int64_t *keys = nullptr, *keys2 = nullptr;
+    int32_t *vals = nullptr, *tmp_i = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0;
+    cudaMalloc(&bad, sizeof(int));
+    cudaMemsetAsync(bad, 0, sizeof(int), s);
+    LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, cam_idx, C, bad);
+    LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, pt_idx, P, bad);
+    int bad_h = 0;
+    cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaStreamSynchronize(s);
+    cudaFree(bad);
+    if (bad_h) { b200ba_plan_destroy(p); FAIL(B200BA_EINVAL, "plan_create: index out of range"); }
+    cudaMalloc(&keys, N * sizeof(int64_t)); cudaMalloc(&keys2, N * sizeof(int64_t));
+    cudaMalloc(&vals, N * sizeof(int32_t)); cudaMalloc(&tmp_i, N * sizeof(int32_t));
+    const int nb = bits_for((int64_t)P * C + C);
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
+    cudaMalloc(&tmp, tmp_bytes);
+    // ps order
+    LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, cam_idx, pt_idx, (int64_t)C, 0, keys, vals);
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
+    LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, cam_idx, p->cam_ps);
+    LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, pt_idx, p->pt_ps);
+    LAUNCH(k_segment_ptr, cdiv(P + 1, 256), 256, 0, s, P, N, p->pt_ps, p->pt_ptr);
+    // cs order (indices into ps rows)
+    LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, p->cam_ps, p->pt_ps, (int64_t)P, 1, keys, vals);
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->perm_cs, (int)N, 0, nb, s);
+    LAUNCH(k_invert_perm, cdiv(N, 256), 256, 0, s, N, p->perm_cs, p->inv_cs);
+    LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->perm_cs, p->cam_ps, tmp_i);
+    LAUNCH(k_segment_ptr, cdiv(C + 1, 256), 256, 0, s, C, N, tmp_i, p->cam_ptr);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(tmp_i); cudaFree(tmp);
+    if (e != cudaSuccess || (e = cudaGetLastError()) != cudaSuccess) {
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, std::string("plan_create: ") + cudaGetErrorString(e));
+    }
+  } else {
+    cudaMemsetAsync(p->pt_ptr, 0, (P + 1) * sizeof(int32_t), s);
+    cudaMemsetAsync(p->cam_ptr, 0, (C + 1) * sizeof(int32_t), s);
+    cudaStreamSynchronize(s);
+  }
+  *out = p;
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
+  if (!p) return B200BA_OK;
+  for (void* q : p->allocs) cudaFree(q);
+  if (p->st_host) cudaFreeHost(p->st_host);
+  if (p->scal_host) cudaFreeHost(p->scal_host);
+  if (p->comm) ncclCommDestroy(p->comm);
+  delete p;
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_plan_set_observations(b200ba_plan* p, const double* obs_xy, void* stream_) {
+  if (!p || (p->N > 0 && !obs_xy)) FAIL(B200BA_EINVAL, "set_observations: null");
+  cudaStream_t s = (cudaStream_t)stream_;
+  if (p->N) LAUNCH(k_permute_obs, cdiv(p->N, 256), 256, 0, s, p->N, p->order_ps, obs_xy, p->obs_ps);
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_nccl_unique_id(char* out) {
+  if (!out) FAIL(B200BA_EINVAL, "null");
+  ncclUniqueId id;
+  CKN(ncclGetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  memcpy(out, &id, 128);
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const char* uid) {
+  if (!p || !uid || nranks < 1 || rank < 0 || rank >= nranks) FAIL(B200BA_EINVAL, "set_comm: bad args");
+  if (nranks == 1) return B200BA_OK;
+  ncclUniqueId id;
+  memcpy(&id, uid, 128);
+  CKN(ncclCommInitRank(&p->comm, nranks, id, rank));
+  p->rank = rank;
+  p->nranks = nranks;
+  return B200BA_OK;
+}
+
+// ---------------------------------------------------------------- solver steps
+// lin_scal (device, after the blocks): [0] sum r^2, [1] |g_p|^2 (both rank-local before the
+// all-reduce); scal: [2] max diag V (local), [3] |g_c|^2, [4] max diag U
+__global__ void k_lin_state(SolverState* st, const double* lin_scal, const double* scal, int init,
+                            double damping) {
+  if (threadIdx.x || blockIdx.x) return;
+  st->loss = 0.5 * lin_scal[0];
+  st->grad2 = lin_scal[1] + scal[3];
+  st->maxdiag = fmax(scal[2], scal[4]);
+  if (init) {
+    st->mu = damping * st->maxdiag;
+    st->nu = 2.0;
+    st->accepted = 0;
+    st->status = 0;
+  }
+}
+
+static int allreduce(b200ba_plan* p, double* buf, size_t n, ncclRedOp_t op, cudaStream_t s) {
+  if (p->nranks > 1) CKN(ncclAllReduce(buf, buf, n, ncclDouble, op, p->comm, s));
+  return 0;
+}
+
+template <typename JT>
+struct Ops {
+  static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
+                       cudaStream_t s) {
+    const int C = p->C, P = p->P;
+    const int64_t N = p->N;
+    LAUNCH(k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
+    if (N) {
+      LAUNCH((k_resjac<JT, true>), p->nblkN, 256, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
+             p->inv_cs, p->r_ps, (JT*)p->Jc_ps, (JT*)p->Jp_ps, (JT*)p->Jc_cs, p->r_cs, p->partN);
+    }
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
+    if (P) LAUNCH((k_point_blocks<JT>), p->nblkP, 256, 0, s, P, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
+    LAUNCH((k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, p->r_cs, nullptr, nullptr, nullptr,
+           p->U, p->gc);
+    int rc;
+    if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
+    if ((rc = allreduce(p, p->scal + 2, 1, ncclMax, s))) return rc;
+    LAUNCH(k_cam_scalars, cdiv(C, 128), 128, 0, s, C, p->U, p->gc, p->part);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 3, 2);
+    CK(cudaGetLastError());
+    return 0;
+  }
+
+  // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start
+  static int prepare(b200ba_plan* p, cudaStream_t s) {
+    const int C = p->C, P = p->P;
+    if (P) LAUNCH((k_point_prepare<JT>), p->nblkP, 256, 0, s, P, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
+                  p->gp, p->Vinv, p->w_ps, p->beta_ps);
+    LAUNCH((k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, nullptr, p->perm_cs, p->w_ps,
+           p->beta_ps, p->Sd, p->rhs_part);
+    int rc;
+    if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
+    LAUNCH(k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part, p->Minv,
+           p->rhs, p->x, p->r, p->z, p->pv, p->part2);
+    LAUNCH((k_pcg_dir<true>), 1, 256, 0, s, C, p->st, p->part2, p->z, p->pv, 0.0, 0);
+    CK(cudaGetLastError());
+    return 0;
+  }
+
+  // y = S x for the current pv (x_in copied to pv by caller) — one PCG matvec
+  static int matvec(b200ba_plan* p, cudaStream_t s) {
+    const int C = p->C, P = p->P;
+    if (P) LAUNCH((k_mv_pt<JT, false>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
+                  (const JT*)p->Jp_ps, p->Vinv, p->pv, p->w_ps, nullptr, nullptr, nullptr);
+    if (p->nranks == 1) {
+      LAUNCH((k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
+             p->pv, p->y, p->part);
+    } else {
+      LAUNCH((k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
+             p->pv, p->y, p->part);
+      int rc;
+      if ((rc = allreduce(p, p->y, (size_t)C * 8, ncclSum, s))) return rc;
+      LAUNCH(k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, p->pv, p->y, p->part);
+    }
+    return 0;
+  }
+
+  static int pcg_iteration(b200ba_plan* p, double rtol, int maxiter, cudaStream_t s) {
+    const int C = p->C;
+    int rc;
+    if ((rc = matvec(p, s))) return rc;
+    LAUNCH(k_pcg_update, cdiv(C, 256), 256, 0, s, C, p->st, p->part, p->Minv, p->pv, p->y, p->x, p->r, p->z, p->part2);
+    LAUNCH((k_pcg_dir<false>), cdiv(C, 256), 256, 0, s, C, p->st, p->part2, p->z, p->pv, rtol, maxiter);
+    LAUNCH(k_pcg_commit, 1, 256, 0, s, C, p->st, p->part2, rtol, maxiter);
+    return 0;
+  }
+
+  // run PCG to convergence; device-side flag, host polls every `chunk` iterations
+  static int pcg_solve(b200ba_plan* p, double rtol, int maxiter, int fixed_iters, int* iters_out, cudaStream_t s) {
+    int rc;
+    int done = 0, launched = 0;
+    const int limit = fixed_iters > 0 ? fixed_iters : maxiter;
+    const double rt = fixed_iters > 0 ? 0.0 : rtol;
+    int chunk = fixed_iters > 0 ? fixed_iters : 16;
+    while (!done && launched < limit) {
+      const int n = (limit - launched) < chunk ? (limit - launched) : chunk;
+      for (int k = 0; k < n; ++k)
+        if ((rc = pcg_iteration(p, rt, limit, s))) return rc;
+      launched += n;
+      CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+      done = p->st_host->pcg_done;
+      chunk = 8;
+    }
+    if (iters_out) *iters_out = p->st_host->pcg_iters;
+    return 0;
+  }
+
+  static int backsub(b200ba_plan* p, cudaStream_t s) {
+    const int P = p->P;
+    if (P) LAUNCH((k_mv_pt<JT, true>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
+                  (const JT*)p->Jp_ps, p->Vinv, p->x, nullptr, p->gp, p->vp, p->partN);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+    return 0;
+  }
+
+  static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
+                  double* out_dev, cudaStream_t s) {
+    LAUNCH(k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
+    if (p->N)
+      LAUNCH((k_resjac<JT, false>), p->nblkN, 256, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
+             inv_w2, p->inv_cs, nullptr, nullptr, nullptr, nullptr, nullptr, p->partN);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
+    return 0;
+  }
+};
+
+// scal[8] = sum r^2 (trial), [9] = v_p.g_p, [10] = |v_p|^2 (rank-local; all-reduced), then add the
+// replicated camera parts -> decide input [8],[11],[12]
+__global__ void k_pack_decide(double* scal) {
+  if (threadIdx.x || blockIdx.x) return;
+  scal[11] = scal[9] + scal[13];   // vg
+  scal[12] = scal[10] + scal[14];  // vv
+  scal[9] = scal[11];
+  scal[10] = scal[12];
+}
+
+#define DISPATCH(p, fn, ...) ((p)->jac_f32 ? Ops<float>::fn(__VA_ARGS__) : Ops<double>::fn(__VA_ARGS__))
+
+static int read_state(b200ba_plan* p, cudaStream_t s) {
+  CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
+                                double inv_w2, double* U, double* gc, double* V, double* gp,
+                                double* scalars_host, void* stream_) {
+  if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "linearize: null");
+  cudaStream_t s = (cudaStream_t)stream_;
+  int rc;
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, 1e-6);
+  if (U) CK(cudaMemcpyAsync(U, p->U, (size_t)p->C * 64 * 8, cudaMemcpyDeviceToDevice, s));
+  if (gc) CK(cudaMemcpyAsync(gc, p->gc, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  if (V) CK(cudaMemcpyAsync(V, p->V, (size_t)p->P * 6 * 8, cudaMemcpyDeviceToDevice, s));
+  if (gp) CK(cudaMemcpyAsync(gp, p->gp, (size_t)p->P * 3 * 8, cudaMemcpyDeviceToDevice, s));
+  if (scalars_host) {
+    if ((rc = read_state(p, s))) return rc;
+    scalars_host[0] = p->st_host->loss;
+    scalars_host[1] = p->st_host->grad2;
+    scalars_host[2] = p->st_host->maxdiag;
+  }
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_residual_jacobian(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
+                                        double inv_w2, double* r, double* Jc, double* Jp, double* cost_host,
+                                        void* stream_) {
+  int rc = b200ba_linearize(p, cam8, k3, pts, inv_w2, nullptr, nullptr, nullptr, nullptr, nullptr, stream_);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream_;
+  const int64_t N = p->N;
+  if (N) {
+    if (r) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->r_ps, 1, 1, r);
+    if (p->jac_f32) {
+      if (Jc) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jc_ps, 8, 8, Jc);
+      if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, 4, 3, Jp);
+    } else {
+      if (Jc) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jc_ps, 8, 8, Jc);
+      if (Jp) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jp_ps, 4, 3, Jp);
+    }
+  }
+  if (cost_host) {
+    if ((rc = read_state(p, s))) return rc;
+    *cost_host = p->st_host->loss;
+  }
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+__global__ void k_set_mu(SolverState* st, double mu) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) st->mu = mu;
+}
+__global__ void k_clear_done(SolverState* st) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) st->pcg_done = 0;
+}
+
+extern "C" int b200ba_schur_prepare(b200ba_plan* p, double mu, double* rhs, void* stream_) {
+  if (!p) FAIL(B200BA_EINVAL, "null plan");
+  cudaStream_t s = (cudaStream_t)stream_;
+  LAUNCH(k_set_mu, 1, 1, 0, s, p->st, mu);
+  int rc;
+  if ((rc = DISPATCH(p, prepare, p, s))) return rc;
+  if (rhs) CK(cudaMemcpyAsync(rhs, p->rhs, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_schur_matvec(b200ba_plan* p, const double* x, double* y, void* stream_) {
+  if (!p || !x || !y) FAIL(B200BA_EINVAL, "null");
+  cudaStream_t s = (cudaStream_t)stream_;
+  // uses pv as the input vector; the PCG state is clobbered (call schur_prepare again before a solve)
+  CK(cudaMemcpyAsync(p->pv, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  LAUNCH(k_clear_done, 1, 1, 0, s, p->st);
+  int rc;
+  if ((rc = DISPATCH(p, matvec, p, s))) return rc;
+  CK(cudaMemcpyAsync(y, p->y, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_schur_solve(b200ba_plan* p, double rtol, int maxiter, double* vc, double* vp, int* iters_host,
+                                  void* stream_) {
+  if (!p) FAIL(B200BA_EINVAL, "null plan");
+  cudaStream_t s = (cudaStream_t)stream_;
+  int rc;
+  if ((rc = DISPATCH(p, pcg_solve, p, rtol, maxiter, 0, iters_host, s))) return rc;
+  if ((rc = DISPATCH(p, backsub, p, s))) return rc;
+  if (vc) CK(cudaMemcpyAsync(vc, p->x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  if (vp) CK(cudaMemcpyAsync(vp, p->vp, (size_t)p->P * 3 * 8, cudaMemcpyDeviceToDevice, s));
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
+                           double* cost_host, void* stream_) {
+  if (!p || !cost_host) FAIL(B200BA_EINVAL, "null");
+  cudaStream_t s = (cudaStream_t)stream_;
+  int rc;
+  if ((rc = DISPATCH(p, cost, p, cam8, k3, pts, inv_w2, p->scal + 8, s))) return rc;
+  if ((rc = allreduce(p, p->scal + 8, 1, ncclSum, s))) return rc;
+  CK(cudaMemcpyAsync(p->scal_host, p->scal + 8, 8, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  *cost_host = 0.5 * p->scal_host[0];
+  return B200BA_OK;
+}
+
+extern "C" void b200ba_lm_default_opts(b200ba_lm_opts* o) {
+  if (!o) return;
+  o->maxiter = 100;
+  o->tol = 1e-6;
+  o->damping_parameter = 1e-6;
+  o->pcg_rtol = 1e-12;
+  o->pcg_maxiter = 1000;
+  o->fixed_pcg_iters = 0;
+  o->verbose = 0;
+}
+
+extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, double* pts, double inv_w2,
+                               const b200ba_lm_opts* opts, b200ba_lm_result* res, void* stream_) {
+  if (!p || !cam8 || !k3 || (p->P && !pts) || !opts || !res) FAIL(B200BA_EINVAL, "lm_solve: null");
+  cudaStream_t s = (cudaStream_t)stream_;
+  const int C = p->C, P = p->P;
+  int rc;
+  res->n_jac_evals = res->n_res_evals = res->n_pcg_iters_total = 0;
+  // init_state
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, opts->damping_parameter);
+  if ((rc = read_state(p, s))) return rc;
+  res->n_jac_evals++;
+  double err = sqrt(p->st_host->grad2);
+  if (res->loss_trajectory_host) res->loss_trajectory_host[0] = p->st_host->loss;
+  if (res->grad_trajectory_host) res->grad_trajectory_host[0] = err;
+  if (res->mu_trajectory_host) res->mu_trajectory_host[0] = p->st_host->mu;
+  int it = 0;
+  int status = 0;
+  while (opts->maxiter > 0) {
+    // ---- update(): solve (J^T J + mu I) v = g through the reduced camera system
+    if ((rc = DISPATCH(p, prepare, p, s))) return rc;
+    int pcg_iters = 0;
+    if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
+    res->n_pcg_iters_total += pcg_iters;
+    if ((rc = DISPATCH(p, backsub, p, s))) return rc;
+    LAUNCH(k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->x, p->gc, p->cam_trial, p->part);
+    LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
+    if (P) LAUNCH(k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
+    if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts_trial, inv_w2, p->scal + 8, s))) return rc;
+    res->n_res_evals++;
+    if ((rc = allreduce(p, p->scal + 8, 3, ncclSum, s))) return rc;
+    LAUNCH(k_pack_decide, 1, 1, 0, s, p->scal);
+    LAUNCH(k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
+    LAUNCH(k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
+    if (P) LAUNCH(k_accept_copy, cdiv(3 * (int64_t)P, 256), 256, 0, s, p->st, 3 * (int64_t)P, p->pts_trial, pts);
+    if ((rc = read_state(p, s))) return rc;
+    const int accepted = p->st_host->accepted;
+    if (accepted) {
+      if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+      LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
+      if ((rc = read_state(p, s))) return rc;
+      res->n_jac_evals++;
+      err = sqrt(p->st_host->grad2);
+    }
+    ++it;
+    if (res->loss_trajectory_host) res->loss_trajectory_host[it] = p->st_host->loss;
+    if (res->grad_trajectory_host) res->grad_trajectory_host[it] = err;
+    if (res->mu_trajectory_host) res->mu_trajectory_host[it] = p->st_host->mu;
+    if (res->pcg_iters_host) res->pcg_iters_host[it - 1] = pcg_iters;
+    if (res->accepted_host) res->accepted_host[it - 1] = accepted;
+    if (opts->verbose)
+      fprintf(stderr, "[b200ba] it %d loss %.9e |g| %.3e mu %.3e rho %.3e acc %d pcg %d\n", it, p->st_host->loss, err,
+              p->st_host->mu, p->st_host->rho, accepted, pcg_iters);
+    status |= p->st_host->status;
+    if (!(it < opts->maxiter && err > opts->tol)) break;  // run(): NaN error also stops (NaN > tol is false)
+  }
+  if (err > opts->tol) status |= B200BA_ST_MAXITER;
+  if (!(p->st_host->loss == p->st_host->loss) || !(err == err)) status |= B200BA_ST_NAN;
+  res->iter_num = it;
+  res->status = status;
+  res->loss = p->st_host->loss;
+  res->grad_l2 = err;
+  res->damping_factor = p->st_host->mu;
+  res->increase_factor = p->st_host->nu;
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_pose_lm_batched(int B, int Npts, double* params8, const double* const3, const double* points,
+                                      const double* obs, const double* mask, double inv_w2, int loss, int maxiter,
+                                      double tol, double damping, int32_t* iter_num, double* loss_out, double* grad_l2,
+                                      double* damping_out, int32_t* status, void* stream_) {
+  if (B < 0 || Npts < 0 || (B && (!params8 || !const3 || !iter_num || !loss_out || !grad_l2 || !status)))
+    FAIL(B200BA_EINVAL, "pose_lm_batched: bad args");
+  if (B && Npts && (!points || !obs || !mask)) FAIL(B200BA_EINVAL, "pose_lm_batched: null data");
+  if (loss != B200BA_LOSS_L2 && loss != B200BA_LOSS_CAUCHY) FAIL(B200BA_EINVAL, "pose_lm_batched: unknown loss");
+  if (B == 0) return B200BA_OK;
+  cudaStream_t s = (cudaStream_t)stream_;
+  size_t smem = sizeof(PoseShared);
+  const size_t stage = (size_t)Npts * 6 * sizeof(double);
+  int stage_smem = 0;
+  if (smem + stage <= 200 * 1024) {
+    smem += stage;
+    stage_smem = 1;
+  }
+  if (loss == B200BA_LOSS_CAUCHY) {
+    CK(cudaFuncSetAttribute(k_pose_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LAUNCH(k_pose_lm<1>, B, POSE_THREADS, smem, s, B, Npts, stage_smem, params8, const3, points, obs, mask, inv_w2,
+           maxiter, tol, damping, iter_num, loss_out, grad_l2, damping_out, status);
+  } else {
+    CK(cudaFuncSetAttribute(k_pose_lm<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LAUNCH(k_pose_lm<0>, B, POSE_THREADS, smem, s, B, Npts, stage_smem, params8, const3, points, obs, mask, inv_w2,
+           maxiter, tol, damping, iter_num, loss_out, grad_l2, damping_out, status);
+  }
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
