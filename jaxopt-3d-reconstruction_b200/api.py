@@ -1,0 +1,405 @@
+"""Host-side mirror of the reference's optimiser façade (the drop-in boundary).
+
+  B200BundleAdjustment  <->  JaxBundleAdjustment   (bundle_adjustment.py:77-129)
+  B200PoseOptimizer     <->  JaxPoseOptimizer      (pose_optimization.py:55-99)
+
+Same method names, argument meaning, parameter packing and error behaviour (the solver never
+raises on NaN; it propagates into the outputs and the caller checks, `helpers.py:24-27,82-85`).
+Arrays come in as NumPy (or torch) host arrays, are copied to the GPU, solved by the CUDA library
+through its C-ABI, and copied back.  torch is used for device memory, streams and
+torch.distributed only.  No CPU path: without a GPU / without libb200ba.so these raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LMOpts, LMResult, check
+
+L2, CAUCHY = 0, 1
+
+
+class LossFunction:
+    """Stand-in for JaxLossFunction (loss.py:17-19)."""
+    L2 = L2
+    CAUCHY = CAUCHY
+
+
+def pose_mat_to_vec(pose):
+    """[R|t] (...,3,4) -> [w, t] (...,6); host NumPy like the reference (utils.py:31-44)."""
+    pose = np.asarray(pose, dtype=np.float64)
+    R = pose[..., :3, :3]
+    n = np.zeros(R.shape[:-2] + (3,))
+    angle = np.arccos(np.clip((R[..., 0, 0] + R[..., 1, 1] + R[..., 2, 2] - 1) / 2, -1, 1))
+    n[..., 0] = R[..., 2, 1] - R[..., 1, 2]
+    n[..., 1] = R[..., 0, 2] - R[..., 2, 0]
+    n[..., 2] = R[..., 1, 0] - R[..., 0, 1]
+    norms = np.linalg.norm(n, axis=-1)
+    nz = norms != 0
+    n[nz] *= (angle[nz] / norms[nz])[..., None]
+    return np.concatenate([n, pose[..., :3, 3]], axis=-1)
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise _lib.B200BAError("b200ba needs a CUDA device (sm_100a); there is no CPU fallback")
+    return _lib.load()
+
+
+def _dev(a, dtype, device):
+    """host/any array -> contiguous device tensor (pinned staging for large host arrays)."""
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype, non_blocking=True).contiguous()
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if t.dtype != dtype:
+        t = t.to(dtype)
+    return t.to(device, non_blocking=True)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+@dataclass
+class LMState:
+    """The fields of jaxopt's LevenbergMarquardtState that the reference's callers read
+    (`benchmark_bundle_adjustment.py:183,196`; `benchmark_pose_optimization.py:190-191,237-239`)
+    plus solver diagnostics."""
+    iter_num: object
+    loss: object
+    error: object               # ||J^T r||_2
+    damping_factor: object
+    increase_factor: object = None
+    status: object = None
+    gradient: object = None
+    loss_trajectory: object = None
+    grad_trajectory: object = None
+    mu_trajectory: object = None
+    pcg_iters: object = None
+    accepted: object = None
+    n_jac_evals: int = 0
+    n_res_evals: int = 0
+    aux: dict = field(default_factory=dict)
+
+
+class BAProblem:
+    """Problem structure resident on the GPU: plan (sorted rows, CSR, workspaces) + observations."""
+
+    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=False):
+        lib = _require_cuda()
+        self.lib = lib
+        self.C, self.P, self.N = int(C_), int(P), int(cam_idx.numel())
+        self.device = device
+        self.cam_idx = cam_idx
+        self.pt_idx = pt_idx
+        plan = C.c_void_p()
+        with torch.cuda.device(device):
+            check(lib.b200ba_plan_create(self.C, self.P, self.N, _ptr(cam_idx), _ptr(pt_idx),
+                                         int(bool(jac_f32)), _stream(), C.byref(plan)), "plan_create")
+            self.plan = plan
+            check(lib.b200ba_plan_set_observations(plan, _ptr(obs), _stream()), "set_observations")
+            torch.cuda.current_stream().synchronize()
+
+    def close(self):
+        if getattr(self, "plan", None):
+            self.lib.b200ba_plan_destroy(self.plan)
+            self.plan = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def shard_points(pt_idx: np.ndarray, P: int, world: int):
+    """Contiguous point ranges balanced by observation count.
+    Returns bounds (world+1,) such that rank r owns points [bounds[r], bounds[r+1])."""
+    counts = np.bincount(np.asarray(pt_idx, dtype=np.int64), minlength=P)
+    cum = np.concatenate([[0], np.cumsum(counts)])
+    total = cum[-1]
+    bounds = np.searchsorted(cum, np.arange(world + 1) * (total / world), side="left")
+    bounds[0], bounds[-1] = 0, P
+    return np.maximum.accumulate(np.minimum(bounds, P)).astype(np.int64)
+
+
+class B200BundleAdjustment:
+    """Drop-in for JaxBundleAdjustment(cam_num, avg_cam_width)."""
+
+    def __init__(self, cam_num, avg_cam_width, device=None, tol=1e-6, maxiter=100,
+                 damping_parameter=1e-6, pcg_rtol=1e-12, pcg_maxiter=1000, jac_f32=False,
+                 verbose=False, process_group=None, distributed=None):
+        self.cam_num = int(cam_num)
+        self.avg_cam_width_sqr = float(avg_cam_width) ** 2
+        self.device = torch.device(device if device is not None else "cuda")
+        self.tol, self.maxiter, self.damping_parameter = tol, maxiter, damping_parameter
+        self.pcg_rtol, self.pcg_maxiter = pcg_rtol, pcg_maxiter
+        self.jac_f32, self.verbose = jac_f32, verbose
+        self.fixed_pcg_iters = 0
+        self.group = process_group
+        import torch.distributed as dist
+        self.world = dist.get_world_size(process_group) if (distributed if distributed is not None else dist.is_initialized()) else 1
+        self.rank = dist.get_rank(process_group) if self.world > 1 else 0
+        self._cache = None  # (arrays, BAProblem)
+
+    # ------------------------------------------------------------------ reference API
+    def prepare_params(self, poses0, intrinsics0, points0):
+        """bundle_adjustment.py:93-102: opt_params = [C*6 | C*2 | P*3], cx_cy_skew (C,3)."""
+        intrinsics0 = np.asarray(intrinsics0, dtype=np.float64)
+        cam = pose_mat_to_vec(np.asarray(poses0, dtype=np.float64)).reshape(-1)
+        opt = np.concatenate([cam, intrinsics0[..., :2].reshape(-1),
+                              np.asarray(points0, dtype=np.float64).reshape(-1)])
+        return opt, intrinsics0[..., 2:].copy()
+
+    def compile(self, points_num=0, indices_num=0):
+        """bundle_adjustment.py:122-129 warms the XLA cache; here: load the library and create
+        the CUDA context (nothing is shape-specialised)."""
+        _require_cuda()
+        torch.zeros(1, device=self.device)
+        torch.cuda.synchronize(self.device)
+
+    def optimize(self, opt_params, points_2d_all, p3d_indices_all=None, cx_cy_skew=None, masks_all=None):
+        """bundle_adjustment.py:104-120.  `points_2d_all` may also be a BAProblem built by
+        build_problem()/build_problem_sparse() (then indices/masks are ignored)."""
+        if isinstance(points_2d_all, BAProblem):
+            prob = points_2d_all
+        else:
+            key = (points_2d_all, p3d_indices_all, masks_all)
+            if self._cache is not None and all(a is b for a, b in zip(self._cache[0], key)):
+                prob = self._cache[1]
+            else:
+                n_pts = (np.asarray(opt_params).shape[0] - 8 * self.cam_num) // 3
+                prob = self.build_problem(points_2d_all, p3d_indices_all, masks_all, n_pts)
+                self._cache = (key, prob)
+        return self._solve(opt_params, cx_cy_skew, prob)
+
+    # ------------------------------------------------------------------ problem builders
+    def build_problem(self, points_2d_all, p3d_indices_all, masks_all, points_num):
+        """Dense padded (C,Nmax) arrays -> sparse rows on the device (mask==1 only; padded slots
+        contribute exactly zero in the reference, `benchmark_bundle_adjustment.py:81-84`)."""
+        _require_cuda()
+        dev = self.device
+        mask = _dev(masks_all, torch.float64, dev)
+        idx = _dev(p3d_indices_all, torch.int64, dev)
+        p2d = _dev(points_2d_all, torch.float64, dev)
+        sel = mask != 0
+        cam_idx = sel.nonzero()[:, 0].to(torch.int32)
+        pt_idx = idx[sel].to(torch.int32)
+        obs = p2d[sel].contiguous()
+        return self.build_problem_sparse(cam_idx, pt_idx, obs, points_num)
+
+    def build_problem_sparse(self, cam_idx, pt_idx, obs, points_num):
+        """One row per observation (any order). With torch.distributed initialised the rows are
+        sharded by point range across ranks (each rank passes the FULL problem)."""
+        _require_cuda()
+        dev = self.device
+        cam_idx = _dev(cam_idx, torch.int32, dev)
+        pt_idx = _dev(pt_idx, torch.int32, dev)
+        obs = _dev(obs, torch.float64, dev)
+        P = int(points_num)
+        lo, hi = 0, P
+        if self.world > 1:
+            bounds = shard_points(pt_idx.cpu().numpy(), P, self.world)
+            lo, hi = int(bounds[self.rank]), int(bounds[self.rank + 1])
+            keep = (pt_idx >= lo) & (pt_idx < hi)
+            cam_idx, pt_idx, obs = cam_idx[keep].contiguous(), (pt_idx[keep] - lo).contiguous(), obs[keep].contiguous()
+        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32)
+        prob.pt_lo, prob.pt_hi, prob.P_global = lo, hi, P
+        if self.world > 1:
+            self._init_comm(prob)
+        return prob
+
+    def _init_comm(self, prob):
+        import torch.distributed as dist
+        uid = torch.zeros(128, dtype=torch.uint8)
+        if self.rank == 0:
+            buf = C.create_string_buffer(128)
+            check(prob.lib.b200ba_nccl_unique_id(buf), "nccl_unique_id")
+            uid = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+        backend = dist.get_backend(self.group)
+        t = uid.to(self.device) if backend == "nccl" else uid
+        dist.broadcast(t, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        raw = bytes(t.cpu().numpy().tobytes())
+        with torch.cuda.device(self.device):
+            check(prob.lib.b200ba_plan_set_comm(prob.plan, self.rank, self.world, raw), "set_comm")
+
+    # ------------------------------------------------------------------ solve
+    def _solve(self, opt_params, cx_cy_skew, prob: BAProblem):
+        lib = prob.lib
+        Cn, dev = self.cam_num, self.device
+        x = np.asarray(opt_params, dtype=np.float64) if not isinstance(opt_params, torch.Tensor) else opt_params
+        xd = _dev(x, torch.float64, dev)
+        cam8 = torch.cat([xd[:6 * Cn].view(Cn, 6), xd[6 * Cn:8 * Cn].view(Cn, 2)], dim=1).contiguous()
+        pts_all = xd[8 * Cn:].view(-1, 3)
+        pts = pts_all[prob.pt_lo:prob.pt_hi].contiguous().clone()
+        k3 = _dev(cx_cy_skew, torch.float64, dev)
+        opts = LMOpts()
+        lib.b200ba_lm_default_opts(C.byref(opts))
+        opts.maxiter, opts.tol, opts.damping_parameter = int(self.maxiter), float(self.tol), float(self.damping_parameter)
+        opts.pcg_rtol, opts.pcg_maxiter = float(self.pcg_rtol), int(self.pcg_maxiter)
+        opts.fixed_pcg_iters, opts.verbose = int(self.fixed_pcg_iters), int(bool(self.verbose))
+        m = max(int(self.maxiter), 1)
+        loss_t = (C.c_double * (m + 1))()
+        grad_t = (C.c_double * (m + 1))()
+        mu_t = (C.c_double * (m + 1))()
+        pcg_t = (C.c_int * m)()
+        acc_t = (C.c_int * m)()
+        res = LMResult()
+        res.loss_trajectory_host = C.cast(loss_t, C.POINTER(C.c_double))
+        res.grad_trajectory_host = C.cast(grad_t, C.POINTER(C.c_double))
+        res.mu_trajectory_host = C.cast(mu_t, C.POINTER(C.c_double))
+        res.pcg_iters_host = C.cast(pcg_t, C.POINTER(C.c_int))
+        res.accepted_host = C.cast(acc_t, C.POINTER(C.c_int))
+        with torch.cuda.device(dev):
+            check(lib.b200ba_lm_solve(prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts),
+                                      1.0 / self.avg_cam_width_sqr, C.byref(opts), C.byref(res), _stream()), "lm_solve")
+        if self.world > 1:
+            import torch.distributed as dist
+            sizes = [None] * self.world
+            dist.all_gather_object(sizes, int(pts.shape[0]), group=self.group)
+            if dist.get_backend(self.group) == "nccl":
+                parts = [torch.empty(s, 3, dtype=torch.float64, device=dev) for s in sizes]
+                dist.all_gather(parts, pts, group=self.group)
+            else:
+                parts = [torch.empty(s, 3, dtype=torch.float64) for s in sizes]
+                dist.all_gather(parts, pts.cpu(), group=self.group)
+                parts = [q.to(dev) for q in parts]
+            pts_full = torch.cat(parts, dim=0)
+        else:
+            pts_full = pts
+        out = torch.cat([cam8[:, :6].reshape(-1), cam8[:, 6:].reshape(-1), pts_full.reshape(-1)]).cpu().numpy()
+        n = res.iter_num
+        state = LMState(iter_num=n, loss=res.loss, error=res.grad_l2, damping_factor=res.damping_factor,
+                        increase_factor=res.increase_factor, status=res.status,
+                        loss_trajectory=np.array(loss_t[:n + 1]), grad_trajectory=np.array(grad_t[:n + 1]),
+                        mu_trajectory=np.array(mu_t[:n + 1]), pcg_iters=np.array(pcg_t[:n]),
+                        accepted=np.array(acc_t[:n]), n_jac_evals=res.n_jac_evals, n_res_evals=res.n_res_evals)
+        return out, state
+
+
+class B200PoseOptimizer:
+    """Drop-in for JaxPoseOptimizer(avg_cam_width, loss_fn=JaxLossFunction.CAUCHY)."""
+
+    def __init__(self, avg_cam_width, loss_fn=CAUCHY, device=None, tol=1e-7, maxiter=100,
+                 damping_parameter=1e-6):
+        self.avg_cam_width_sqr = float(avg_cam_width) ** 2
+        self.loss_fn = int(loss_fn)
+        self.device = torch.device(device if device is not None else "cuda")
+        self.tol, self.maxiter, self.damping_parameter = tol, maxiter, damping_parameter
+
+    def prepare_params(self, poses0, intrinsics0):
+        """pose_optimization.py:73-84: (B,8) = [w, t, fx, fy], cx_cy_skew (B,3)."""
+        intrinsics0 = np.asarray(intrinsics0, dtype=np.float64)
+        cam = pose_mat_to_vec(np.asarray(poses0, dtype=np.float64))
+        return np.concatenate([cam, intrinsics0[..., :2]], axis=-1), intrinsics0[..., 2:].copy()
+
+    def compile(self, points_num=0, batch_size=8):
+        _require_cuda()
+        torch.zeros(1, device=self.device)
+        torch.cuda.synchronize(self.device)
+
+    def optimize_device(self, params, points, observations, cx_cy_skew, mask):
+        """Device tensors in (params is updated IN PLACE), device tensors out. No host copies."""
+        lib = _require_cuda()
+        B, N = int(points.shape[0]), int(points.shape[1])
+        dev = params.device
+        it = torch.empty(B, dtype=torch.int32, device=dev)
+        st = torch.empty(B, dtype=torch.int32, device=dev)
+        loss = torch.empty(B, dtype=torch.float64, device=dev)
+        err = torch.empty(B, dtype=torch.float64, device=dev)
+        mu = torch.empty(B, dtype=torch.float64, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.b200ba_pose_lm_batched(B, N, _ptr(params), _ptr(cx_cy_skew), _ptr(points), _ptr(observations),
+                                             _ptr(mask), 1.0 / self.avg_cam_width_sqr, self.loss_fn, int(self.maxiter),
+                                             float(self.tol), float(self.damping_parameter), _ptr(it), _ptr(loss),
+                                             _ptr(err), _ptr(mu), _ptr(st), _stream()), "pose_lm_batched")
+        return params, it, loss, err, mu, st
+
+    def optimize(self, opt_params, points, observations, cx_cy_skew, mask):
+        """pose_optimization.py:86-89. Host arrays in, (params (B,8), state) out; inputs untouched."""
+        _require_cuda()
+        dev = self.device
+        p = _dev(opt_params, torch.float64, dev).clone()
+        pts = _dev(points, torch.float64, dev)
+        obs = _dev(observations, torch.float64, dev)
+        k3 = _dev(cx_cy_skew, torch.float64, dev)
+        m = _dev(mask, torch.float64, dev)
+        p, it, loss, err, mu, st = self.optimize_device(p, pts, obs, k3, m)
+        out = torch.cat([p, loss[:, None], err[:, None], mu[:, None], it.to(torch.float64)[:, None],
+                         st.to(torch.float64)[:, None]], dim=1).cpu().numpy()  # one D2H copy
+        state = LMState(iter_num=out[:, 11].astype(np.int64), loss=out[:, 8].copy(), error=out[:, 9].copy(),
+                        damping_factor=out[:, 10].copy(), status=out[:, 12].astype(np.int64))
+        return out[:, :8].copy(), state
+
+
+# ---------------------------------------------------------------------- building blocks (tests, bench)
+class BAKernels:
+    """Thin per-kernel access used by the parity tests and per-kernel benchmarks."""
+
+    def __init__(self, prob: BAProblem, avg_cam_width):
+        self.prob, self.lib = prob, prob.lib
+        self.inv_w2 = 1.0 / float(avg_cam_width) ** 2
+        self.dev = prob.device
+
+    def residual_jacobian(self, cam8, k3, pts):
+        N, d = self.prob.N, self.dev
+        r = torch.empty(N, dtype=torch.float64, device=d)
+        Jc = torch.empty(N, 8, dtype=torch.float64, device=d)
+        Jp = torch.empty(N, 3, dtype=torch.float64, device=d)
+        cost = C.c_double()
+        with torch.cuda.device(d):
+            check(self.lib.b200ba_residual_jacobian(self.prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts), self.inv_w2,
+                                                    _ptr(r), _ptr(Jc), _ptr(Jp), C.byref(cost), _stream()), "residual_jacobian")
+        return r, Jc, Jp, cost.value
+
+    def linearize(self, cam8, k3, pts, want_blocks=True, want_scalars=True):
+        Cn, P, d = self.prob.C, self.prob.P, self.dev
+        U = torch.empty(Cn, 8, 8, dtype=torch.float64, device=d) if want_blocks else None
+        gc = torch.empty(Cn, 8, dtype=torch.float64, device=d) if want_blocks else None
+        V = torch.empty(P, 6, dtype=torch.float64, device=d) if want_blocks else None
+        gp = torch.empty(P, 3, dtype=torch.float64, device=d) if want_blocks else None
+        sc = (C.c_double * 3)()
+        with torch.cuda.device(d):
+            check(self.lib.b200ba_linearize(self.prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts), self.inv_w2, _ptr(U),
+                                            _ptr(gc), _ptr(V), _ptr(gp),
+                                            C.cast(sc, C.POINTER(C.c_double)) if want_scalars else None, _stream()), "linearize")
+        return U, gc, V, gp, (sc[0], sc[1], sc[2])
+
+    def schur_prepare(self, mu, want_rhs=True):
+        rhs = torch.empty(self.prob.C, 8, dtype=torch.float64, device=self.dev) if want_rhs else None
+        with torch.cuda.device(self.dev):
+            check(self.lib.b200ba_schur_prepare(self.prob.plan, float(mu), _ptr(rhs), _stream()), "schur_prepare")
+        return rhs
+
+    def schur_matvec(self, x, y=None):
+        y = torch.empty_like(x) if y is None else y
+        with torch.cuda.device(self.dev):
+            check(self.lib.b200ba_schur_matvec(self.prob.plan, _ptr(x), _ptr(y), _stream()), "schur_matvec")
+        return y
+
+    def schur_solve(self, rtol=1e-12, maxiter=1000):
+        vc = torch.empty(self.prob.C, 8, dtype=torch.float64, device=self.dev)
+        vp = torch.empty(self.prob.P, 3, dtype=torch.float64, device=self.dev)
+        it = C.c_int()
+        with torch.cuda.device(self.dev):
+            check(self.lib.b200ba_schur_solve(self.prob.plan, float(rtol), int(maxiter), _ptr(vc), _ptr(vp), C.byref(it), _stream()), "schur_solve")
+        return vc, vp, it.value
+
+    def cost(self, cam8, k3, pts):
+        c = C.c_double()
+        with torch.cuda.device(self.dev):
+            check(self.lib.b200ba_cost(self.prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts), self.inv_w2, C.byref(c), _stream()), "cost")
+        return c.value
+
+
+def launch_count() -> int:
+    return int(_lib.load().b200ba_launch_count())
