@@ -1,0 +1,96 @@
+"""GPU parity tests proper: CUDA path (through the C-ABI) vs the float64 oracle on the same
+seeded inputs.  Tolerances: per-iteration cost 1e-5 rel, final RMS 1e-4 rel (north_star)."""
+import numpy as np
+import pytest
+import torch
+
+import b200ba
+from oracle import ba_oracle as bo
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(shape, seed=0, jac_f32=False, **kw):
+    sc = b200ba.synth.make_ba_scene(shape, seed=seed, **kw)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=jac_f32)
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    return sc, ba, x0, k3
+
+
+def _dev_params(x0, k3, C):
+    xd = torch.from_numpy(x0).cuda()
+    cam8 = torch.cat([xd[:6 * C].view(C, 6), xd[6 * C:8 * C].view(C, 2)], 1).contiguous()
+    pts = xd[8 * C:].view(-1, 3).contiguous()
+    return cam8, torch.from_numpy(k3).cuda(), pts
+
+
+@pytest.mark.parametrize("shape", ["tiny", "small", "ladybug49"])
+def test_residual_jacobian_rows(shape):
+    sc, ba, x0, k3 = _setup(shape)
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    K = b200ba.BAKernels(prob, sc.avg_cam_width)
+    cam8, k3d, pts = _dev_params(x0, k3, sc.C)
+    r, Jc, Jp, cost = K.residual_jacobian(cam8, k3d, pts)
+    ro, _, a, b = bo.ba_eval(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width ** 2)
+    np.testing.assert_allclose(r.cpu().numpy(), ro, rtol=1e-10, atol=1e-18)
+    np.testing.assert_allclose(Jc.cpu().numpy(), a, rtol=1e-9, atol=1e-12 * np.abs(a).max())
+    np.testing.assert_allclose(Jp.cpu().numpy(), b, rtol=1e-9, atol=1e-12 * np.abs(b).max())
+    assert cost == pytest.approx(0.5 * float(ro @ ro), rel=1e-12)
+
+
+@pytest.mark.parametrize("shape", ["tiny", "small", "ladybug49"])
+def test_schur_blocks_and_step(shape):
+    sc, ba, x0, k3 = _setup(shape)
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    K = b200ba.BAKernels(prob, sc.avg_cam_width)
+    cam8, k3d, pts = _dev_params(x0, k3, sc.C)
+    U, gc, V, gp, (loss, g2, maxdiag) = K.linearize(cam8, k3d, pts)
+    ci, pi = sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)
+    r, _, a, b = bo.ba_eval(x0, sc.C, ci, pi, sc.obs, k3, sc.avg_cam_width ** 2)
+    Uo = np.zeros((sc.C, 8, 8)); np.add.at(Uo, ci, a[:, :, None] * a[:, None, :])
+    Vo = np.zeros((sc.P, 3, 3)); np.add.at(Vo, pi, b[:, :, None] * b[:, None, :])
+    gco = np.zeros((sc.C, 8)); np.add.at(gco, ci, a * r[:, None])
+    gpo = np.zeros((sc.P, 3)); np.add.at(gpo, pi, b * r[:, None])
+    np.testing.assert_allclose(U.cpu().numpy(), Uo, rtol=1e-9, atol=1e-12 * np.abs(Uo).max())
+    Vf = V.cpu().numpy()
+    np.testing.assert_allclose(Vf, Vo[:, [0, 0, 0, 1, 1, 2], [0, 1, 2, 1, 2, 2]], rtol=1e-9, atol=1e-12 * np.abs(Vo).max())
+    np.testing.assert_allclose(gc.cpu().numpy(), gco, rtol=1e-9, atol=1e-12 * np.abs(gco).max())
+    np.testing.assert_allclose(gp.cpu().numpy(), gpo, rtol=1e-9, atol=1e-12 * np.abs(gpo).max())
+    md = max(np.einsum("cii->ci", Uo).max(), np.einsum("pii->pi", Vo).max())
+    assert maxdiag == pytest.approx(md, rel=1e-12)
+    assert g2 == pytest.approx((gco ** 2).sum() + (gpo ** 2).sum(), rel=1e-10)
+    # one damped solve vs the exact Schur/Cholesky oracle solve
+    mu = 1e-6 * md
+    g = np.concatenate([gco[:, :6].reshape(-1), gco[:, 6:].reshape(-1), gpo.reshape(-1)])
+    v = bo._solve_schur_exact(a, b, g, mu, sc.C, sc.P, ci, pi)
+    K.schur_prepare(mu)
+    vc, vp, iters = K.schur_solve(rtol=1e-13, maxiter=2000)
+    vco = np.concatenate([v[:6 * sc.C].reshape(sc.C, 6), v[6 * sc.C:8 * sc.C].reshape(sc.C, 2)], 1)
+    vpo = v[8 * sc.C:].reshape(sc.P, 3)
+    assert iters < 2000
+    assert np.linalg.norm(vc.cpu().numpy() - vco) <= 1e-5 * np.linalg.norm(vco)
+    assert np.linalg.norm(vp.cpu().numpy() - vpo) <= 1e-5 * np.linalg.norm(vpo)
+
+
+@pytest.mark.parametrize("shape", ["small", "ladybug49"])
+def test_lm_trajectory_vs_exact_oracle(shape):
+    sc, ba, x0, k3 = _setup(shape)
+    params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+    ref = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    assert list(st.accepted.astype(bool)) == ref.trace.accepted
+    rms = bo.rms_reprojection_px(params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    rms_ref = bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    assert rms == pytest.approx(rms_ref, rel=1e-4)
+    assert not np.isnan(params).any()
+
+
+def test_dense_padded_contract_equals_sparse():
+    sc, ba, x0, k3 = _setup("small")
+    p2d, idx, mask = sc.to_dense_padded()
+    pa, sa = ba.optimize(x0, p2d, idx, k3, mask)
+    pb, sb = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+    assert sa.iter_num == sb.iter_num
+    np.testing.assert_array_equal(pa, pb)  # row order must not matter: bit-identical
+    np.testing.assert_array_equal(sa.loss_trajectory, sb.loss_trajectory)
