@@ -110,6 +110,13 @@ int b200ba_pose_lm_batched(int B, int Npts, double* params8_inout, const double*
                            double* loss_out /*B*/, double* grad_l2 /*B*/,
                            double* damping_out /*B or NULL*/, int32_t* status /*B*/, void* stream);
 
+/* ---- measurement: per-kernel-class CUDA-event timing on the launching stream.  Classes:
+ * 0 residual+Jacobian (K1), 1 point blocks, 2 camera blocks, 3 point inverses, 4 Schur camera
+ * corrections, 5 block-Jacobi inverses, 6 matvec point pass, 7 matvec camera pass, 8 PCG vector
+ * kernels, 9 back-substitution, 10 trial cost, 11 other. */
+int b200ba_profile_enable(b200ba_plan* plan, int on);
+int b200ba_profile_get(b200ba_plan* plan, double* ms_out /*[16]*/, int64_t* count_out /*[16]*/);
+
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 int64_t b200ba_launch_count(void);
 

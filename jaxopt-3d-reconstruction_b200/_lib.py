@@ -15,7 +15,7 @@ SYMBOLS = [
     "b200ba_plan_set_observations", "b200ba_nccl_unique_id", "b200ba_plan_set_comm",
     "b200ba_residual_jacobian", "b200ba_lm_default_opts", "b200ba_lm_solve", "b200ba_linearize",
     "b200ba_schur_prepare", "b200ba_schur_matvec", "b200ba_schur_solve", "b200ba_cost",
-    "b200ba_pose_lm_batched", "b200ba_launch_count",
+    "b200ba_pose_lm_batched", "b200ba_launch_count", "b200ba_profile_enable", "b200ba_profile_get",
 ]
 
 
@@ -76,6 +76,8 @@ def load():
     lib.b200ba_cost.argtypes = [vp, vp, vp, vp, dbl, C.POINTER(dbl), vp]
     lib.b200ba_pose_lm_batched.argtypes = [i32, i32, vp, vp, vp, vp, vp, dbl, i32, i32, dbl, dbl,
                                            vp, vp, vp, vp, vp, vp]
+    lib.b200ba_profile_enable.argtypes = [vp, i32]
+    lib.b200ba_profile_get.argtypes = [vp, C.POINTER(dbl), C.POINTER(i64)]
     for name in SYMBOLS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int and name not in ("b200ba_version",):

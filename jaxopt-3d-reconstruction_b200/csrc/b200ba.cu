@@ -75,7 +75,31 @@ struct b200ba_plan {
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
   std::vector<void*> allocs;
+  // optional per-kernel-class CUDA-event timing (b200ba_profile_*)
+  bool prof = false;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
+  struct Rec { int cls; size_t e0, e1; };
+  std::vector<Rec> recs;
+  cudaEvent_t get_event() {
+    if (ev_used == ev_pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ev_pool.push_back(e);
+    }
+    return ev_pool[ev_used++];
+  }
 };
+enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, PC_CAM_FINISH, PC_MV_PT, PC_MV_CAM,
+       PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_COUNT };
+#define PLAUNCH(p, cls, kern, grid, block, smem, st, ...)                                \
+  do {                                                                                   \
+    size_t i0_ = 0, i1_ = 0;                                                             \
+    if ((p)->prof) { i0_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); }      \
+    kern<<<(grid), (block), (smem), (st)>>>(__VA_ARGS__);                                \
+    ++g_launches;                                                                        \
+    if ((p)->prof) { i1_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); (p)->recs.push_back({(cls), i0_, i1_}); } \
+  } while (0)
 
 template <typename T>
 static int dalloc(b200ba_plan* p, T** ptr, size_t n) {
@@ -232,6 +256,7 @@ extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
   if (p->st_host) cudaFreeHost(p->st_host);
   if (p->scal_host) cudaFreeHost(p->scal_host);
   if (p->comm) ncclCommDestroy(p->comm);
+  for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
   delete p;
   return B200BA_OK;
 }
@@ -292,22 +317,22 @@ struct Ops {
                        cudaStream_t s) {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
-    LAUNCH(k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
+    PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
     if (N) {
-      LAUNCH((k_resjac<JT, true>), p->nblkN, 256, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
+      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), p->nblkN, 256, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
              p->inv_cs, p->r_ps, (JT*)p->Jc_ps, (JT*)p->Jp_ps, (JT*)p->Jc_cs, p->r_cs, p->partN);
     }
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
-    if (P) LAUNCH((k_point_blocks<JT>), p->nblkP, 256, 0, s, P, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
-    LAUNCH((k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, p->r_cs, nullptr, nullptr, nullptr,
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
+    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
+    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, p->r_cs, nullptr, nullptr, nullptr,
            p->U, p->gc);
     int rc;
     if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
     if ((rc = allreduce(p, p->scal + 2, 1, ncclMax, s))) return rc;
-    LAUNCH(k_cam_scalars, cdiv(C, 128), 128, 0, s, C, p->U, p->gc, p->part);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 3, 2);
+    PLAUNCH(p, PC_OTHER, k_cam_scalars, cdiv(C, 128), 128, 0, s, C, p->U, p->gc, p->part);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 3, 2);
     CK(cudaGetLastError());
     return 0;
   }
@@ -315,15 +340,15 @@ struct Ops {
   // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start
   static int prepare(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, P = p->P;
-    if (P) LAUNCH((k_point_prepare<JT>), p->nblkP, 256, 0, s, P, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
+    if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
                   p->gp, p->Vinv, p->w_ps, p->beta_ps);
-    LAUNCH((k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, nullptr, p->perm_cs, p->w_ps,
+    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, nullptr, p->perm_cs, p->w_ps,
            p->beta_ps, p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
-    LAUNCH(k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part, p->Minv,
+    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part, p->Minv,
            p->rhs, p->x, p->r, p->z, p->pv, p->part2);
-    LAUNCH((k_pcg_dir<true>), 1, 256, 0, s, C, p->st, p->part2, p->z, p->pv, 0.0, 0);
+    PLAUNCH(p, PC_PCG_VEC, (k_pcg_dir<true>), 1, 256, 0, s, C, p->st, p->part2, p->z, p->pv, 0.0, 0);
     CK(cudaGetLastError());
     return 0;
   }
@@ -331,17 +356,17 @@ struct Ops {
   // y = S x for the current pv (x_in copied to pv by caller) — one PCG matvec
   static int matvec(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, P = p->P;
-    if (P) LAUNCH((k_mv_pt<JT, false>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
+    if (P) PLAUNCH(p, PC_MV_PT, (k_mv_pt<JT, false>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
                   (const JT*)p->Jp_ps, p->Vinv, p->pv, p->w_ps, nullptr, nullptr, nullptr);
     if (p->nranks == 1) {
-      LAUNCH((k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
+      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
              p->pv, p->y, p->part);
     } else {
-      LAUNCH((k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
+      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
              p->pv, p->y, p->part);
       int rc;
       if ((rc = allreduce(p, p->y, (size_t)C * 8, ncclSum, s))) return rc;
-      LAUNCH(k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, p->pv, p->y, p->part);
+      PLAUNCH(p, PC_PCG_VEC, k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, p->pv, p->y, p->part);
     }
     return 0;
   }
@@ -350,9 +375,9 @@ struct Ops {
     const int C = p->C;
     int rc;
     if ((rc = matvec(p, s))) return rc;
-    LAUNCH(k_pcg_update, cdiv(C, 256), 256, 0, s, C, p->st, p->part, p->Minv, p->pv, p->y, p->x, p->r, p->z, p->part2);
-    LAUNCH((k_pcg_dir<false>), cdiv(C, 256), 256, 0, s, C, p->st, p->part2, p->z, p->pv, rtol, maxiter);
-    LAUNCH(k_pcg_commit, 1, 256, 0, s, C, p->st, p->part2, rtol, maxiter);
+    PLAUNCH(p, PC_PCG_VEC, k_pcg_update, cdiv(C, 256), 256, 0, s, C, p->st, p->part, p->Minv, p->pv, p->y, p->x, p->r, p->z, p->part2);
+    PLAUNCH(p, PC_PCG_VEC, (k_pcg_dir<false>), cdiv(C, 256), 256, 0, s, C, p->st, p->part2, p->z, p->pv, rtol, maxiter);
+    PLAUNCH(p, PC_PCG_VEC, k_pcg_commit, 1, 256, 0, s, C, p->st, p->part2, rtol, maxiter);
     return 0;
   }
 
@@ -379,19 +404,19 @@ struct Ops {
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
     const int P = p->P;
-    if (P) LAUNCH((k_mv_pt<JT, true>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
+    if (P) PLAUNCH(p, PC_BACKSUB, (k_mv_pt<JT, true>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
                   (const JT*)p->Jp_ps, p->Vinv, p->x, nullptr, p->gp, p->vp, p->partN);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;
   }
 
   static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
                   double* out_dev, cudaStream_t s) {
-    LAUNCH(k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
+    PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
     if (p->N)
-      LAUNCH((k_resjac<JT, false>), p->nblkN, 256, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
+      PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->nblkN, 256, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
              inv_w2, p->inv_cs, nullptr, nullptr, nullptr, nullptr, nullptr, p->partN);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
     return 0;
   }
 };
@@ -421,7 +446,7 @@ extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double
   cudaStream_t s = (cudaStream_t)stream_;
   int rc;
   if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
-  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, 1e-6);
+  PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, 1e-6);
   if (U) CK(cudaMemcpyAsync(U, p->U, (size_t)p->C * 64 * 8, cudaMemcpyDeviceToDevice, s));
   if (gc) CK(cudaMemcpyAsync(gc, p->gc, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   if (V) CK(cudaMemcpyAsync(V, p->V, (size_t)p->P * 6 * 8, cudaMemcpyDeviceToDevice, s));
@@ -538,7 +563,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   res->n_jac_evals = res->n_res_evals = res->n_pcg_iters_total = 0;
   // init_state
   if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
-  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, opts->damping_parameter);
+  PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, opts->damping_parameter);
   if ((rc = read_state(p, s))) return rc;
   res->n_jac_evals++;
   double err = sqrt(p->st_host->grad2);
@@ -554,21 +579,21 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
     res->n_pcg_iters_total += pcg_iters;
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-    LAUNCH(k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->x, p->gc, p->cam_trial, p->part);
-    LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
-    if (P) LAUNCH(k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
+    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->x, p->gc, p->cam_trial, p->part);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
+    if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
     if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts_trial, inv_w2, p->scal + 8, s))) return rc;
     res->n_res_evals++;
     if ((rc = allreduce(p, p->scal + 8, 3, ncclSum, s))) return rc;
-    LAUNCH(k_pack_decide, 1, 1, 0, s, p->scal);
-    LAUNCH(k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
-    LAUNCH(k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
-    if (P) LAUNCH(k_accept_copy, cdiv(3 * (int64_t)P, 256), 256, 0, s, p->st, 3 * (int64_t)P, p->pts_trial, pts);
+    PLAUNCH(p, PC_OTHER, k_pack_decide, 1, 1, 0, s, p->scal);
+    PLAUNCH(p, PC_OTHER, k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
+    PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
+    if (P) PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(3 * (int64_t)P, 256), 256, 0, s, p->st, 3 * (int64_t)P, p->pts_trial, pts);
     if ((rc = read_state(p, s))) return rc;
     const int accepted = p->st_host->accepted;
     if (accepted) {
       if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
-      LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
+      PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
       if ((rc = read_state(p, s))) return rc;
       res->n_jac_evals++;
       err = sqrt(p->st_host->grad2);
@@ -624,5 +649,29 @@ extern "C" int b200ba_pose_lm_batched(int B, int Npts, double* params8, const do
            maxiter, tol, damping, iter_num, loss_out, grad_l2, damping_out, status);
   }
   CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_profile_enable(b200ba_plan* p, int on) {
+  if (!p) FAIL(B200BA_EINVAL, "null plan");
+  p->prof = on != 0;
+  p->ev_used = 0;
+  p->recs.clear();
+  return B200BA_OK;
+}
+
+// Sum CUDA-event durations per kernel class since the last enable/get; resets the log.
+extern "C" int b200ba_profile_get(b200ba_plan* p, double* ms_out /*[16]*/, int64_t* count_out /*[16]*/) {
+  if (!p || !ms_out || !count_out) FAIL(B200BA_EINVAL, "null");
+  CK(cudaDeviceSynchronize());
+  for (int k = 0; k < 16; ++k) { ms_out[k] = 0.0; count_out[k] = 0; }
+  for (const auto& r : p->recs) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, p->ev_pool[r.e0], p->ev_pool[r.e1]));
+    ms_out[r.cls] += ms;
+    count_out[r.cls] += 1;
+  }
+  p->ev_used = 0;
+  p->recs.clear();
   return B200BA_OK;
 }
