@@ -233,21 +233,18 @@ class B200BundleAdjustment:
             check(prob.lib.b200ba_plan_set_comm(prob.plan, self.rank, self.world, raw), "set_comm")
 
     # ------------------------------------------------------------------ solve
-    def _solve(self, opt_params, cx_cy_skew, prob: BAProblem):
+    def solve_device(self, prob: BAProblem, cam8, k3, pts, maxiter=None, tol=None):
+        """LM solve on device-resident tensors: cam8 (C,8) and pts (P_local,3) are updated IN PLACE.
+        No host<->device copies of problem data. Returns (LMResult struct, trajectory buffers)."""
         lib = prob.lib
-        Cn, dev = self.cam_num, self.device
-        x = np.asarray(opt_params, dtype=np.float64) if not isinstance(opt_params, torch.Tensor) else opt_params
-        xd = _dev(x, torch.float64, dev)
-        cam8 = torch.cat([xd[:6 * Cn].view(Cn, 6), xd[6 * Cn:8 * Cn].view(Cn, 2)], dim=1).contiguous()
-        pts_all = xd[8 * Cn:].view(-1, 3)
-        pts = pts_all[prob.pt_lo:prob.pt_hi].contiguous().clone()
-        k3 = _dev(cx_cy_skew, torch.float64, dev)
         opts = LMOpts()
         lib.b200ba_lm_default_opts(C.byref(opts))
-        opts.maxiter, opts.tol, opts.damping_parameter = int(self.maxiter), float(self.tol), float(self.damping_parameter)
+        opts.maxiter = int(self.maxiter if maxiter is None else maxiter)
+        opts.tol = float(self.tol if tol is None else tol)
+        opts.damping_parameter = float(self.damping_parameter)
         opts.pcg_rtol, opts.pcg_maxiter = float(self.pcg_rtol), int(self.pcg_maxiter)
         opts.fixed_pcg_iters, opts.verbose = int(self.fixed_pcg_iters), int(bool(self.verbose))
-        m = max(int(self.maxiter), 1)
+        m = max(opts.maxiter, 1)
         loss_t = (C.c_double * (m + 1))()
         grad_t = (C.c_double * (m + 1))()
         mu_t = (C.c_double * (m + 1))()
@@ -259,9 +256,22 @@ class B200BundleAdjustment:
         res.mu_trajectory_host = C.cast(mu_t, C.POINTER(C.c_double))
         res.pcg_iters_host = C.cast(pcg_t, C.POINTER(C.c_int))
         res.accepted_host = C.cast(acc_t, C.POINTER(C.c_int))
-        with torch.cuda.device(dev):
+        with torch.cuda.device(self.device):
             check(lib.b200ba_lm_solve(prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts),
                                       1.0 / self.avg_cam_width_sqr, C.byref(opts), C.byref(res), _stream()), "lm_solve")
+        return res, (loss_t, grad_t, mu_t, pcg_t, acc_t)
+
+    def _solve(self, opt_params, cx_cy_skew, prob: BAProblem):
+        lib = prob.lib
+        Cn, dev = self.cam_num, self.device
+        x = np.asarray(opt_params, dtype=np.float64) if not isinstance(opt_params, torch.Tensor) else opt_params
+        xd = _dev(x, torch.float64, dev)
+        cam8 = torch.cat([xd[:6 * Cn].view(Cn, 6), xd[6 * Cn:8 * Cn].view(Cn, 2)], dim=1).contiguous()
+        pts_all = xd[8 * Cn:].view(-1, 3)
+        pts = pts_all[prob.pt_lo:prob.pt_hi].contiguous().clone()
+        k3 = _dev(cx_cy_skew, torch.float64, dev)
+        res, traj = self.solve_device(prob, cam8, k3, pts)
+        loss_t, grad_t, mu_t, pcg_t, acc_t = traj
         if self.world > 1:
             import torch.distributed as dist
             sizes = [None] * self.world
