@@ -1,0 +1,136 @@
+"""CPU tests: pin the oracle against every golden vector the reference holds for the path
+(COLMAP's projection KATs, the pose fixture), against autodiff of the literal restatement of the
+reference's residual functions, and check the LM state machine's internal consistency."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200ba
+from oracle import ba_oracle as bo
+from oracle import pose_oracle as po
+from oracle import ref_literal as rl
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _project_identity(f, X):
+    """pinhole projection through the oracle with identity-like pose (tiny rotation: the
+    reference's Rodrigues has no guard at w=0, utils.py:23-24)."""
+    w = np.array([1e-12, 0, 0])
+    x = np.concatenate([w, [0, 0, 0], [f, f], X])
+    r, dxdy, _, _ = bo.ba_eval(x, 1, np.array([0]), np.array([0]), np.zeros((1, 2)), np.zeros((1, 3)), 1.0,
+                               want_jac=False)
+    return dxdy[0]
+
+
+@pytest.mark.parametrize("f,X,uv", [
+    (1.0, (0, 0, 1), (0, 0)), (1.0, (0, 1, 1), (0, 1)), (2.0, (0, 1, 1), (0, 2)), (2.0, (-1, 1, 1), (-2, 2))])
+def test_colmap_projection_known_answers(f, X, uv):
+    """colmap/src/base/cost_functions_test.cc:41-69 (BundleAdjustmentCostFunction KATs)."""
+    np.testing.assert_allclose(_project_identity(f, np.array(X, float)), uv, atol=1e-10)
+
+
+def test_pose_fixture_roundtrip():
+    """src/dataset/camera_pose/tests/test_pose.txt (3x4 [R|t]): log then exp reproduces R."""
+    P = np.loadtxt(os.path.join(GOLD, "test_pose.txt")).reshape(3, 4)
+    v = bo.pose_mat_to_vec(P)
+    R = bo.rot_mat_from_vec(v[:3])
+    np.testing.assert_allclose(R, P[:, :3], atol=1e-6)
+    np.testing.assert_allclose(v[3:], P[:, 3])
+    np.testing.assert_allclose(b200ba.pose_mat_to_vec(P), v)
+
+
+def test_rodrigues_vs_scipy():
+    from scipy.spatial.transform import Rotation
+    rng = np.random.default_rng(0)
+    w = rng.standard_normal((50, 3))
+    np.testing.assert_allclose(bo.rot_mat_from_vec(w), Rotation.from_rotvec(w).as_matrix(), atol=1e-13)
+    w2 = bo.pose_mat_to_vec(np.concatenate([bo.rot_mat_from_vec(w), np.zeros((50, 3, 1))], axis=2))[:, :3]
+    np.testing.assert_allclose(bo.rot_mat_from_vec(w2), bo.rot_mat_from_vec(w), atol=1e-12)
+
+
+def _dense_slots(sc):
+    order = np.argsort(sc.cam_idx, kind="stable")
+    cam_s = sc.cam_idx[order]
+    counts = np.bincount(cam_s, minlength=sc.C)
+    start = np.concatenate([[0], np.cumsum(counts)[:-1]])
+    slot = np.arange(sc.N) - start[cam_s]
+    return order, cam_s * counts.max() + slot
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_ba_residual_and_jacobian_vs_literal_autodiff(seed):
+    sc = b200ba.synth.make_ba_scene("tiny", seed=seed)
+    x0, ccs = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    w2 = sc.avg_cam_width ** 2
+    r, _, a, b = bo.ba_eval(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, ccs, w2)
+    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)).toarray()
+    p2d, idx, mask = sc.to_dense_padded()
+    f = lambda p: rl.ba_get_residuals(p, torch.tensor(p2d), torch.tensor(idx), torch.tensor(ccs),
+                                      torch.tensor(mask), sc.C, w2)
+    rd = f(torch.tensor(x0)).numpy()
+    Jd = torch.autograd.functional.jacobian(f, torch.tensor(x0)).numpy()
+    order, flat = _dense_slots(sc)
+    np.testing.assert_allclose(rd[flat], r[order], rtol=1e-12, atol=1e-20)
+    np.testing.assert_allclose(Jd[flat], J[order], rtol=1e-9, atol=1e-12 * np.abs(J).max())
+    pad = np.setdiff1d(np.arange(rd.size), flat)
+    assert np.all(rd[pad] == 0) and np.all(Jd[pad] == 0)  # masked slots are exact zero rows
+
+
+@pytest.mark.parametrize("loss", [po.L2, po.CAUCHY])
+def test_pose_residual_and_jacobian_vs_literal_autodiff(loss):
+    pb = b200ba.synth.make_pose_batch(B=3, npts=16, seed=4, ragged=True)
+    x0 = np.concatenate([bo.pose_mat_to_vec(pb.poses0), pb.intrinsics0[:, :2]], axis=1)
+    k3 = pb.intrinsics0[:, 2:]
+    w2 = pb.avg_cam_width ** 2
+    r, J = po.pose_eval(x0, pb.points, pb.obs, k3, pb.mask, w2, loss)
+    fn = rl.cauchy_loss if loss == po.CAUCHY else rl.l2_loss
+    for i in range(3):
+        f = lambda p: rl.pose_get_residuals(p, torch.tensor(pb.points[i]), torch.tensor(pb.obs[i]),
+                                            torch.tensor(k3[i]), torch.tensor(pb.mask[i]), w2, fn)
+        np.testing.assert_allclose(f(torch.tensor(x0[i])).numpy(), r[i], rtol=1e-12, atol=1e-20)
+        Jd = torch.autograd.functional.jacobian(f, torch.tensor(x0[i])).numpy()
+        np.testing.assert_allclose(Jd, J[i], rtol=1e-9, atol=1e-12 * np.abs(J[i]).max())
+
+
+def test_lm_exact_step_solves_normal_equations():
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, ccs = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    ci, pi = sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)
+    r, _, a, b = bo.ba_eval(x0, sc.C, ci, pi, sc.obs, ccs, sc.avg_cam_width ** 2)
+    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, ci, pi)
+    g = J.T @ r
+    mu = 1e-6 * float(np.asarray(J.multiply(J).sum(axis=0)).max())
+    v = bo._solve_schur_exact(a, b, g, mu, sc.C, sc.P, ci, pi)
+    res = J.T @ (J @ v) + mu * v - g
+    assert np.linalg.norm(res) <= 1e-10 * np.linalg.norm(g)
+
+
+def test_lm_trajectory_golden_and_modes():
+    """Frozen trajectory (tests/golden/ba_small_seed0.npz, made by tests/golden/make_golden.py) and
+    the documented gap between the reference's loose CG and the exact inner solve."""
+    gold = np.load(os.path.join(GOLD, "ba_small_seed0.npz"))
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, ccs = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    np.testing.assert_array_equal(x0, gold["x0"])
+    ex = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, ccs, sc.avg_cam_width)
+    assert ex.iter_num == int(gold["iter_num"])
+    np.testing.assert_allclose(ex.trace.loss, gold["loss"], rtol=1e-7)
+    assert all(ex.trace.accepted)
+    assert ex.grad_l2 <= 1e-6
+    cg = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, ccs, sc.avg_cam_width, solver="jaxopt_cg")
+    dev = np.abs(np.array(cg.trace.loss[:4]) - np.array(ex.trace.loss[:4])) / np.array(ex.trace.loss[:4])
+    assert dev.max() < 0.2          # same basin
+    assert max(cg.trace.inner_iters) > 50  # the reference's inner solve is hundreds of CG iterations
+
+
+def test_pose_oracle_golden():
+    gold = np.load(os.path.join(GOLD, "pose_b16_seed3.npz"))
+    pb = b200ba.synth.make_pose_batch(B=16, npts=512, seed=3, rot_noise=5e-3, pos_noise=5e-3)
+    x0 = np.concatenate([bo.pose_mat_to_vec(pb.poses0), pb.intrinsics0[:, :2]], axis=1)
+    res = po.pose_lm_batched(x0, pb.points, pb.obs, pb.intrinsics0[:, 2:], pb.mask, pb.avg_cam_width)
+    np.testing.assert_array_equal(res.iter_num, gold["iter_num"])
+    np.testing.assert_allclose(res.loss, gold["loss"], rtol=1e-7)
+    np.testing.assert_allclose(res.params, gold["params"], rtol=1e-7, atol=1e-10)
