@@ -57,6 +57,8 @@ struct b200ba_plan {
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // ps rows
   int32_t *perm_cs = nullptr, *inv_cs = nullptr;                     // cs<->ps
   int32_t *pt_ptr = nullptr, *cam_ptr = nullptr;
+  int32_t *chunk_row = nullptr, *chunk_pt = nullptr;  // matvec pass-1 chunks of whole points
+  int nchunks = 0;
   double2* obs_ps = nullptr;
   // linearisation
   void *Jc_ps = nullptr, *Jp_ps = nullptr, *Jc_cs = nullptr;
@@ -64,7 +66,7 @@ struct b200ba_plan {
   double *tab = nullptr, *tab_trial = nullptr;
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
-  double *x = nullptr, *r = nullptr, *z = nullptr, *pv = nullptr, *y = nullptr, *vp = nullptr;
+  double *x = nullptr, *r = nullptr, *z = nullptr, *pv = nullptr, *sv = nullptr, *y = nullptr, *vp = nullptr;
   double *cam_trial = nullptr, *pts_trial = nullptr;
   double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
   SolverState* st = nullptr;
@@ -177,14 +179,14 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
-  A(x, (size_t)C * 8) A(r, (size_t)C * 8) A(z, (size_t)C * 8) A(pv, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
+  A(x, (size_t)C * 8) A(r, (size_t)C * 8) A(z, (size_t)C * 8) A(pv, (size_t)C * 8) A(sv, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
   A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts_trial, (size_t)P * 3)
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
   p->lin_scal = p->gc + (size_t)C * 8;
   p->nblkN = (int)cdiv(N, 256); p->nblkP = (int)cdiv(P, 256);
   A(part, 2 * (size_t)C + 16) A(part2, 2 * (size_t)C + 16)
-  A(partN, 2 * (size_t)(p->nblkN > p->nblkP ? p->nblkN : p->nblkP) + 16) A(scal, 32) A(st, 1)
+  A(scal, 32) A(st, 1)
 #undef A
   {
     void* q = nullptr;
@@ -192,7 +194,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     p->allocs.push_back(q); p->Jc_ps = q;
     if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_cs"); }
     p->allocs.push_back(q); p->Jc_cs = q;
-    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 4 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
+    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
     p->allocs.push_back(q); p->Jp_ps = q;
   }
   if (cudaMallocHost((void**)&p->st_host, sizeof(SolverState)) != cudaSuccess ||
@@ -201,6 +203,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     FAIL(B200BA_ECUDA, "cudaMallocHost failed");
   }
   cudaMemsetAsync(p->st, 0, sizeof(SolverState), s);
+  cudaMemsetAsync(p->vp, 0, (size_t)(P ? P : 1) * 3 * sizeof(double), s);
 
   if (N > 0) {
     // validate, then sort rows by (point, camera) and by (camera, point) with CUB radix sort
@@ -245,6 +248,38 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaMemsetAsync(p->pt_ptr, 0, (P + 1) * sizeof(int32_t), s);
     cudaMemsetAsync(p->cam_ptr, 0, (C + 1) * sizeof(int32_t), s);
     cudaStreamSynchronize(s);
+  }
+  {
+    // greedy chunks of whole points with <= MV_CH rows (a point with more rows is its own chunk)
+    std::vector<int32_t> hptr((size_t)P + 1), crow, cpt;
+    if (cudaMemcpy(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, "plan_create: pt_ptr readback");
+    }
+    crow.push_back(0);
+    cpt.push_back(0);
+    int cur = 0;
+    for (int q = 0; q < P; ++q) {
+      const int d = hptr[q + 1] - hptr[q];
+      if ((cur > 0 && cur + d > MV_CH) || q - cpt.back() >= MV_CH) {
+        crow.push_back(hptr[q]);
+        cpt.push_back(q);
+        cur = 0;
+      }
+      cur += d;
+    }
+    crow.push_back((int32_t)N);
+    cpt.push_back(P);
+    p->nchunks = (int)crow.size() - 1;
+    size_t mx = (size_t)p->nblkN;
+    if ((size_t)p->nblkP > mx) mx = p->nblkP;
+    if ((size_t)p->nchunks > mx) mx = p->nchunks;
+    if (dalloc(p, &p->chunk_row, crow.size()) || dalloc(p, &p->chunk_pt, cpt.size()) || dalloc(p, &p->partN, 2 * mx + 16)) {
+      b200ba_plan_destroy(p);
+      return B200BA_ECUDA;
+    }
+    cudaMemcpy(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    cudaMemcpy(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
   }
   *out = p;
   return B200BA_OK;
@@ -323,7 +358,7 @@ struct Ops {
              p->inv_cs, p->r_ps, (JT*)p->Jc_ps, (JT*)p->Jp_ps, (JT*)p->Jc_cs, p->r_cs, p->partN);
     }
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
-    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
+    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
     PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, p->r_cs, nullptr, nullptr, nullptr,
@@ -340,45 +375,44 @@ struct Ops {
   // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start
   static int prepare(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, P = p->P;
-    if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
+    if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
                   p->gp, p->Vinv, p->w_ps, p->beta_ps);
     PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, nullptr, p->perm_cs, p->w_ps,
            p->beta_ps, p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
-    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part, p->Minv,
-           p->rhs, p->x, p->r, p->z, p->pv, p->part2);
-    PLAUNCH(p, PC_PCG_VEC, (k_pcg_dir<true>), 1, 256, 0, s, C, p->st, p->part2, p->z, p->pv, 0.0, 0);
+    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
+            p->Minv, p->rhs, p->x, p->r, p->z, p->pv, p->sv, p->part2);
+    PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
     CK(cudaGetLastError());
-    return 0;
+    return matvec(p, p->z, s);  // w = S u, delta partials
   }
 
-  // y = S x for the current pv (x_in copied to pv by caller) — one PCG matvec
-  static int matvec(b200ba_plan* p, cudaStream_t s) {
-    const int C = p->C, P = p->P;
-    if (P) PLAUNCH(p, PC_MV_PT, (k_mv_pt<JT, false>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
-                  (const JT*)p->Jp_ps, p->Vinv, p->pv, p->w_ps, nullptr, nullptr, nullptr);
+  // y = S xin (xin: C x 8 device vector); part[c] = xin_c . y_c
+  static int matvec(b200ba_plan* p, const double* xin, cudaStream_t s) {
+    const int C = p->C;
+    if (p->N) PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false>), p->nchunks, MV_CH, 0, s, (size_t)p->N, p->st, p->chunk_row,
+                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps, p->Vinv, xin,
+                      p->w_ps, nullptr, nullptr, nullptr);
     if (p->nranks == 1) {
-      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
-             p->pv, p->y, p->part);
+      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs,
+              p->w_ps, p->U, xin, p->y, p->part);
     } else {
-      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_ps, p->U,
-             p->pv, p->y, p->part);
+      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs,
+              p->w_ps, p->U, xin, p->y, p->part);
       int rc;
       if ((rc = allreduce(p, p->y, (size_t)C * 8, ncclSum, s))) return rc;
-      PLAUNCH(p, PC_PCG_VEC, k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, p->pv, p->y, p->part);
+      PLAUNCH(p, PC_PCG_VEC, k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, xin, p->y, p->part);
     }
     return 0;
   }
 
-  static int pcg_iteration(b200ba_plan* p, double rtol, int maxiter, cudaStream_t s) {
+  // one Chronopoulos-Gear PCG iteration: vector kernel (alpha/beta, x/r/u/p/s update) + matvec of u
+  static int pcg_iteration(b200ba_plan* p, int it, double rtol, int maxiter, cudaStream_t s) {
     const int C = p->C;
-    int rc;
-    if ((rc = matvec(p, s))) return rc;
-    PLAUNCH(p, PC_PCG_VEC, k_pcg_update, cdiv(C, 256), 256, 0, s, C, p->st, p->part, p->Minv, p->pv, p->y, p->x, p->r, p->z, p->part2);
-    PLAUNCH(p, PC_PCG_VEC, (k_pcg_dir<false>), cdiv(C, 256), 256, 0, s, C, p->st, p->part2, p->z, p->pv, rtol, maxiter);
-    PLAUNCH(p, PC_PCG_VEC, k_pcg_commit, 1, 256, 0, s, C, p->st, p->part2, rtol, maxiter);
-    return 0;
+    PLAUNCH(p, PC_PCG_VEC, k_pcg_vec, cdiv(8 * (int64_t)C, 256), 256, 0, s, C, it, p->st, p->part2, p->part, p->Minv, p->y,
+            p->x, p->r, p->z, p->pv, p->sv, p->part2, rtol, maxiter);
+    return matvec(p, p->z, s);
   }
 
   // run PCG to convergence; device-side flag, host polls every `chunk` iterations
@@ -388,10 +422,10 @@ struct Ops {
     const int limit = fixed_iters > 0 ? fixed_iters : maxiter;
     const double rt = fixed_iters > 0 ? 0.0 : rtol;
     int chunk = fixed_iters > 0 ? fixed_iters : 16;
-    while (!done && launched < limit) {
-      const int n = (limit - launched) < chunk ? (limit - launched) : chunk;
+    while (!done && launched <= limit) {
+      const int n = (limit + 1 - launched) < chunk ? (limit + 1 - launched) : chunk;
       for (int k = 0; k < n; ++k)
-        if ((rc = pcg_iteration(p, rt, limit, s))) return rc;
+        if ((rc = pcg_iteration(p, launched + k, rt, limit, s))) return rc;
       launched += n;
       CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
       CK(cudaStreamSynchronize(s));
@@ -404,9 +438,11 @@ struct Ops {
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
     const int P = p->P;
-    if (P) PLAUNCH(p, PC_BACKSUB, (k_mv_pt<JT, true>), p->nblkP, 256, 0, s, P, p->st, p->pt_ptr, p->cam_ps, (const JT*)p->Jc_ps,
-                  (const JT*)p->Jp_ps, p->Vinv, p->x, nullptr, p->gp, p->vp, p->partN);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+    if (p->N) PLAUNCH(p, PC_BACKSUB, (k_mv_rows<JT, true>), p->nchunks, MV_CH, 0, s, (size_t)p->N, p->st, p->chunk_row,
+                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps, p->Vinv, p->x,
+                      nullptr, p->gp, p->vp, p->partN);
+    (void)P;
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;
   }
 
@@ -469,13 +505,13 @@ extern "C" int b200ba_residual_jacobian(b200ba_plan* p, const double* cam8, cons
   cudaStream_t s = (cudaStream_t)stream_;
   const int64_t N = p->N;
   if (N) {
-    if (r) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->r_ps, 1, 1, r);
+    if (r) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->r_ps, (size_t)0, 1, r);
     if (p->jac_f32) {
-      if (Jc) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jc_ps, 8, 8, Jc);
-      if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, 4, 3, Jp);
+      if (Jc) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jc_ps, (size_t)N, 8, Jc);
+      if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, (size_t)N, 3, Jp);
     } else {
-      if (Jc) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jc_ps, 8, 8, Jc);
-      if (Jp) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jp_ps, 4, 3, Jp);
+      if (Jc) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jc_ps, (size_t)N, 8, Jc);
+      if (Jp) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jp_ps, (size_t)N, 3, Jp);
     }
   }
   if (cost_host) {
@@ -508,10 +544,10 @@ extern "C" int b200ba_schur_matvec(b200ba_plan* p, const double* x, double* y, v
   if (!p || !x || !y) FAIL(B200BA_EINVAL, "null");
   cudaStream_t s = (cudaStream_t)stream_;
   // uses pv as the input vector; the PCG state is clobbered (call schur_prepare again before a solve)
-  CK(cudaMemcpyAsync(p->pv, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  CK(cudaMemcpyAsync(p->z, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   LAUNCH(k_clear_done, 1, 1, 0, s, p->st);
   int rc;
-  if ((rc = DISPATCH(p, matvec, p, s))) return rc;
+  if ((rc = DISPATCH(p, matvec, p, p->z, s))) return rc;
   CK(cudaMemcpyAsync(y, p->y, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return B200BA_OK;

@@ -33,30 +33,15 @@ __device__ __forceinline__ void store8<float>(float* __restrict__ p, const doubl
   q[0] = make_float4((float)a[0], (float)a[1], (float)a[2], (float)a[3]);
   q[1] = make_float4((float)a[4], (float)a[5], (float)a[6], (float)a[7]);
 }
-// point part: 4 JT per row (b0,b1,b2,pad) so a row is one aligned vector load
+// ps-order rows are stored SoA: value k of row i lives at base[k * N + i], so a warp that maps
+// one lane to one row issues perfectly coalesced loads/stores (8 camera + 3 point arrays).
 template <typename JT>
-__device__ __forceinline__ void load3(const JT* __restrict__ p, double* b);
-template <>
-__device__ __forceinline__ void load3<double>(const double* __restrict__ p, double* b) {
-  const double2* q = reinterpret_cast<const double2*>(p);
-  double2 v0 = __ldg(q), v1 = __ldg(q + 1);
-  b[0] = v0.x; b[1] = v0.y; b[2] = v1.x;
-}
-template <>
-__device__ __forceinline__ void load3<float>(const float* __restrict__ p, double* b) {
-  float4 v = __ldg(reinterpret_cast<const float4*>(p));
-  b[0] = v.x; b[1] = v.y; b[2] = v.z;
+__device__ __forceinline__ double jget(const JT* __restrict__ base, size_t N, int k, size_t i) {
+  return (double)__ldg(base + (size_t)k * N + i);
 }
 template <typename JT>
-__device__ __forceinline__ void store3(JT* __restrict__ p, const double* b);
-template <>
-__device__ __forceinline__ void store3<double>(double* __restrict__ p, const double* b) {
-  double2* q = reinterpret_cast<double2*>(p);
-  q[0] = make_double2(b[0], b[1]); q[1] = make_double2(b[2], 0.0);
-}
-template <>
-__device__ __forceinline__ void store3<float>(float* __restrict__ p, const double* b) {
-  *reinterpret_cast<float4*>(p) = make_float4((float)b[0], (float)b[1], (float)b[2], 0.f);
+__device__ __forceinline__ void jput(JT* __restrict__ base, size_t N, int k, size_t i, double v) {
+  base[(size_t)k * N + i] = (JT)v;
 }
 
 // ---------------------------------------------------------------- K0: camera tables
@@ -94,8 +79,10 @@ k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restric
       double a[8], b[3];
       jac_row(T, pr, X, Y, Z, 2.0 * dx * inv_w2, 2.0 * dy * inv_w2, a, b);
       r_ps[i] = r;
-      store8<JT>(Jc_ps + 8 * i, a);
-      store3<JT>(Jp_ps + 4 * i, b);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) jput<JT>(Jc_ps, (size_t)N, k, (size_t)i, a[k]);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) jput<JT>(Jp_ps, (size_t)N, k, (size_t)i, b[k]);
       const int64_t j = __ldg(inv_cs + i);
       store8<JT>(Jc_cs + 8 * j, a);
       r_cs[j] = r;
@@ -112,7 +99,7 @@ k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restric
 // part[2*block+0] = sum |g_p|^2, part[2*block+1] = max diag V.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_point_blocks(int P, const int32_t* __restrict__ pt_ptr, const JT* __restrict__ Jp_ps,
+k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __restrict__ Jp_ps,
                const double* __restrict__ r_ps, double* __restrict__ V, double* __restrict__ gp,
                double* __restrict__ part) {
   __shared__ double sm[32];
@@ -124,7 +111,8 @@ k_point_blocks(int P, const int32_t* __restrict__ pt_ptr, const JT* __restrict__
     const int e = pt_ptr[p + 1];
     for (int i = pt_ptr[p]; i < e; ++i) {
       double b[3];
-      load3<JT>(Jp_ps + 4 * (size_t)i, b);
+      #pragma unroll
+      for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, (size_t)i);
       const double r = __ldg(r_ps + i);
       v[0] += b[0] * b[0]; v[1] += b[0] * b[1]; v[2] += b[0] * b[2];
       v[3] += b[1] * b[1]; v[4] += b[1] * b[2]; v[5] += b[2] * b[2];
@@ -229,7 +217,7 @@ __device__ __forceinline__ void inv3_sym(const double* v, double mu, double* o) 
 // Vinv_p = (V_p + mu I)^-1; per row w_i = b_i . (Vinv g_p) and beta_i = b_i^T Vinv b_i.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_point_prepare(int P, const double* __restrict__ mu_ptr, const int32_t* __restrict__ pt_ptr,
+k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_t* __restrict__ pt_ptr,
                 const JT* __restrict__ Jp_ps, const double* __restrict__ V,
                 const double* __restrict__ gp, double* __restrict__ Vinv, double* __restrict__ w_ps,
                 double* __restrict__ beta_ps) {
@@ -249,7 +237,8 @@ k_point_prepare(int P, const double* __restrict__ mu_ptr, const int32_t* __restr
   const int e = pt_ptr[p + 1];
   for (int i = pt_ptr[p]; i < e; ++i) {
     double b[3];
-    load3<JT>(Jp_ps + 4 * (size_t)i, b);
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, (size_t)i);
     w_ps[i] = b[0] * z0 + b[1] * z1 + b[2] * z2;
     const double t0 = vi[0] * b[0] + vi[1] * b[1] + vi[2] * b[2];
     const double t1 = vi[1] * b[0] + vi[3] * b[1] + vi[4] * b[2];
@@ -259,13 +248,13 @@ k_point_prepare(int P, const double* __restrict__ mu_ptr, const int32_t* __restr
 }
 
 // rhs = g_c + rhs_part; Minv_c = (U_c + mu I + Sd_part)^-1 (8x8, Cholesky, one thread per camera);
-// PCG start: x = 0, r = rhs, z = Minv r, p = z; part[2c] = r.z, part[2c+1] = r.r
+// PCG start: x = 0, r = rhs, u = Minv r, p = s = 0; part[2c] = r.u, part[2c+1] = r.r
 __global__ void __launch_bounds__(64)
 k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __restrict__ U,
                      const double* __restrict__ gc, const double* __restrict__ Sd_part,
                      const double* __restrict__ rhs_part, double* __restrict__ Minv,
                      double* __restrict__ rhs, double* __restrict__ x, double* __restrict__ r,
-                     double* __restrict__ z, double* __restrict__ pv, double* __restrict__ part) {
+                     double* __restrict__ z, double* __restrict__ pv, double* __restrict__ sv, double* __restrict__ part) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const double mu = *mu_ptr;
@@ -304,7 +293,7 @@ k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __r
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const size_t o = 8 * (size_t)c + k;
-    rhs[o] = rr[k]; x[o] = 0.0; r[o] = rr[k]; z[o] = zz[k]; pv[o] = zz[k];
+    rhs[o] = rr[k]; x[o] = 0.0; r[o] = rr[k]; z[o] = zz[k]; pv[o] = 0.0; sv[o] = 0.0;
   }
   part[2 * c] = rz;
   part[2 * c + 1] = r2;

@@ -5,71 +5,136 @@
 #include "ba_kernels.cuh"
 
 // ---------------------------------------------------------------- K3b pass 1 (point side)
-// t_p = sum_i b_i (a_i . x_c(i));  z_p = Vinv_p t_p;  w_i = b_i . z_p      (ps order)
-// BACKSUB: instead v_p = Vinv_p (g_p - t_p) -> vp; part[2*block] = v_p.g_p, [2*block+1] = |v_p|^2
+// Rows are processed in CHUNKS of whole points (<= MV_CH rows, built once per plan), one CTA per
+// chunk, one THREAD PER ROW: phase 1 s_i = a_i . x_c(i) with coalesced SoA loads, b_i s_i to shared
+// memory; phase 2 one thread per point sums its run in order, z_p = Vinv_p t_p; phase 3 every row
+// thread computes w_i = b_i . z_p and stores it coalesced.
+// BACKSUB: phase 2 instead does v_p = Vinv_p (g_p - t_p) -> vp; part[2*chunk] = v_p.g_p, [+1] = |v_p|^2
+#define MV_CH 256
 template <typename JT, bool BACKSUB>
-__global__ void __launch_bounds__(256)
-k_mv_pt(int P, const SolverState* __restrict__ st, const int32_t* __restrict__ pt_ptr,
-        const int32_t* __restrict__ cam_ps, const JT* __restrict__ Jc_ps, const JT* __restrict__ Jp_ps,
-        const double* __restrict__ Vinv, const double* __restrict__ x, double* __restrict__ w_ps,
-        const double* __restrict__ gp, double* __restrict__ vp, double* __restrict__ part) {
-  __shared__ double sm[64];
+__global__ void __launch_bounds__(MV_CH)
+k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restrict__ chunk_row,
+          const int32_t* __restrict__ chunk_pt, const int32_t* __restrict__ pt_ptr,
+          const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
+          const JT* __restrict__ Jc_ps, const JT* __restrict__ Jp_ps, const double* __restrict__ Vinv,
+          const double* __restrict__ x, double* __restrict__ w_ps, const double* __restrict__ gp,
+          double* __restrict__ vp, double* __restrict__ part) {
+  __shared__ double sb[3][MV_CH];
+  __shared__ double sz[3][MV_CH];
+  __shared__ double sred[3 * 32];
   if (!BACKSUB && st->pcg_done) return;
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int ch = blockIdx.x, tid = threadIdx.x;
+  const int r0 = chunk_row[ch], nrows = chunk_row[ch + 1] - r0;
+  const int p0 = chunk_pt[ch], npts = chunk_pt[ch + 1] - p0;
   double acc[2] = {0.0, 0.0};
-  if (p < P) {
-    const int beg = pt_ptr[p], end = pt_ptr[p + 1];
-    double t0 = 0, t1 = 0, t2 = 0;
-    for (int i = beg; i < end; ++i) {
-      double a[8], b[3];
-      load8<JT>(Jc_ps + 8 * (size_t)i, a);
-      load3<JT>(Jp_ps + 4 * (size_t)i, b);
-      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + i));
+  if (nrows <= MV_CH) {
+    double b[3] = {0, 0, 0};
+    const size_t row = (size_t)r0 + tid;
+    if (tid < nrows) {
+      double a[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] = jget<JT>(Jc_ps, N, k, row);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, row);
+      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + row));
       const double2 x0 = xc[0], x1 = xc[1], x2 = xc[2], x3 = xc[3];
       const double s = a[0] * x0.x + a[1] * x0.y + a[2] * x1.x + a[3] * x1.y + a[4] * x2.x +
                        a[5] * x2.y + a[6] * x3.x + a[7] * x3.y;
-      t0 += b[0] * s; t1 += b[1] * s; t2 += b[2] * s;
+      sb[0][tid] = b[0] * s; sb[1][tid] = b[1] * s; sb[2][tid] = b[2] * s;
     }
+    __syncthreads();
+    if (tid < npts) {
+      const int p = p0 + tid;
+      const int beg = pt_ptr[p] - r0, end = pt_ptr[p + 1] - r0;
+      double t0 = 0, t1 = 0, t2 = 0;
+      for (int i = beg; i < end; ++i) { t0 += sb[0][i]; t1 += sb[1][i]; t2 += sb[2][i]; }
+      double vi[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
+      if (BACKSUB) {
+        const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
+        t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
+        const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
+        const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
+        const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
+        vp[3 * (size_t)p] = z0; vp[3 * (size_t)p + 1] = z1; vp[3 * (size_t)p + 2] = z2;
+        acc[0] = z0 * g0 + z1 * g1 + z2 * g2;
+        acc[1] = z0 * z0 + z1 * z1 + z2 * z2;
+      } else {
+        sz[0][tid] = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
+        sz[1][tid] = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
+        sz[2][tid] = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
+      }
+    }
+    if (!BACKSUB) {
+      __syncthreads();
+      if (tid < nrows) {
+        const int lp = __ldg(pt_ps + row) - p0;
+        w_ps[row] = b[0] * sz[0][lp] + b[1] * sz[1][lp] + b[2] * sz[2][lp];
+      }
+    }
+  } else {
+    // a single point with more than MV_CH observations: CTA-wide loop + ordered reduction
+    const int p = p0;
+    double t[3] = {0, 0, 0};
+    for (int i = tid; i < nrows; i += MV_CH) {
+      const size_t row = (size_t)r0 + i;
+      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + row));
+      double s = 0.0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const double2 xv = xc[k];
+        s += jget<JT>(Jc_ps, N, 2 * k, row) * xv.x + jget<JT>(Jc_ps, N, 2 * k + 1, row) * xv.y;
+      }
+#pragma unroll
+      for (int k = 0; k < 3; ++k) t[k] += jget<JT>(Jp_ps, N, k, row) * s;
+    }
+    block_sum<3>(t, sred);
+    if (tid == 0) { sz[0][0] = t[0]; sz[1][0] = t[1]; sz[2][0] = t[2]; }
+    __syncthreads();
+    double t0 = sz[0][0], t1 = sz[1][0], t2 = sz[2][0];
     double vi[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
     if (BACKSUB) {
-      const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
-      t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
-      const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
-      const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
-      const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
-      vp[3 * (size_t)p] = z0; vp[3 * (size_t)p + 1] = z1; vp[3 * (size_t)p + 2] = z2;
-      acc[0] = z0 * g0 + z1 * g1 + z2 * g2;
-      acc[1] = z0 * z0 + z1 * z1 + z2 * z2;
+      if (tid == 0) {
+        const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
+        t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
+        const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
+        const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
+        const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
+        vp[3 * (size_t)p] = z0; vp[3 * (size_t)p + 1] = z1; vp[3 * (size_t)p + 2] = z2;
+        acc[0] = z0 * g0 + z1 * g1 + z2 * g2;
+        acc[1] = z0 * z0 + z1 * z1 + z2 * z2;
+      }
     } else {
       const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
       const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
       const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
-      for (int i = beg; i < end; ++i) {
-        double b[3];
-        load3<JT>(Jp_ps + 4 * (size_t)i, b);
-        w_ps[i] = b[0] * z0 + b[1] * z1 + b[2] * z2;
+      for (int i = tid; i < nrows; i += MV_CH) {
+        const size_t row = (size_t)r0 + i;
+        w_ps[row] = jget<JT>(Jp_ps, N, 0, row) * z0 + jget<JT>(Jp_ps, N, 1, row) * z1 +
+                    jget<JT>(Jp_ps, N, 2, row) * z2;
       }
     }
   }
   if (BACKSUB) {
-    block_sum<2>(acc, sm);
-    if (threadIdx.x == 0) {
-      part[2 * blockIdx.x] = acc[0];
-      part[2 * blockIdx.x + 1] = acc[1];
+    block_sum<2>(acc, sred);
+    if (tid == 0) {
+      part[2 * ch] = acc[0];
+      part[2 * ch + 1] = acc[1];
     }
   }
 }
 
 // ---------------------------------------------------------------- K3b pass 2 (camera side)
-// ypart_c = - sum_{j in cs run of c} a_j w[perm[j]].  FUSE (single rank): y_c = (U_c + mu I) p_c +
-// ypart_c and part[c] = p_c . y_c, so no separate vector kernel is needed.
+// ypart_c = - sum_{j in cs run of c} a_j w[perm[j]].  FUSE (single rank): y_c = (U_c + mu I) x_c +
+// ypart_c and part[c] = x_c . y_c, so no separate vector kernel is needed.
 template <typename JT, bool FUSE>
 __global__ void __launch_bounds__(256)
 k_mv_cam(const SolverState* __restrict__ st, const int32_t* __restrict__ cam_ptr,
          const int32_t* __restrict__ perm_cs, const JT* __restrict__ Jc_cs,
-         const double* __restrict__ w_ps, const double* __restrict__ U, const double* __restrict__ pv,
+         const double* __restrict__ w_ps, const double* __restrict__ U, const double* __restrict__ xin,
          double* __restrict__ y, double* __restrict__ part) {
   __shared__ double sm[8 * 32];
   if (st->pcg_done) return;
@@ -86,22 +151,19 @@ k_mv_cam(const SolverState* __restrict__ st, const int32_t* __restrict__ cam_ptr
   block_sum<8>(acc, sm);
   if (threadIdx.x < 32) {
     if (FUSE) {
-      // lanes 0..7: row k of (U+mu I) p
-      const int k = threadIdx.x & 7;
+      const int k = threadIdx.x & 7;  // lanes 0..7: row k of (U + mu I) x
       const double mu = st->mu;
       double s = 0.0;
 #pragma unroll
-      for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * pv[8 * (size_t)c + l];
-      const double pk = pv[8 * (size_t)c + k];
-      s += mu * pk;
+      for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * xin[8 * (size_t)c + l];
+      const double xk = xin[8 * (size_t)c + k];
+      s += mu * xk;
       double yk = 0.0;
 #pragma unroll
-      for (int l = 0; l < 8; ++l) {
-        const double al = __shfl_sync(0xffffffffu, acc[l], 0);
-        if (l == k) yk = al;
-      }
+      for (int l = 0; l < 8; ++l)
+        if (l == k) yk = acc[l];
       yk += s;
-      double d = (threadIdx.x < 8) ? yk * pk : 0.0;
+      double d = (threadIdx.x < 8) ? yk * xk : 0.0;
       d = warp_sum(d);
       if (threadIdx.x < 8) y[8 * (size_t)c + k] = yk;
       if (threadIdx.x == 0) part[c] = d;
@@ -114,7 +176,7 @@ k_mv_cam(const SolverState* __restrict__ st, const int32_t* __restrict__ cam_ptr
 
 // multi-rank variant of the fused epilogue, run after the all-reduce of ypart
 __global__ void k_pcg_y(int C, const SolverState* __restrict__ st, const double* __restrict__ U,
-                        const double* __restrict__ pv, double* __restrict__ y, double* __restrict__ part) {
+                        const double* __restrict__ xin, double* __restrict__ y, double* __restrict__ part) {
   if (st->pcg_done) return;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -122,12 +184,12 @@ __global__ void k_pcg_y(int C, const SolverState* __restrict__ st, const double*
   double d = 0.0;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    double s = mu * pv[8 * (size_t)c + k];
+    double s = mu * xin[8 * (size_t)c + k];
 #pragma unroll
-    for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * pv[8 * (size_t)c + l];
+    for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * xin[8 * (size_t)c + l];
     const double yk = y[8 * (size_t)c + k] + s;
     y[8 * (size_t)c + k] = yk;
-    d += yk * pv[8 * (size_t)c + k];
+    d += yk * xin[8 * (size_t)c + k];
   }
   part[c] = d;
 }
@@ -146,94 +208,95 @@ __device__ __forceinline__ double cta_sum_strided(const double* __restrict__ in,
   return r;
 }
 
-// ---------------------------------------------------------------- K3c: PCG vector updates
-// Every CTA re-reduces the per-camera partials of p.y (ordered, identical in all CTAs), then
-// alpha = rz / pAp; x += alpha p; r -= alpha y; z = Minv r; part2[2c] = r.z, part2[2c+1] = r.r
+// ---------------------------------------------------------------- K3c: PCG vector kernel
+// Chronopoulos-Gear form of preconditioned CG: ONE fused reduction point per iteration, so an
+// iteration is three launches (this kernel, matvec pass 1, matvec pass 2) with no grid sync:
+//   gamma = (r,u), delta = (w,u) with u = Minv r, w = S u        [partials from earlier kernels]
+//   beta = gamma/gamma_old, alpha = gamma / (delta - beta gamma / alpha_old)   (it 0: beta 0, alpha gamma/delta)
+//   p = u + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  u = Minv r
+// Every CTA re-reduces the per-camera partials in the same order (bit-identical alpha/beta in all
+// CTAs).  Scalars carried between iterations are double-buffered in st->cg[it & 1] so no CTA can
+// read a value another CTA of the same launch has already overwritten.  8 threads per camera.
 __global__ void __launch_bounds__(256)
-k_pcg_update(int C, SolverState* __restrict__ st, const double* __restrict__ part,
-             const double* __restrict__ Minv, const double* __restrict__ pv,
-             const double* __restrict__ y, double* __restrict__ x, double* __restrict__ r,
-             double* __restrict__ z, double* __restrict__ part2) {
+k_pcg_vec(int C, int it, SolverState* __restrict__ st, const double* __restrict__ part_gr /*2C: gamma_c, rr_c*/,
+          const double* __restrict__ part_d /*C: delta_c*/, const double* __restrict__ Minv,
+          const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r, double* __restrict__ u,
+          double* __restrict__ pv, double* __restrict__ sv, double* __restrict__ part_out /*2C*/, double rtol,
+          int maxiter) {
   __shared__ double sm[32];
   if (st->pcg_done) return;
-  const double pAp = cta_sum_strided(part, C, 1, sm);
-  const double alpha = st->rz / pAp;
+  const double gamma = cta_sum_strided(part_gr, C, 2, sm);
+  const double rr = cta_sum_strided(part_gr + 1, C, 2, sm);
+  const double delta = cta_sum_strided(part_d, C, 1, sm);
+  const bool conv = rr <= rtol * rtol * st->rhs2;
+  const bool bad = !(rr == rr) || !(delta == delta);
+  const bool stop = conv || bad || it >= maxiter;
+  double alpha, beta;
+  if (it == 0) {
+    beta = 0.0;
+    alpha = gamma / delta;
+  } else {
+    const double g_old = st->cg[it & 1][0], a_old = st->cg[it & 1][1];
+    beta = gamma / g_old;
+    alpha = gamma / (delta - beta * gamma / a_old);
+  }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    st->pAp = pAp;
-    st->alpha = alpha;
-  }
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double rr[8];
-  double r2 = 0.0, rz = 0.0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const size_t o = 8 * (size_t)c + k;
-    x[o] += alpha * pv[o];
-    rr[k] = r[o] - alpha * y[o];
-    r[o] = rr[k];
-    r2 += rr[k] * rr[k];
-  }
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    double s = 0.0;
-#pragma unroll
-    for (int l = 0; l < 8; ++l) s += Minv[64 * (size_t)c + 8 * k + l] * rr[l];
-    z[8 * (size_t)c + k] = s;
-    rz += s * rr[k];
-  }
-  part2[2 * c] = rz;
-  part2[2 * c + 1] = r2;
-}
-
-// beta = rz_new / rz; p = z + beta p; convergence flag.  INIT: only reduce rz / |rhs|^2.
-template <bool INIT>
-__global__ void __launch_bounds__(256)
-k_pcg_dir(int C, SolverState* __restrict__ st, const double* __restrict__ part2,
-          const double* __restrict__ z, double* __restrict__ pv, double rtol, int maxiter) {
-  __shared__ double sm[32];
-  if (!INIT && st->pcg_done) return;
-  const double rz_new = cta_sum_strided(part2, C, 2, sm);
-  const double rr = cta_sum_strided(part2 + 1, C, 2, sm);
-  if (INIT) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-      st->rz = rz_new;
-      st->rr = rr;
-      st->rhs2 = rr;
-      st->pcg_iters = 0;
-      st->pcg_done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
-    }
-    return;
-  }
-  const double beta = rz_new / st->rz;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c < C) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const size_t o = 8 * (size_t)c + k;
-      pv[o] = z[o] + beta * pv[o];
-    }
-  }
-  // last CTA-independent state write must come after every CTA has read st->rz: deferred to
-  // k_pcg_commit (next kernel in stream order).
-  (void)rr; (void)rtol; (void)maxiter;
-}
-
-__global__ void k_pcg_commit(int C, SolverState* __restrict__ st, const double* __restrict__ part2,
-                             double rtol, int maxiter) {
-  __shared__ double sm[32];
-  if (st->pcg_done) return;
-  const double rz_new = cta_sum_strided(part2, C, 2, sm);
-  const double rr = cta_sum_strided(part2 + 1, C, 2, sm);
-  if (threadIdx.x == 0) {
-    st->beta = rz_new / st->rz;
-    st->rz = rz_new;
     st->rr = rr;
-    st->pcg_iters += 1;
-    const bool conv = rr <= rtol * rtol * st->rhs2;
-    const bool bad = !(rr == rr);
-    if (conv || bad || st->pcg_iters >= maxiter) st->pcg_done = 1;
-    if (!conv && !bad && st->pcg_iters >= maxiter) st->status |= 4;
+    st->pcg_iters = it;
+    if (stop) {
+      st->pcg_done = 1;
+      if (!conv && !bad) st->status |= 4;
+    } else {
+      st->cg[(it + 1) & 1][0] = gamma;
+      st->cg[(it + 1) & 1][1] = alpha;
+      st->alpha = alpha;
+      st->beta = beta;
+    }
+  }
+  if (stop) return;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;  // element index: camera e>>3, row e&7
+  const int c = e >> 3, k = e & 7;
+  double rk = 0.0, uk = 0.0;
+  const bool act = c < C;
+  if (act) {
+    const double pk = u[e] + beta * pv[e];
+    const double sk = w[e] + beta * sv[e];
+    pv[e] = pk;
+    sv[e] = sk;
+    x[e] += alpha * pk;
+    rk = r[e] - alpha * sk;
+    r[e] = rk;
+  }
+  // u_k = sum_l Minv[k][l] r_l : r of the camera lives in the 8-lane group
+  const int base = (threadIdx.x & 31) & ~7;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) {
+    const double rl = __shfl_sync(0xffffffffu, rk, base + l);
+    if (act) uk += Minv[64 * (size_t)c + 8 * k + l] * rl;
+  }
+  if (act) u[e] = uk;
+  double g = rk * uk, q = rk * rk;
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    g += __shfl_xor_sync(0xffffffffu, g, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (act && k == 0) {
+    part_out[2 * c] = g;
+    part_out[2 * c + 1] = q;
+  }
+}
+
+// PCG start-up reduction: rhs2 = |rhs|^2
+__global__ void __launch_bounds__(256)
+k_pcg_init(int C, SolverState* __restrict__ st, const double* __restrict__ part_gr) {
+  __shared__ double sm[32];
+  const double rr = cta_sum_strided(part_gr + 1, C, 2, sm);
+  if (threadIdx.x == 0) {
+    st->rr = rr;
+    st->rhs2 = rr;
+    st->pcg_iters = 0;
+    st->pcg_done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
   }
 }
 
@@ -315,12 +378,12 @@ __global__ void k_accept_copy(const SolverState* __restrict__ st, int64_t n, con
   if (i < n) dst[i] = src[i];
 }
 
-// row gather for the API that returns rows in the caller's order: out[order[i]*w + k] = in[i*ws + k]
+// rows back in the caller's order: out[order[i]*w + k] = in[k*kstride + i]   (SoA ps arrays)
 template <typename TI>
 __global__ void k_unpermute_rows(int64_t N, const int32_t* __restrict__ order_ps, const TI* __restrict__ in,
-                                 int ws, int w, double* __restrict__ out) {
+                                 size_t kstride, int w, double* __restrict__ out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N) return;
   const int64_t o = order_ps[i];
-  for (int k = 0; k < w; ++k) out[o * w + k] = (double)in[i * ws + k];
+  for (int k = 0; k < w; ++k) out[o * w + k] = (double)in[(size_t)k * kstride + i];
 }

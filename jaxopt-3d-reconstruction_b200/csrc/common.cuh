@@ -10,6 +10,7 @@
 struct SolverState {
   double mu, nu, loss, loss_trial, grad2, maxdiag, rho, denom;
   double rz, rz_new, pAp, rr, rhs2, alpha, beta, vg, vv;
+  double cg[2][2];  // double-buffered (gamma, alpha) of the Chronopoulos-Gear recurrence
   int accepted, pcg_done, pcg_iters, status;
 };
 
