@@ -38,7 +38,8 @@ int b200ba_plan_destroy(b200ba_plan* plan);
  * (points_2d_all of bundle_adjustment.py:104-111 with mask==1 rows only). */
 int b200ba_plan_set_observations(b200ba_plan* plan, const double* obs_xy, void* stream);
 /* Optional: sum camera blocks / gradients / PCG dots across ranks (NCCL over NVLink).
- * unique_id_host: 128 bytes from b200ba_nccl_unique_id on rank 0, broadcast by the caller. */
+ * unique_id_host: 128 bytes from b200ba_nccl_unique_id on rank 0, broadcast by the caller; the
+ * communicator is created once per process and shared by later plans (pass NULL to re-use it). */
 int b200ba_nccl_unique_id(char* unique_id_host /*128 B*/);
 int b200ba_plan_set_comm(b200ba_plan* plan, int rank, int nranks, const char* unique_id_host);
 

@@ -218,8 +218,14 @@ class B200BundleAdjustment:
             self._init_comm(prob)
         return prob
 
+    _comm_ready = False  # one NCCL communicator per process, shared by every plan
+
     def _init_comm(self, prob):
         import torch.distributed as dist
+        if B200BundleAdjustment._comm_ready:
+            with torch.cuda.device(self.device):
+                check(prob.lib.b200ba_plan_set_comm(prob.plan, self.rank, self.world, None), "set_comm")
+            return
         uid = torch.zeros(128, dtype=torch.uint8)
         if self.rank == 0:
             buf = C.create_string_buffer(128)
@@ -231,6 +237,7 @@ class B200BundleAdjustment:
         raw = bytes(t.cpu().numpy().tobytes())
         with torch.cuda.device(self.device):
             check(prob.lib.b200ba_plan_set_comm(prob.plan, self.rank, self.world, raw), "set_comm")
+        B200BundleAdjustment._comm_ready = True
 
     # ------------------------------------------------------------------ solve
     def solve_device(self, prob: BAProblem, cam8, k3, pts, maxiter=None, tol=None):

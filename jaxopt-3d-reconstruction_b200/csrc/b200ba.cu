@@ -184,7 +184,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
   p->lin_scal = p->gc + (size_t)C * 8;
-  p->nblkN = (int)cdiv(N, 256); p->nblkP = (int)cdiv(P, 256);
+  p->nblkN = (int)cdiv(N, RJ_THREADS); p->nblkP = (int)cdiv(P, 256);
   A(part, 2 * (size_t)C + 16) A(part2, 2 * (size_t)C + 16)
   A(scal, 32) A(st, 1)
 #undef A
@@ -290,7 +290,6 @@ extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
   for (void* q : p->allocs) cudaFree(q);
   if (p->st_host) cudaFreeHost(p->st_host);
   if (p->scal_host) cudaFreeHost(p->scal_host);
-  if (p->comm) ncclCommDestroy(p->comm);
   for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
   delete p;
   return B200BA_OK;
@@ -313,12 +312,23 @@ extern "C" int b200ba_nccl_unique_id(char* out) {
   return B200BA_OK;
 }
 
+// One communicator per process, shared by every plan (creating one costs ~1 s, a plan is rebuilt per
+// problem).  unique_id_host == NULL re-uses the communicator created by an earlier call.
+static ncclComm_t g_comm = nullptr;
+static int g_rank = 0, g_nranks = 1;
 extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const char* uid) {
-  if (!p || !uid || nranks < 1 || rank < 0 || rank >= nranks) FAIL(B200BA_EINVAL, "set_comm: bad args");
+  if (!p || nranks < 1 || rank < 0 || rank >= nranks) FAIL(B200BA_EINVAL, "set_comm: bad args");
   if (nranks == 1) return B200BA_OK;
-  ncclUniqueId id;
-  memcpy(&id, uid, 128);
-  CKN(ncclCommInitRank(&p->comm, nranks, id, rank));
+  if (uid) {
+    if (g_comm) { ncclCommDestroy(g_comm); g_comm = nullptr; }
+    ncclUniqueId id;
+    memcpy(&id, uid, 128);
+    CKN(ncclCommInitRank(&g_comm, nranks, id, rank));
+    g_rank = rank;
+    g_nranks = nranks;
+  }
+  if (!g_comm || g_rank != rank || g_nranks != nranks) FAIL(B200BA_EINVAL, "set_comm: no matching communicator; pass a unique id");
+  p->comm = g_comm;
   p->rank = rank;
   p->nranks = nranks;
   return B200BA_OK;
@@ -354,7 +364,7 @@ struct Ops {
     const int64_t N = p->N;
     PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
     if (N) {
-      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), p->nblkN, 256, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
+      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), p->nblkN, RJ_THREADS, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
              p->inv_cs, p->r_ps, (JT*)p->Jc_ps, (JT*)p->Jp_ps, (JT*)p->Jc_cs, p->r_cs, p->partN);
     }
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
@@ -450,7 +460,7 @@ struct Ops {
                   double* out_dev, cudaStream_t s) {
     PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
     if (p->N)
-      PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->nblkN, 256, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
+      PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->nblkN, RJ_THREADS, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
              inv_w2, p->inv_cs, nullptr, nullptr, nullptr, nullptr, nullptr, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
     return 0;

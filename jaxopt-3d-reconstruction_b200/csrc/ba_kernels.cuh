@@ -52,22 +52,38 @@ __global__ void k_cam_table(int C, const double* __restrict__ cam8, const double
 }
 
 // ---------------------------------------------------------------- K1: residual + Jacobian rows
-// One thread per observation in ps order.  Writes r and the Jacobian row in ps order and the
-// camera part again at the row's cs position (64/32 B aligned scatter = whole sectors), which
-// the camera-side reductions then stream.  cost_part[block] = sum r^2 of the block.
+// One thread per observation in ps order.  The camera of every row differs, so the 26-double
+// camera tables are fetched COOPERATIVELY: for each of the warp's 32 rows the whole warp issues one
+// coalesced 256 B load of that row's table into shared memory (row stride 33 doubles: conflict-free
+// per-lane reads afterwards) instead of 26 scattered 8 B loads per lane.
+// Writes r and the Jacobian row in ps order (SoA, coalesced) and the camera part again at the
+// row's cs position (64 B aligned scatter = whole sectors), which the camera-side reductions then
+// stream.  cost_part[block] = sum r^2 of the block.
+#define RJ_THREADS 128
+#define RJ_TSTRIDE 33
 template <typename JT, bool WITH_JAC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(RJ_THREADS)
 k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
          const double2* __restrict__ obs_ps, const double* __restrict__ tab,
          const double* __restrict__ pts, double inv_w2, const int32_t* __restrict__ inv_cs,
          double* __restrict__ r_ps, JT* __restrict__ Jc_ps, JT* __restrict__ Jp_ps,
          JT* __restrict__ Jc_cs, double* __restrict__ r_cs, double* __restrict__ cost_part) {
   __shared__ double sm[32];
+  __shared__ double stab[RJ_THREADS / 32][32][RJ_TSTRIDE];
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const bool act = i < N;
+  const int c = act ? __ldg(cam_ps + i) : 0;
+#pragma unroll 8
+  for (int rr = 0; rr < 32; ++rr) {
+    const int cr = __shfl_sync(0xffffffffu, c, rr);
+    stab[wid][rr][lane] = __ldg(tab + (size_t)TAB_STRIDE * cr + lane);
+  }
+  __syncwarp();
   double v[1] = {0.0};
-  if (i < N) {
-    const int c = __ldg(cam_ps + i), p = __ldg(pt_ps + i);
-    const double* T = tab + (size_t)TAB_STRIDE * c;
+  if (act) {
+    const int p = __ldg(pt_ps + i);
+    const double* T = &stab[wid][lane][0];
     const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1),
                  Z = __ldg(pts + 3 * (size_t)p + 2);
     const double2 o = __ldg(obs_ps + i);
