@@ -38,8 +38,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="venice1778")
-    ap.add_argument("--jac-f32", action="store_true", help="fp32 Jacobian rows (not the parity default)")
-    ap.add_argument("--pcg-rtol", type=float, default=1e-12)
+    ap.add_argument("--jac-f64", action="store_true", help="store Jacobian rows in fp64 (default: fp32 rows, fp64 accumulation)")
+    ap.add_argument("--pcg-rtol", type=float, default=1e-10)
     ap.add_argument("--no-pose", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
@@ -218,7 +218,7 @@ def run_b200(args):
         return float(t.item())
 
     sc = b200ba.synth.make_ba_scene(args.workload, seed=args.seed)
-    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device=dev, jac_f32=args.jac_f32,
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device=dev, jac_f32=not args.jac_f64,
                                      pcg_rtol=args.pcg_rtol)
     x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
     # pinned host copies (the e2e leg copies from these every solve)
@@ -270,7 +270,7 @@ def run_b200(args):
     cnt_cls = (C.c_int64 * 16)()
     lib.b200ba_profile_get(prob.plan, ms_cls, cnt_cls)
     lib.b200ba_profile_enable(prob.plan, 0)
-    jsz = 4 if args.jac_f32 else 8
+    jsz = 8 if args.jac_f64 else 4
     bm = bytes_models(sc.C, prob.P, prob.N, jsz)
     peak, peak_src = load_peaks()
     kern = {}
@@ -318,11 +318,11 @@ def run_b200(args):
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64" if not args.jac_f32 else "f64 (f32 J rows)",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64" if args.jac_f64 else "f64 (f32-stored Jacobian rows, f64 accumulation)",
             "data": "synthetic",
             "config": {"workload": args.workload, "C": sc.C, "P": sc.P, "N": sc.N, "parallelism": f"point-shard x{world}",
                        "pcg_rtol": args.pcg_rtol, "l2": "inputs exceed L2 (Jacobian rows %.2f GB per matvec)" %
-                       ((bm["mv_pt"] + bm["mv_cam"]) / 1e9), "jacobian_rows": "fp32" if args.jac_f32 else "fp64"},
+                       ((bm["mv_pt"] + bm["mv_cam"]) / 1e9), "jacobian_rows": "fp64" if args.jac_f64 else "fp32"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
             "extra": {"solves": [{"iters": i[0], "loss": i[1], "grad_l2": i[2], "pcg_iters": i[3], "jac_evals": i[4],
                                   "status": i[5]} for i in info],

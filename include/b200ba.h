@@ -31,7 +31,7 @@ int b200ba_version(void);
  * camera-major permutation and CSR offsets, sizes all workspaces.  C is the GLOBAL camera
  * count; P/N are this rank's points / observations (multi-GPU: shard by point). */
 int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_idx, const int32_t* pt_idx,
-                       int jac_f32 /*0: fp64 Jacobian rows (parity default), 1: fp32 rows*/,
+                       int jac_f32 /*1: Jacobian rows stored fp32, fp64 accumulation (default of the facade); 0: fp64 rows*/,
                        void* stream, b200ba_plan** out);
 int b200ba_plan_destroy(b200ba_plan* plan);
 /* obs: N x 2 pixels in the SAME row order as cam_idx/pt_idx given to plan_create

@@ -94,7 +94,7 @@ class LMState:
 class BAProblem:
     """Problem structure resident on the GPU: plan (sorted rows, CSR, workspaces) + observations."""
 
-    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=False):
+    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True):
         lib = _require_cuda()
         self.lib = lib
         self.C, self.P, self.N = int(C_), int(P), int(cam_idx.numel())
@@ -136,7 +136,7 @@ class B200BundleAdjustment:
     """Drop-in for JaxBundleAdjustment(cam_num, avg_cam_width)."""
 
     def __init__(self, cam_num, avg_cam_width, device=None, tol=1e-6, maxiter=100,
-                 damping_parameter=1e-6, pcg_rtol=1e-12, pcg_maxiter=1000, jac_f32=False,
+                 damping_parameter=1e-6, pcg_rtol=1e-10, pcg_maxiter=1000, jac_f32=True,
                  verbose=False, process_group=None, distributed=None):
         self.cam_num = int(cam_num)
         self.avg_cam_width_sqr = float(avg_cam_width) ** 2

@@ -594,7 +594,7 @@ extern "C" void b200ba_lm_default_opts(b200ba_lm_opts* o) {
   o->maxiter = 100;
   o->tol = 1e-6;
   o->damping_parameter = 1e-6;
-  o->pcg_rtol = 1e-12;
+  o->pcg_rtol = 1e-10;
   o->pcg_maxiter = 1000;
   o->fixed_pcg_iters = 0;
   o->verbose = 0;

@@ -30,13 +30,26 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
   if (nrows <= MV_CH) {
     double b[3] = {0, 0, 0};
     const size_t row = (size_t)r0 + tid;
+    // issue every global load of the CTA's lifetime up front (one DRAM round trip + the x gather)
+    double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
+    int beg = 0, end = 0, lp = 0;
+    if (tid < npts) {
+      const int p = p0 + tid;
+      beg = __ldg(pt_ptr + p) - r0;
+      end = __ldg(pt_ptr + p + 1) - r0;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
+      if (BACKSUB) { g0 = gp[3 * (size_t)p]; g1 = gp[3 * (size_t)p + 1]; g2 = gp[3 * (size_t)p + 2]; }
+    }
     if (tid < nrows) {
       double a[8];
+      const int cam = __ldg(cam_ps + row);
+      if (!BACKSUB) lp = __ldg(pt_ps + row) - p0;
 #pragma unroll
       for (int k = 0; k < 8; ++k) a[k] = jget<JT>(Jc_ps, N, k, row);
 #pragma unroll
       for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, row);
-      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + row));
+      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)cam);
       const double2 x0 = xc[0], x1 = xc[1], x2 = xc[2], x3 = xc[3];
       const double s = a[0] * x0.x + a[1] * x0.y + a[2] * x1.x + a[3] * x1.y + a[4] * x2.x +
                        a[5] * x2.y + a[6] * x3.x + a[7] * x3.y;
@@ -45,14 +58,9 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
     __syncthreads();
     if (tid < npts) {
       const int p = p0 + tid;
-      const int beg = pt_ptr[p] - r0, end = pt_ptr[p + 1] - r0;
       double t0 = 0, t1 = 0, t2 = 0;
       for (int i = beg; i < end; ++i) { t0 += sb[0][i]; t1 += sb[1][i]; t2 += sb[2][i]; }
-      double vi[6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
       if (BACKSUB) {
-        const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
         t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
         const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
         const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
@@ -68,10 +76,7 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
     }
     if (!BACKSUB) {
       __syncthreads();
-      if (tid < nrows) {
-        const int lp = __ldg(pt_ps + row) - p0;
-        w_ps[row] = b[0] * sz[0][lp] + b[1] * sz[1][lp] + b[2] * sz[2][lp];
-      }
+      if (tid < nrows) w_ps[row] = b[0] * sz[0][lp] + b[1] * sz[1][lp] + b[2] * sz[2][lp];
     }
   } else {
     // a single point with more than MV_CH observations: CTA-wide loop + ordered reduction

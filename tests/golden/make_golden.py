@@ -15,7 +15,7 @@ from oracle import pose_oracle as po  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 
-for shape, seed in [("small", 0), ("ladybug49", 0)]:
+for shape, seed in [("small", 0), ("ladybug49", 0), ("trafalgar257", 0)]:
     sc = b200ba.synth.make_ba_scene(shape, seed=seed)
     x0, ccs = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
     res = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, ccs, sc.avg_cam_width)

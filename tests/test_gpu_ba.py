@@ -10,7 +10,7 @@ from oracle import ba_oracle as bo
 pytestmark = pytest.mark.gpu
 
 
-def _setup(shape, seed=0, jac_f32=False, **kw):
+def _setup(shape, seed=0, jac_f32=False, **kw):  # building-block tests use fp64 rows (tight row tolerances)
     sc = b200ba.synth.make_ba_scene(shape, seed=seed, **kw)
     ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=jac_f32)
     x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
@@ -72,9 +72,12 @@ def test_schur_blocks_and_step(shape):
     assert np.linalg.norm(vp.cpu().numpy() - vpo) <= 1e-5 * np.linalg.norm(vpo)
 
 
+@pytest.mark.parametrize("jac_f32", [True, False])
 @pytest.mark.parametrize("shape", ["small", "ladybug49"])
-def test_lm_trajectory_vs_exact_oracle(shape):
-    sc, ba, x0, k3 = _setup(shape)
+def test_lm_trajectory_vs_exact_oracle(shape, jac_f32):
+    """default build (fp32-stored rows, fp64 accumulation) and the fp64-row build, both within the
+    north_star tolerances: per-iteration cost 1e-5 rel, final RMS 1e-4 rel."""
+    sc, ba, x0, k3 = _setup(shape, jac_f32=jac_f32)
     params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
     ref = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width)
     assert st.iter_num == ref.iter_num
@@ -94,3 +97,36 @@ def test_dense_padded_contract_equals_sparse():
     assert sa.iter_num == sb.iter_num
     np.testing.assert_array_equal(pa, pb)  # row order must not matter: bit-identical
     np.testing.assert_array_equal(sa.loss_trajectory, sb.loss_trajectory)
+
+
+def test_trafalgar_config_trajectory_golden():
+    """BASELINE config 3 (Trafalgar-257 shape) against the frozen exact-oracle trajectory
+    (tests/golden/ba_trafalgar257_seed0.npz; the oracle solve takes ~10 s so it is not re-run here)."""
+    import os
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "ba_trafalgar257_seed0.npz"))
+    sc = b200ba.synth.make_ba_scene("trafalgar257", seed=0)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width)
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    np.testing.assert_array_equal(x0[:64], gold["x0"])
+    params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+    assert st.iter_num == int(gold["iter_num"])
+    np.testing.assert_allclose(st.loss_trajectory, gold["loss"], rtol=1e-5)
+    rms = bo.rms_reprojection_px(params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    assert rms == pytest.approx(float(gold["rms_px"]), rel=1e-4)
+
+
+def test_fp32_rows_track_fp64_rows_at_scale():
+    """Size-independent check at a shape the exact oracle cannot reach in seconds: the default
+    fp32-row build follows the (oracle-validated) fp64-row build within 1e-5 per iteration."""
+    sc = b200ba.synth.make_ba_scene(C=600, P=150000, N=750000, seed=5)
+    out = []
+    for f32 in (True, False):
+        ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=f32, pcg_rtol=1e-10 if f32 else 1e-12)
+        x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+        out.append(ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None))
+    (pa, sa), (pb, sb) = out
+    assert sa.iter_num == sb.iter_num
+    np.testing.assert_allclose(sa.loss_trajectory, sb.loss_trajectory, rtol=1e-5)
+    ra = bo.rms_reprojection_px(pa, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    rb = bo.rms_reprojection_px(pb, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    assert ra == pytest.approx(rb, rel=1e-4)
