@@ -121,38 +121,26 @@ def bytes_models(C, P, N, jsz):
 
 # ---------------------------------------------------------------------------- CPU baseline (oracle)
 def cpu_lm_iteration_sample(sc, x0, k3, cg_cap):
-    """One LM iteration of the reference's formulation on the host cores: residual + Jacobian,
-    then jaxopt-style unpreconditioned CG on the full normal equations TRUNCATED at `cg_cap`
-    iterations (the tol=1e-5 solve needs hundreds), trial residual, gain ratio.  Because the CG is
-    cut short the resulting iterations/s is an UPPER bound on the CPU path's speed."""
-    from oracle import ba_oracle as bo
-    ci, pi = sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)
-    w2 = sc.avg_cam_width ** 2
+    """One LM iteration of the reference's formulation on ALL host cores (oracle/ba_oracle_c.c, OpenMP):
+    residual + Jacobian, jaxopt-style unpreconditioned CG on the full normal equations TRUNCATED at
+    `cg_cap` iterations (the tol=1e-5 solve needs hundreds), trial residual, gain ratio, and (on
+    accept) re-linearisation.  Because the CG is cut short the resulting iterations/s is an UPPER
+    bound on the CPU path's speed."""
+    from oracle import c_binding as cb
     t0 = time.perf_counter()
-    r, _, a, b = bo.ba_eval(x0, sc.C, ci, pi, sc.obs, k3, w2)
-    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, ci, pi)
-    g = J.T @ r
-    diag = np.asarray(J.multiply(J).sum(axis=0)).reshape(-1)
-    mu = 1e-6 * float(diag.max())
-    v, inner = bo._cg_jaxopt(lambda p: J.T @ (J @ p) + mu * p, g, tol=1e-5, maxiter=cg_cap)
-    xn = x0 - v
-    rn, _, _, _ = bo.ba_eval(xn, sc.C, ci, pi, sc.obs, k3, w2, want_jac=False)
-    rho = (0.5 * r @ r - 0.5 * rn @ rn) / (0.5 * (-v) @ (mu * (-v) - g))
-    return time.perf_counter() - t0, inner, float(rho)
+    res = cb.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width, maxiter=1, cg_cap=cg_cap)
+    return time.perf_counter() - t0, int(res["cg_iters"][0]), float(res["loss"][-1])
 
 
 def cpu_threads():
-    try:
-        from threadpoolctl import threadpool_info
-        n = [p.get("num_threads", 1) for p in threadpool_info()]
-        return max(n) if n else 1
-    except Exception:
-        return 1
+    from oracle import c_binding as cb
+    return cb.num_threads()
 
 
 def run_reference(args):
     """--impl reference: the reference's CPU path. jax/jaxopt are not installable here (no wheels,
-    no network), so this times the oracle port (float64 NumPy/SciPy restatement, jaxopt_cg mode)."""
+    no network), so this times the oracle port (oracle/ba_oracle_c.c: float64 C + OpenMP restatement of
+    the reference's residual and jaxopt's LM with full-system CG) on all host cores."""
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
@@ -160,7 +148,7 @@ def run_reference(args):
     sc = b200ba.synth.make_ba_scene(args.workload, seed=args.seed)
     from oracle import ba_oracle as bo
     x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
-    cg_cap = 10
+    cg_cap = 25
     for _ in range(min(args.warmup, 1)):
         cpu_lm_iteration_sample(sc, x0, k3, 2)
     ts = []
@@ -331,7 +319,7 @@ def run_b200(args):
     if not args.no_pose and world == 1:
         line["extra"]["pose"] = bench_pose(b200ba, dev, args)
     if not args.no_cpu_baseline and world == 1:
-        t, inner, rho = cpu_lm_iteration_sample(sc, x0, k3, 10)
+        t, inner, rho = cpu_lm_iteration_sample(sc, x0, k3, 25)
         line["cpu_baseline"] = {"value": 1.0 / t, "unit": UNIT, "cores": cpu_threads(), "kind": "port",
                                 "sample": f"1 LM iteration at {args.workload} (residual+Jacobian, unpreconditioned CG "
                                           f"truncated at {inner} its, trial residual); upper bound on CPU it/s"}
