@@ -25,6 +25,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")  # spinning OpenMP workers oversubscribe shared host cores
 os.environ["NCCL_DEBUG"] = "WARN"  # NCCL prints its version banner on stdout at VERSION/INFO; stdout is one JSON line
 
 METRIC = "ba_lm_iterations_per_s"
