@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ba.so")
+LIB_PATH = os.environ.get("B200BA_LIB") or os.path.join(_HERE, "libb200ba.so")  # B200BA_LIB: kernel-variant experiments
 
 SYMBOLS = [
     "b200ba_last_error", "b200ba_version", "b200ba_plan_create", "b200ba_plan_destroy",

@@ -8,6 +8,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -52,6 +53,7 @@ struct b200ba_plan {
   int C = 0, P = 0;
   int64_t N = 0;
   int jac_f32 = 0;
+  int wscatter = 0;  // matvec pass 1 writes w at camera-sorted positions (else pass 2 gathers)
   size_t jsz = 8;
   // structure (device)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // ps rows
@@ -62,7 +64,7 @@ struct b200ba_plan {
   double2* obs_ps = nullptr;
   // linearisation
   void *Jc_ps = nullptr, *Jp_ps = nullptr, *Jc_cs = nullptr;
-  double *r_ps = nullptr, *r_cs = nullptr, *w_ps = nullptr, *beta_ps = nullptr;
+  double *r_ps = nullptr, *r_cs = nullptr, *w_ps = nullptr, *beta_ps = nullptr, *w_cs = nullptr;
   double *tab = nullptr, *tab_trial = nullptr;
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
@@ -171,11 +173,12 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   cudaStream_t s = (cudaStream_t)stream_;
   b200ba_plan* p = new b200ba_plan();
   p->C = C; p->P = P; p->N = N; p->jac_f32 = jac_f32 ? 1 : 0; p->jsz = jac_f32 ? 4 : 8;
+  { const char* e = getenv("B200BA_WSCATTER"); p->wscatter = e ? atoi(e) : 0; }
   int rc = 0;
 #define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
   A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(perm_cs, N) A(inv_cs, N)
   A(pt_ptr, P + 1) A(cam_ptr, C + 1) A(obs_ps, N)
-  A(r_ps, N) A(r_cs, N) A(w_ps, N) A(beta_ps, N)
+  A(r_ps, N) A(r_cs, N) A(w_ps, N) A(beta_ps, N) A(w_cs, N)
   A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
@@ -250,7 +253,8 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaStreamSynchronize(s);
   }
   {
-    // greedy chunks of whole points with <= MV_CH rows (a point with more rows is its own chunk)
+    // greedy chunks of whole points with <= cap rows and <= MV_T points (a point with more rows is its own chunk)
+    const int cap = MV_T * (p->jac_f32 ? MvCfg<float>::RPT : MvCfg<double>::RPT);
     std::vector<int32_t> hptr((size_t)P + 1), crow, cpt;
     if (cudaMemcpy(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
       b200ba_plan_destroy(p);
@@ -261,7 +265,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int cur = 0;
     for (int q = 0; q < P; ++q) {
       const int d = hptr[q + 1] - hptr[q];
-      if ((cur > 0 && cur + d > MV_CH) || q - cpt.back() >= MV_CH) {
+      if ((cur > 0 && cur + d > cap) || q - cpt.back() >= MV_T) {
         crow.push_back(hptr[q]);
         cpt.push_back(q);
         cur = 0;
@@ -401,19 +405,25 @@ struct Ops {
   // y = S xin (xin: C x 8 device vector); part[c] = xin_c . y_c
   static int matvec(b200ba_plan* p, const double* xin, cudaStream_t s) {
     const int C = p->C;
-    if (p->N) PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false>), p->nchunks, MV_CH, 0, s, (size_t)p->N, p->st, p->chunk_row,
-                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps, p->Vinv, xin,
-                      p->w_ps, nullptr, nullptr, nullptr);
+#define MV_ARGS (size_t)p->N, p->st, p->chunk_row, p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, p->inv_cs, (const JT*)p->Jc_ps, \
+                (const JT*)p->Jp_ps, p->Vinv, xin, p->w_cs, nullptr, nullptr, nullptr
+#define CAM_ARGS p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_cs, p->U, xin, p->y, p->part
+    if (p->N) {
+      if (p->wscatter) PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false, true>), p->nchunks, MV_T, 0, s, MV_ARGS);
+      else PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false, false>), p->nchunks, MV_T, 0, s, MV_ARGS);
+    }
     if (p->nranks == 1) {
-      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs,
-              p->w_ps, p->U, xin, p->y, p->part);
+      if (p->wscatter) PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true, false>), C, 256, 0, s, CAM_ARGS);
+      else PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true, true>), C, 256, 0, s, CAM_ARGS);
     } else {
-      PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false>), C, 256, 0, s, p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs,
-              p->w_ps, p->U, xin, p->y, p->part);
+      if (p->wscatter) PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false, false>), C, 256, 0, s, CAM_ARGS);
+      else PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false, true>), C, 256, 0, s, CAM_ARGS);
       int rc;
       if ((rc = allreduce(p, p->y, (size_t)C * 8, ncclSum, s))) return rc;
       PLAUNCH(p, PC_PCG_VEC, k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, xin, p->y, p->part);
     }
+#undef MV_ARGS
+#undef CAM_ARGS
     return 0;
   }
 
@@ -448,9 +458,9 @@ struct Ops {
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
     const int P = p->P;
-    if (p->N) PLAUNCH(p, PC_BACKSUB, (k_mv_rows<JT, true>), p->nchunks, MV_CH, 0, s, (size_t)p->N, p->st, p->chunk_row,
-                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps, p->Vinv, p->x,
-                      nullptr, p->gp, p->vp, p->partN);
+    if (p->N) PLAUNCH(p, PC_BACKSUB, (k_mv_rows<JT, true, false>), p->nchunks, MV_T, 0, s, (size_t)p->N, p->st, p->chunk_row,
+                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, p->inv_cs, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps,
+                      p->Vinv, p->x, nullptr, p->gp, p->vp, p->partN);
     (void)P;
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;

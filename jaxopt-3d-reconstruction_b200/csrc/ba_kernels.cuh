@@ -5,19 +5,28 @@
 #pragma once
 #include "common.cuh"
 
+// 256-bit read-only loads (sm_100: LDG.E.256): one request per 32 B sector instead of two 128-bit
+// ones — halves the L1 wavefronts of every 32/64 B row gather.  p must be 32 B aligned.
+__device__ __forceinline__ void ld256(const double* __restrict__ p, double* v) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld256(const float* __restrict__ p, float* v) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
 template <typename JT>
 __device__ __forceinline__ void load8(const JT* __restrict__ p, double* a);
 template <>
 __device__ __forceinline__ void load8<double>(const double* __restrict__ p, double* a) {
-  const double2* q = reinterpret_cast<const double2*>(p);
-  double2 v0 = __ldg(q), v1 = __ldg(q + 1), v2 = __ldg(q + 2), v3 = __ldg(q + 3);
-  a[0] = v0.x; a[1] = v0.y; a[2] = v1.x; a[3] = v1.y; a[4] = v2.x; a[5] = v2.y; a[6] = v3.x; a[7] = v3.y;
+  ld256(p, a);
+  ld256(p + 4, a + 4);
 }
 template <>
 __device__ __forceinline__ void load8<float>(const float* __restrict__ p, double* a) {
-  const float4* q = reinterpret_cast<const float4*>(p);
-  float4 v0 = __ldg(q), v1 = __ldg(q + 1);
-  a[0] = v0.x; a[1] = v0.y; a[2] = v0.z; a[3] = v0.w; a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
+  float v[8];
+  ld256(p, v);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = v[k];
 }
 template <typename JT>
 __device__ __forceinline__ void store8(JT* __restrict__ p, const double* a);

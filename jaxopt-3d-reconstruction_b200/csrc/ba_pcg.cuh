@@ -5,34 +5,43 @@
 #include "ba_kernels.cuh"
 
 // ---------------------------------------------------------------- K3b pass 1 (point side)
-// Rows are processed in CHUNKS of whole points (<= MV_CH rows, built once per plan), one CTA per
-// chunk, one THREAD PER ROW: phase 1 s_i = a_i . x_c(i) with coalesced SoA loads, b_i s_i to shared
-// memory; phase 2 one thread per point sums its run in order, z_p = Vinv_p t_p; phase 3 every row
-// thread computes w_i = b_i . z_p and stores it coalesced.
+// Rows are processed in CHUNKS of whole points (<= MV_T*RPT rows and <= MV_T points, built once per
+// plan), one CTA per chunk, RPT rows per thread (row = r0 + tid + j*MV_T: coalesced SoA loads, all
+// issued before the first barrier so a CTA costs ~one DRAM round trip + the x gather):
+//   phase 1  s_i = a_i . x_c(i);  b_i s_i -> shared memory
+//   phase 2  one thread per point sums its run in order, z_p = Vinv_p t_p
+//   phase 3  w_i = b_i . z_p, written at the row's CAMERA-SORTED position (w_cs[inv_cs[i]]) so that
+//            pass 2 is a pure stream; the 40 MB/5M-row w array stays L2 resident between the passes.
 // BACKSUB: phase 2 instead does v_p = Vinv_p (g_p - t_p) -> vp; part[2*chunk] = v_p.g_p, [+1] = |v_p|^2
-#define MV_CH 256
-template <typename JT, bool BACKSUB>
-__global__ void __launch_bounds__(MV_CH)
+#define MV_T 256
+template <typename JT> struct MvCfg;
+#ifndef MV_RPT_F32
+#define MV_RPT_F32 2
+#endif
+template <> struct MvCfg<float>  { static constexpr int RPT = MV_RPT_F32; static constexpr int MINB = MV_RPT_F32 == 1 ? 5 : 3; };
+template <> struct MvCfg<double> { static constexpr int RPT = 2; static constexpr int MINB = 3; };
+
+template <typename JT, bool BACKSUB, bool WSCAT>
+__global__ void __launch_bounds__(MV_T, MvCfg<JT>::MINB)
 k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restrict__ chunk_row,
           const int32_t* __restrict__ chunk_pt, const int32_t* __restrict__ pt_ptr,
           const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
-          const JT* __restrict__ Jc_ps, const JT* __restrict__ Jp_ps, const double* __restrict__ Vinv,
-          const double* __restrict__ x, double* __restrict__ w_ps, const double* __restrict__ gp,
-          double* __restrict__ vp, double* __restrict__ part) {
-  __shared__ double sb[3][MV_CH];
-  __shared__ double sz[3][MV_CH];
+          const int32_t* __restrict__ inv_cs, const JT* __restrict__ Jc_ps, const JT* __restrict__ Jp_ps,
+          const double* __restrict__ Vinv, const double* __restrict__ x, double* __restrict__ w_cs,
+          const double* __restrict__ gp, double* __restrict__ vp, double* __restrict__ part) {
+  constexpr int RPT = MvCfg<JT>::RPT;
+  constexpr int CAP = MV_T * RPT;
+  __shared__ double sb[3][CAP];
+  __shared__ double sz[3][MV_T];
   __shared__ double sred[3 * 32];
   if (!BACKSUB && st->pcg_done) return;
   const int ch = blockIdx.x, tid = threadIdx.x;
   const int r0 = chunk_row[ch], nrows = chunk_row[ch + 1] - r0;
   const int p0 = chunk_pt[ch], npts = chunk_pt[ch + 1] - p0;
   double acc[2] = {0.0, 0.0};
-  if (nrows <= MV_CH) {
-    double b[3] = {0, 0, 0};
-    const size_t row = (size_t)r0 + tid;
-    // issue every global load of the CTA's lifetime up front (one DRAM round trip + the x gather)
+  if (nrows <= CAP) {
     double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
-    int beg = 0, end = 0, lp = 0;
+    int beg = 0, end = 0;
     if (tid < npts) {
       const int p = p0 + tid;
       beg = __ldg(pt_ptr + p) - r0;
@@ -41,19 +50,34 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
       for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
       if (BACKSUB) { g0 = gp[3 * (size_t)p]; g1 = gp[3 * (size_t)p + 1]; g2 = gp[3 * (size_t)p + 2]; }
     }
-    if (tid < nrows) {
-      double a[8];
-      const int cam = __ldg(cam_ps + row);
-      if (!BACKSUB) lp = __ldg(pt_ps + row) - p0;
+    JT a[RPT][8], b[RPT][3];  // kept in storage precision until used (register budget)
+    int cam[RPT], lp[RPT], dst[RPT];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) a[k] = jget<JT>(Jc_ps, N, k, row);
+    for (int j = 0; j < RPT; ++j) {
+      const int i = tid + j * MV_T;
+      const size_t row = (size_t)r0 + i;
+      cam[j] = 0; lp[j] = 0; dst[j] = 0;
+      if (i < nrows) {
+        cam[j] = __ldg(cam_ps + row);
+        if (!BACKSUB) { lp[j] = __ldg(pt_ps + row) - p0; dst[j] = WSCAT ? __ldg(inv_cs + row) : (int)row; }
 #pragma unroll
-      for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, row);
-      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)cam);
-      const double2 x0 = xc[0], x1 = xc[1], x2 = xc[2], x3 = xc[3];
-      const double s = a[0] * x0.x + a[1] * x0.y + a[2] * x1.x + a[3] * x1.y + a[4] * x2.x +
-                       a[5] * x2.y + a[6] * x3.x + a[7] * x3.y;
-      sb[0][tid] = b[0] * s; sb[1][tid] = b[1] * s; sb[2][tid] = b[2] * s;
+        for (int k = 0; k < 8; ++k) a[j][k] = __ldg(Jc_ps + (size_t)k * N + row);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) b[j][k] = __ldg(Jp_ps + (size_t)k * N + row);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < RPT; ++j) {
+      const int i = tid + j * MV_T;
+      if (i < nrows) {
+        double xv[8];
+        ld256(x + 8 * (size_t)cam[j], xv);
+        ld256(x + 8 * (size_t)cam[j] + 4, xv + 4);
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s += (double)a[j][k] * xv[k];
+        sb[0][i] = (double)b[j][0] * s; sb[1][i] = (double)b[j][1] * s; sb[2][i] = (double)b[j][2] * s;
+      }
     }
     __syncthreads();
     if (tid < npts) {
@@ -76,13 +100,18 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
     }
     if (!BACKSUB) {
       __syncthreads();
-      if (tid < nrows) w_ps[row] = b[0] * sz[0][lp] + b[1] * sz[1][lp] + b[2] * sz[2][lp];
+#pragma unroll
+      for (int j = 0; j < RPT; ++j) {
+        const int i = tid + j * MV_T;
+        if (i < nrows)
+          w_cs[dst[j]] = (double)b[j][0] * sz[0][lp[j]] + (double)b[j][1] * sz[1][lp[j]] + (double)b[j][2] * sz[2][lp[j]];
+      }
     }
   } else {
-    // a single point with more than MV_CH observations: CTA-wide loop + ordered reduction
+    // a single point with more than CAP observations: CTA-wide loop + ordered reduction
     const int p = p0;
     double t[3] = {0, 0, 0};
-    for (int i = tid; i < nrows; i += MV_CH) {
+    for (int i = tid; i < nrows; i += MV_T) {
       const size_t row = (size_t)r0 + i;
       const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + row));
       double s = 0.0;
@@ -116,10 +145,10 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
       const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
       const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
       const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
-      for (int i = tid; i < nrows; i += MV_CH) {
+      for (int i = tid; i < nrows; i += MV_T) {
         const size_t row = (size_t)r0 + i;
-        w_ps[row] = jget<JT>(Jp_ps, N, 0, row) * z0 + jget<JT>(Jp_ps, N, 1, row) * z1 +
-                    jget<JT>(Jp_ps, N, 2, row) * z2;
+        w_cs[WSCAT ? (size_t)__ldg(inv_cs + row) : row] = jget<JT>(Jp_ps, N, 0, row) * z0 + jget<JT>(Jp_ps, N, 1, row) * z1 +
+                                    jget<JT>(Jp_ps, N, 2, row) * z2;
       }
     }
   }
@@ -133,23 +162,24 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
 }
 
 // ---------------------------------------------------------------- K3b pass 2 (camera side)
-// ypart_c = - sum_{j in cs run of c} a_j w[perm[j]].  FUSE (single rank): y_c = (U_c + mu I) x_c +
+// ypart_c = - sum_{j in cs run of c} a_j w_cs[j]  (pure stream).  FUSE (single rank): y_c = (U_c + mu I) x_c +
 // ypart_c and part[c] = x_c . y_c, so no separate vector kernel is needed.
-template <typename JT, bool FUSE>
+template <typename JT, bool FUSE, bool WGATHER>
 __global__ void __launch_bounds__(256)
 k_mv_cam(const SolverState* __restrict__ st, const int32_t* __restrict__ cam_ptr,
          const int32_t* __restrict__ perm_cs, const JT* __restrict__ Jc_cs,
-         const double* __restrict__ w_ps, const double* __restrict__ U, const double* __restrict__ xin,
+         const double* __restrict__ w_cs, const double* __restrict__ U, const double* __restrict__ xin,
          double* __restrict__ y, double* __restrict__ part) {
   __shared__ double sm[8 * 32];
   if (st->pcg_done) return;
   const int c = blockIdx.x;
   const int beg = cam_ptr[c], end = cam_ptr[c + 1];
   double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 4
   for (int j = beg + threadIdx.x; j < end; j += blockDim.x) {
     double a[8];
     load8<JT>(Jc_cs + 8 * (size_t)j, a);
-    const double w = __ldg(w_ps + __ldg(perm_cs + j));
+    const double w = WGATHER ? __ldg(w_cs + __ldg(perm_cs + j)) : __ldg(w_cs + j);
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] -= a[k] * w;
   }
@@ -230,9 +260,19 @@ k_pcg_vec(int C, int it, SolverState* __restrict__ st, const double* __restrict_
           int maxiter) {
   __shared__ double sm[32];
   if (st->pcg_done) return;
-  const double gamma = cta_sum_strided(part_gr, C, 2, sm);
-  const double rr = cta_sum_strided(part_gr + 1, C, 2, sm);
-  const double delta = cta_sum_strided(part_d, C, 1, sm);
+  __shared__ double sm3[3 * 32];
+  __shared__ double bc3[3];
+  double v3[3] = {0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    v3[0] += part_gr[2 * (size_t)i];
+    v3[1] += part_gr[2 * (size_t)i + 1];
+    v3[2] += part_d[i];
+  }
+  block_sum<3>(v3, sm3);
+  if (threadIdx.x == 0) { bc3[0] = v3[0]; bc3[1] = v3[1]; bc3[2] = v3[2]; }
+  __syncthreads();
+  const double gamma = bc3[0], rr = bc3[1], delta = bc3[2];
+  (void)sm;
   const bool conv = rr <= rtol * rtol * st->rhs2;
   const bool bad = !(rr == rr) || !(delta == delta);
   const bool stop = conv || bad || it >= maxiter;
