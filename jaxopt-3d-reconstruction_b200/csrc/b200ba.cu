@@ -53,22 +53,23 @@ struct b200ba_plan {
   int C = 0, P = 0;
   int64_t N = 0;
   int jac_f32 = 0;
-  int wscatter = 0;  // matvec pass 1 writes w at camera-sorted positions (else pass 2 gathers)
   size_t jsz = 8;
-  // structure (device)
-  int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // ps rows
-  int32_t *perm_cs = nullptr, *inv_cs = nullptr;                     // cs<->ps
-  int32_t *pt_ptr = nullptr, *cam_ptr = nullptr;
-  int32_t *chunk_row = nullptr, *chunk_pt = nullptr;  // matvec pass-1 chunks of whole points
-  int nchunks = 0;
+  // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
+  int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
+  int32_t *posB = nullptr;                                           // A row -> B position
+  int32_t *pt_ptr = nullptr, *runptr = nullptr;                      // A: CSR by point; B: nPB*C+1 run offsets
+  int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
+  int nchunks = 0, nPB = 1, block_rows = 0, max_cam_rows = 0, stash_rows = 0;
+  size_t stash_bytes = 0;
   double2* obs_ps = nullptr;
   // linearisation
-  void *Jc_ps = nullptr, *Jp_ps = nullptr, *Jc_cs = nullptr;
-  double *r_ps = nullptr, *r_cs = nullptr, *w_ps = nullptr, *beta_ps = nullptr, *w_cs = nullptr;
+  void *Jp_ps = nullptr, *Jc_B = nullptr;
+  double *r_ps = nullptr, *r_B = nullptr, *w_B = nullptr, *beta_B = nullptr, *sig = nullptr, *omg = nullptr;
   double *tab = nullptr, *tab_trial = nullptr;
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
-  double *x = nullptr, *r = nullptr, *z = nullptr, *pv = nullptr, *sv = nullptr, *y = nullptr, *vp = nullptr;
+  PcgVecs v = {};
+  double *y = nullptr, *vp = nullptr;
   double *cam_trial = nullptr, *pts_trial = nullptr;
   double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
   SolverState* st = nullptr;
@@ -126,6 +127,27 @@ __global__ void k_make_keys(int64_t N, const int32_t* __restrict__ cam, const in
   keys[i] = which == 0 ? (int64_t)pt[i] * mul_a + cam[i] : (int64_t)cam[i] * mul_a + pt[i];
   vals[i] = (int32_t)i;
 }
+// B-order key of an A row: (point block of the row's point) * C + camera; the point block is the
+// A position of the point's first row divided by block_rows (blocks are contiguous point ranges).
+__global__ void k_make_keys_B(int64_t N, int C, int block_rows, const int32_t* __restrict__ cam_ps,
+                              const int32_t* __restrict__ pt_ps, const int32_t* __restrict__ pt_ptr,
+                              int64_t* __restrict__ keys, int32_t* __restrict__ vals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  keys[i] = (int64_t)(pt_ptr[pt_ps[i]] / block_rows) * C + cam_ps[i];
+  vals[i] = (int32_t)i;
+}
+__global__ void k_segment_ptr64(int64_t nseg, int64_t N, const int64_t* __restrict__ key_sorted,
+                                int32_t* __restrict__ ptr) {
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s > nseg) return;
+  int64_t lo = 0, hi = N;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (key_sorted[mid] < s) lo = mid + 1; else hi = mid;
+  }
+  ptr[s] = (int32_t)lo;
+}
 __global__ void k_gather_i32(int64_t N, const int32_t* __restrict__ idx, const int32_t* __restrict__ src,
                              int32_t* __restrict__ dst) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -173,30 +195,40 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   cudaStream_t s = (cudaStream_t)stream_;
   b200ba_plan* p = new b200ba_plan();
   p->C = C; p->P = P; p->N = N; p->jac_f32 = jac_f32 ? 1 : 0; p->jsz = jac_f32 ? 4 : 8;
-  { const char* e = getenv("B200BA_WSCATTER"); p->wscatter = e ? atoi(e) : 0; }
+  // point blocks: ~160 rows per camera per block (long coalesced runs on the camera side), window of
+  // the exchange arrays (16 B/row) a few MB so it stays in L2; at most MAXPB blocks
+  {
+    int64_t br = 160LL * C;
+    if (br < 65536) br = 65536;
+    if (br > (1 << 20)) br = 1 << 20;
+    if (const char* e = getenv("B200BA_BLOCK_ROWS")) { const long v = atol(e); if (v > 0) br = v; }
+    if (N > br * MAXPB) br = (N + MAXPB - 1) / MAXPB;
+    p->block_rows = (int)br;
+    p->nPB = N ? (int)((N - 1) / br + 1) : 1;
+  }
+  const size_t nruns = (size_t)p->nPB * C;
   int rc = 0;
 #define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
-  A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(perm_cs, N) A(inv_cs, N)
-  A(pt_ptr, P + 1) A(cam_ptr, C + 1) A(obs_ps, N)
-  A(r_ps, N) A(r_cs, N) A(w_ps, N) A(beta_ps, N) A(w_cs, N)
+  A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(posB, N)
+  A(pt_ptr, P + 1) A(runptr, nruns + 1) A(obs_ps, N)
+  A(r_ps, N) A(r_B, N) A(w_B, N) A(beta_B, N) A(sig, N) A(omg, N)
   A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
-  A(x, (size_t)C * 8) A(r, (size_t)C * 8) A(z, (size_t)C * 8) A(pv, (size_t)C * 8) A(sv, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
+  A(v.x, (size_t)C * 8) A(v.r, (size_t)C * 8) A(v.u, (size_t)C * 8) A(v.w, (size_t)C * 8) A(v.z, (size_t)C * 8)
+  A(v.q, (size_t)C * 8) A(v.s, (size_t)C * 8) A(v.p, (size_t)C * 8) A(v.m, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
   A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts_trial, (size_t)P * 3)
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
   p->lin_scal = p->gc + (size_t)C * 8;
   p->nblkN = (int)cdiv(N, RJ_THREADS); p->nblkP = (int)cdiv(P, 256);
-  A(part, 2 * (size_t)C + 16) A(part2, 2 * (size_t)C + 16)
+  A(part, 4 * (size_t)C + 16) A(part2, 4 * (size_t)C + 16)
   A(scal, 32) A(st, 1)
 #undef A
   {
     void* q = nullptr;
-    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_ps"); }
-    p->allocs.push_back(q); p->Jc_ps = q;
-    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_cs"); }
-    p->allocs.push_back(q); p->Jc_cs = q;
+    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_B"); }
+    p->allocs.push_back(q); p->Jc_B = q;
     if (cudaMalloc(&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
     p->allocs.push_back(q); p->Jp_ps = q;
   }
@@ -209,10 +241,10 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   cudaMemsetAsync(p->vp, 0, (size_t)(P ? P : 1) * 3 * sizeof(double), s);
 
   if (N > 0) {
-    // validate, then sort rows by (point, camera) and by (camera, point) with CUB radix sort
+    // validate, then sort rows by (point, camera) [A] and by (point block, camera, point) [B] with CUB radix sort
     int* bad = nullptr;
     int64_t *keys = nullptr, *keys2 = nullptr;
-    int32_t *vals = nullptr, *tmp_i = nullptr;
+    int32_t *vals = nullptr, *permBA = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
     cudaMalloc(&bad, sizeof(int));
@@ -225,36 +257,64 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaFree(bad);
     if (bad_h) { b200ba_plan_destroy(p); FAIL(B200BA_EINVAL, "plan_create: index out of range"); }
     cudaMalloc(&keys, N * sizeof(int64_t)); cudaMalloc(&keys2, N * sizeof(int64_t));
-    cudaMalloc(&vals, N * sizeof(int32_t)); cudaMalloc(&tmp_i, N * sizeof(int32_t));
+    cudaMalloc(&vals, N * sizeof(int32_t)); cudaMalloc(&permBA, N * sizeof(int32_t));
     const int nb = bits_for((int64_t)P * C + C);
+    const int nbB = bits_for((int64_t)nruns + 1);
     cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
     cudaMalloc(&tmp, tmp_bytes);
-    // ps order
+    // A order
     LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, cam_idx, pt_idx, (int64_t)C, 0, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
     LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, cam_idx, p->cam_ps);
     LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, pt_idx, p->pt_ps);
     LAUNCH(k_segment_ptr, cdiv(P + 1, 256), 256, 0, s, P, N, p->pt_ps, p->pt_ptr);
-    // cs order (indices into ps rows)
-    LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, p->cam_ps, p->pt_ps, (int64_t)P, 1, keys, vals);
-    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->perm_cs, (int)N, 0, nb, s);
-    LAUNCH(k_invert_perm, cdiv(N, 256), 256, 0, s, N, p->perm_cs, p->inv_cs);
-    LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->perm_cs, p->cam_ps, tmp_i);
-    LAUNCH(k_segment_ptr, cdiv(C + 1, 256), 256, 0, s, C, N, tmp_i, p->cam_ptr);
+    // B order: stable sort of the A rows by (point block, camera) keeps the point order inside a run
+    LAUNCH(k_make_keys_B, cdiv(N, 256), 256, 0, s, N, C, p->block_rows, p->cam_ps, p->pt_ps, p->pt_ptr, keys, vals);
+    cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, permBA, (int)N, 0, nbB, s);
+    LAUNCH(k_invert_perm, cdiv(N, 256), 256, 0, s, N, permBA, p->posB);
+    LAUNCH(k_segment_ptr64, cdiv((int64_t)nruns + 1, 256), 256, 0, s, (int64_t)nruns, N, keys2, p->runptr);
     cudaError_t e = cudaStreamSynchronize(s);
-    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(tmp_i); cudaFree(tmp);
+    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(permBA); cudaFree(tmp);
     if (e != cudaSuccess || (e = cudaGetLastError()) != cudaSuccess) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, std::string("plan_create: ") + cudaGetErrorString(e));
     }
   } else {
     cudaMemsetAsync(p->pt_ptr, 0, (P + 1) * sizeof(int32_t), s);
-    cudaMemsetAsync(p->cam_ptr, 0, (C + 1) * sizeof(int32_t), s);
+    cudaMemsetAsync(p->runptr, 0, (nruns + 1) * sizeof(int32_t), s);
     cudaStreamSynchronize(s);
   }
   {
-    // greedy chunks of whole points with <= cap rows and <= MV_T points (a point with more rows is its own chunk)
-    const int cap = MV_T * (p->jac_f32 ? MvCfg<float>::RPT : MvCfg<double>::RPT);
+    // rows per camera -> size of the shared-memory row stash of the fused camera kernel
+    std::vector<int32_t> hrun(nruns + 1);
+    if (cudaMemcpy(hrun.data(), p->runptr, (nruns + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, "plan_create: runptr readback");
+    }
+    std::vector<int64_t> rows(C, 0);
+    for (int r = 0; r < p->nPB; ++r)
+      for (int c = 0; c < C; ++c) rows[c] += hrun[(size_t)r * C + c + 1] - hrun[(size_t)r * C + c];
+    int64_t mx = 0;
+    for (int c = 0; c < C; ++c) mx = rows[c] > mx ? rows[c] : mx;
+    p->max_cam_rows = (int)mx;
+    size_t cap = 96 * 1024;
+    if (const char* e = getenv("B200BA_STASH_KB")) cap = (size_t)atol(e) * 1024;
+    const size_t row_bytes = 8 * p->jsz;
+    size_t sr = cap / row_bytes;
+    if ((size_t)mx < sr) sr = (size_t)mx;
+    sr = (sr + 3) & ~(size_t)3;
+    p->stash_rows = (int)sr;
+    p->stash_bytes = sr * row_bytes;
+    cudaError_t e1 = cudaFuncSetAttribute(k_cs<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
+    cudaError_t e2 = cudaFuncSetAttribute(k_cs<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
+    if (e1 != cudaSuccess || e2 != cudaSuccess || p->stash_bytes > 100 * 1024) {
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, "plan_create: shared-memory stash configuration");
+    }
+  }
+  {
+    // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk)
+    const int cap = PS_T * PS_RPT;
     std::vector<int32_t> hptr((size_t)P + 1), crow, cpt;
     if (cudaMemcpy(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
       b200ba_plan_destroy(p);
@@ -265,7 +325,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int cur = 0;
     for (int q = 0; q < P; ++q) {
       const int d = hptr[q + 1] - hptr[q];
-      if ((cur > 0 && cur + d > cap) || q - cpt.back() >= MV_T) {
+      if ((cur > 0 && cur + d > cap) || q - cpt.back() >= PS_T) {
         crow.push_back(hptr[q]);
         cpt.push_back(q);
         cur = 0;
@@ -360,6 +420,12 @@ static int allreduce(b200ba_plan* p, double* buf, size_t n, ncclRedOp_t op, cuda
   return 0;
 }
 
+static int read_state(b200ba_plan* p, cudaStream_t s) {
+  CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
 template <typename JT>
 struct Ops {
   static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
@@ -369,13 +435,13 @@ struct Ops {
     PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
     if (N) {
       PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), p->nblkN, RJ_THREADS, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
-             p->inv_cs, p->r_ps, (JT*)p->Jc_ps, (JT*)p->Jp_ps, (JT*)p->Jc_cs, p->r_cs, p->partN);
+             p->posB, p->r_ps, (JT*)p->Jp_ps, (JT*)p->Jc_B, p->r_B, p->partN);
     }
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
     if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
-    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, p->r_cs, nullptr, nullptr, nullptr,
+    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, C, p->nPB, p->runptr, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
            p->U, p->gc);
     int rc;
     if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
@@ -386,70 +452,107 @@ struct Ops {
     return 0;
   }
 
-  // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start
-  static int prepare(b200ba_plan* p, cudaStream_t s) {
-    const int C = p->C, P = p->P;
-    if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, (const JT*)p->Jp_ps, p->V,
-                  p->gp, p->Vinv, p->w_ps, p->beta_ps);
-    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, p->cam_ptr, (const JT*)p->Jc_cs, nullptr, p->perm_cs, p->w_ps,
-           p->beta_ps, p->Sd, p->rhs_part);
-    int rc;
-    if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
-    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
-            p->Minv, p->rhs, p->x, p->r, p->z, p->pv, p->sv, p->part2);
-    PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
-    CK(cudaGetLastError());
-    return matvec(p, p->z, s);  // w = S u, delta partials
+  // camera-side kernel (see ba_pcg.cuh): flags select matvec tail / vector update / matvec head
+  static void cs(b200ba_plan* p, int cls, int flags, const double* vin, cudaStream_t s) {
+    const size_t smem = (flags & CS_C) && (flags & CS_A) ? p->stash_bytes : 0;
+    PLAUNCH(p, cls, (k_cs<JT>), p->C, CS_T, smem, s, p->C, p->nPB, flags, smem ? p->stash_rows : 0, p->st, p->runptr,
+            (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin, p->y, p->v, p->part2);
   }
-
-  // y = S xin (xin: C x 8 device vector); part[c] = xin_c . y_c
-  static int matvec(b200ba_plan* p, const double* xin, cudaStream_t s) {
-    const int C = p->C;
-#define MV_ARGS (size_t)p->N, p->st, p->chunk_row, p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, p->inv_cs, (const JT*)p->Jc_ps, \
-                (const JT*)p->Jp_ps, p->Vinv, xin, p->w_cs, nullptr, nullptr, nullptr
-#define CAM_ARGS p->st, p->cam_ptr, p->perm_cs, (const JT*)p->Jc_cs, p->w_cs, p->U, xin, p->y, p->part
-    if (p->N) {
-      if (p->wscatter) PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false, true>), p->nchunks, MV_T, 0, s, MV_ARGS);
-      else PLAUNCH(p, PC_MV_PT, (k_mv_rows<JT, false, false>), p->nchunks, MV_T, 0, s, MV_ARGS);
-    }
+  // point-side kernel: omega from sigma (and the PCG scalars of iteration `it` when do_scalars)
+  static void ps(b200ba_plan* p, int it, int do_scalars, double rtol, int maxiter, cudaStream_t s) {
+    PLAUNCH(p, PC_MV_PT, (k_ps<JT, false>), p->nchunks > 0 ? p->nchunks : 1, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, it,
+            do_scalars, rtol, maxiter, p->st, p->part2, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB,
+            (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr);
+  }
+  // matvec tail + vector update + next matvec head; multi-rank: partial sums are all-reduced in between
+  static int cs_step(b200ba_plan* p, int upd_flag, const double* vin, cudaStream_t s) {
     if (p->nranks == 1) {
-      if (p->wscatter) PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true, false>), C, 256, 0, s, CAM_ARGS);
-      else PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, true, true>), C, 256, 0, s, CAM_ARGS);
+      cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
     } else {
-      if (p->wscatter) PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false, false>), C, 256, 0, s, CAM_ARGS);
-      else PLAUNCH(p, PC_MV_CAM, (k_mv_cam<JT, false, true>), C, 256, 0, s, CAM_ARGS);
+      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, nullptr, s);
       int rc;
-      if ((rc = allreduce(p, p->y, (size_t)C * 8, ncclSum, s))) return rc;
-      PLAUNCH(p, PC_PCG_VEC, k_pcg_y, cdiv(C, 128), 128, 0, s, C, p->st, p->U, xin, p->y, p->part);
+      if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
+      cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | upd_flag | CS_A, vin, s);
     }
-#undef MV_ARGS
-#undef CAM_ARGS
     return 0;
   }
 
-  // one Chronopoulos-Gear PCG iteration: vector kernel (alpha/beta, x/r/u/p/s update) + matvec of u
-  static int pcg_iteration(b200ba_plan* p, int it, double rtol, int maxiter, cudaStream_t s) {
-    const int C = p->C;
-    PLAUNCH(p, PC_PCG_VEC, k_pcg_vec, cdiv(8 * (int64_t)C, 256), 256, 0, s, C, it, p->st, p->part2, p->part, p->Minv, p->y,
-            p->x, p->r, p->z, p->pv, p->sv, p->part2, rtol, maxiter);
-    return matvec(p, p->z, s);
+  // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start:
+  // x = 0, r = rhs, u = Minv r, w = S u, m = Minv w, sigma = rows . m
+  static int prepare(b200ba_plan* p, cudaStream_t s) {
+    const int C = p->C, P = p->P;
+    if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, p->posB,
+                  (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->w_B, p->beta_B);
+    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, C, p->nPB, p->runptr, (const JT*)p->Jc_B, nullptr, p->w_B,
+           p->beta_B, p->Sd, p->rhs_part);
+    int rc;
+    if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
+    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
+            p->Minv, p->rhs, p->v.x, p->v.r, p->v.u, p->v.p, p->v.s, p->part2);
+    PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
+    cs(p, PC_MV_CAM, CS_A, p->v.u, s);
+    ps(p, 0, 0, 0.0, 0, s);
+    if ((rc = cs_step(p, CS_INIT, p->v.u, s))) return rc;
+    CK(cudaGetLastError());
+    return 0;
   }
 
-  // run PCG to convergence; device-side flag, host polls every `chunk` iterations
+  // y = S xin (xin: C x 8 device vector) — building block for tests; clobbers sigma/omega
+  static int matvec(b200ba_plan* p, const double* xin, cudaStream_t s) {
+    cs(p, PC_MV_CAM, CS_A | CS_IGNORE_DONE, xin, s);
+    ps(p, 0, 2, 0.0, 0, s);
+    if (p->nranks == 1) {
+      cs(p, PC_MV_CAM, CS_C | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
+    } else {
+      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y | CS_IGNORE_DONE, nullptr, s);
+      int rc;
+      if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
+      cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
+    }
+    return 0;
+  }
+
+  // one pipelined PCG iteration: point kernel (scalars of iteration `it` + omega) then camera kernel
+  static int pcg_iteration(b200ba_plan* p, int it, double rtol, int maxiter, cudaStream_t s) {
+    ps(p, it, 1, rtol, maxiter, s);
+    return cs_step(p, CS_ITER, p->v.m, s);
+  }
+
+  // run PCG to convergence; device-side flag, host polls every `chunk` iterations.  When the recurrence
+  // residual says "converged" (or stagnates) the TRUE residual rhs - S x is formed by one plain matvec and
+  // checked on the device; if it is not below rtol the method restarts from x with r = true residual.
   static int pcg_solve(b200ba_plan* p, double rtol, int maxiter, int fixed_iters, int* iters_out, cudaStream_t s) {
     int rc;
-    int done = 0, launched = 0;
+    int launched = 0, restarts = 0;
     const int limit = fixed_iters > 0 ? fixed_iters : maxiter;
     const double rt = fixed_iters > 0 ? 0.0 : rtol;
     int chunk = fixed_iters > 0 ? fixed_iters : 16;
-    while (!done && launched <= limit) {
-      const int n = (limit + 1 - launched) < chunk ? (limit + 1 - launched) : chunk;
-      for (int k = 0; k < n; ++k)
-        if ((rc = pcg_iteration(p, launched + k, rt, limit, s))) return rc;
-      launched += n;
-      CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
-      CK(cudaStreamSynchronize(s));
-      done = p->st_host->pcg_done;
+    for (;;) {
+      int done = 0;
+      while (!done && launched <= limit) {
+        const int n = (limit + 1 - launched) < chunk ? (limit + 1 - launched) : chunk;
+        for (int k = 0; k < n; ++k)
+          if ((rc = pcg_iteration(p, launched + k, rt, limit, s))) return rc;
+        launched += n;
+        if ((rc = read_state(p, s))) return rc;
+        done = p->st_host->pcg_done;
+        chunk = 8;
+      }
+      if (fixed_iters > 0 || !done) break;
+      const int stop = p->st_host->pcg_stop;
+      if (stop == 1 || stop == 2 || p->st_host->rhs2 == 0.0) break;  // maxiter / NaN / zero rhs
+      if (restarts >= 6) { p->st_host->status |= 4; break; }
+      launched = p->st_host->pcg_iters;
+      // verify: y = S x, r = rhs - y, u = Minv r, |r|^2 -> done (true residual small) or restart state
+      if ((rc = matvec(p, p->v.x, s))) return rc;
+      PLAUNCH(p, PC_PCG_VEC, k_pcg_true_residual, cdiv(8 * (int64_t)p->C, 256), 256, 0, s, p->C, p->rhs, p->y, p->Minv, p->v.r, p->v.u, p->part2);
+      PLAUNCH(p, PC_PCG_VEC, k_pcg_verify, 1, 256, 0, s, p->C, p->st, p->part2, rtol);
+      cs(p, PC_MV_CAM, CS_A, p->v.u, s);
+      ps(p, 0, 0, 0.0, 0, s);
+      if ((rc = cs_step(p, CS_INIT, p->v.u, s))) return rc;
+      if ((rc = read_state(p, s))) return rc;
+      if (p->st_host->pcg_done) break;
+      ++restarts;
       chunk = 8;
     }
     if (iters_out) *iters_out = p->st_host->pcg_iters;
@@ -457,11 +560,10 @@ struct Ops {
   }
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
-    const int P = p->P;
-    if (p->N) PLAUNCH(p, PC_BACKSUB, (k_mv_rows<JT, true, false>), p->nchunks, MV_T, 0, s, (size_t)p->N, p->st, p->chunk_row,
-                      p->chunk_pt, p->pt_ptr, p->cam_ps, p->pt_ps, p->inv_cs, (const JT*)p->Jc_ps, (const JT*)p->Jp_ps,
-                      p->Vinv, p->x, nullptr, p->gp, p->vp, p->partN);
-    (void)P;
+    cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, p->v.x, s);
+    if (p->N) PLAUNCH(p, PC_BACKSUB, (k_ps<JT, true>), p->nchunks, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, 0, 0, 0.0, 0, p->st,
+                      nullptr, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB, (const JT*)p->Jp_ps, p->Vinv, p->sig,
+                      nullptr, p->gp, p->vp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;
   }
@@ -471,7 +573,7 @@ struct Ops {
     PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
     if (p->N)
       PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->nblkN, RJ_THREADS, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
-             inv_w2, p->inv_cs, nullptr, nullptr, nullptr, nullptr, nullptr, p->partN);
+             inv_w2, p->posB, nullptr, nullptr, nullptr, nullptr, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
     return 0;
   }
@@ -489,11 +591,6 @@ __global__ void k_pack_decide(double* scal) {
 
 #define DISPATCH(p, fn, ...) ((p)->jac_f32 ? Ops<float>::fn(__VA_ARGS__) : Ops<double>::fn(__VA_ARGS__))
 
-static int read_state(b200ba_plan* p, cudaStream_t s) {
-  CK(cudaMemcpyAsync(p->st_host, p->st, sizeof(SolverState), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
-  return 0;
-}
 
 extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
                                 double inv_w2, double* U, double* gc, double* V, double* gp,
@@ -527,10 +624,10 @@ extern "C" int b200ba_residual_jacobian(b200ba_plan* p, const double* cam8, cons
   if (N) {
     if (r) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->r_ps, (size_t)0, 1, r);
     if (p->jac_f32) {
-      if (Jc) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jc_ps, (size_t)N, 8, Jc);
+      if (Jc) LAUNCH((k_unpermute_jc<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->posB, (const float*)p->Jc_B, Jc);
       if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, (size_t)N, 3, Jp);
     } else {
-      if (Jc) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jc_ps, (size_t)N, 8, Jc);
+      if (Jc) LAUNCH((k_unpermute_jc<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->posB, (const double*)p->Jc_B, Jc);
       if (Jp) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->Jp_ps, (size_t)N, 3, Jp);
     }
   }
@@ -563,11 +660,10 @@ extern "C" int b200ba_schur_prepare(b200ba_plan* p, double mu, double* rhs, void
 extern "C" int b200ba_schur_matvec(b200ba_plan* p, const double* x, double* y, void* stream_) {
   if (!p || !x || !y) FAIL(B200BA_EINVAL, "null");
   cudaStream_t s = (cudaStream_t)stream_;
-  // uses pv as the input vector; the PCG state is clobbered (call schur_prepare again before a solve)
-  CK(cudaMemcpyAsync(p->z, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
-  LAUNCH(k_clear_done, 1, 1, 0, s, p->st);
+  // the PCG state is clobbered (call schur_prepare again before a solve)
+  CK(cudaMemcpyAsync(p->v.q, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   int rc;
-  if ((rc = DISPATCH(p, matvec, p, p->z, s))) return rc;
+  if ((rc = DISPATCH(p, matvec, p, p->v.q, s))) return rc;
   CK(cudaMemcpyAsync(y, p->y, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return B200BA_OK;
@@ -580,7 +676,7 @@ extern "C" int b200ba_schur_solve(b200ba_plan* p, double rtol, int maxiter, doub
   int rc;
   if ((rc = DISPATCH(p, pcg_solve, p, rtol, maxiter, 0, iters_host, s))) return rc;
   if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-  if (vc) CK(cudaMemcpyAsync(vc, p->x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  if (vc) CK(cudaMemcpyAsync(vc, p->v.x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   if (vp) CK(cudaMemcpyAsync(vp, p->vp, (size_t)p->P * 3 * 8, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return B200BA_OK;
@@ -635,7 +731,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
     res->n_pcg_iters_total += pcg_iters;
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->x, p->gc, p->cam_trial, p->part);
+    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->v.x, p->gc, p->cam_trial, p->part);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
     if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
     if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts_trial, inv_w2, p->scal + 8, s))) return rc;

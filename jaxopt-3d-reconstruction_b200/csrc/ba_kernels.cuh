@@ -53,6 +53,69 @@ __device__ __forceinline__ void jput(JT* __restrict__ base, size_t N, int k, siz
   base[(size_t)k * N + i] = (JT)v;
 }
 
+// raw (storage-precision) 8-value row moves: global -> registers -> shared -> registers
+__device__ __forceinline__ void ldrow(const float* __restrict__ p, float* v) { ld256(p, v); }
+__device__ __forceinline__ void ldrow(const double* __restrict__ p, double* v) { ld256(p, v); ld256(p + 4, v + 4); }
+__device__ __forceinline__ void strow(float* p, const float* v) {
+  float4* q = reinterpret_cast<float4*>(p);
+  q[0] = make_float4(v[0], v[1], v[2], v[3]);
+  q[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void strow(double* p, const double* v) {
+  double2* q = reinterpret_cast<double2*>(p);
+  q[0] = make_double2(v[0], v[1]); q[1] = make_double2(v[2], v[3]);
+  q[2] = make_double2(v[4], v[5]); q[3] = make_double2(v[6], v[7]);
+}
+__device__ __forceinline__ void ldrow_shared(const float* p, float* v) {
+  const float4* q = reinterpret_cast<const float4*>(p);
+  const float4 a = q[0], b = q[1];
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void ldrow_shared(const double* p, double* v) {
+  const double2* q = reinterpret_cast<const double2*>(p);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { const double2 a = q[k]; v[2 * k] = a.x; v[2 * k + 1] = a.y; }
+}
+
+// Rows of one camera in B order = nPB runs [runptr[r*C+c], runptr[r*C+c+1]).  The CTA flattens them:
+// logical row l in [0, L) -> B position via the run prefix kept in shared memory (locate() scans
+// forward from the caller's previous run, l only grows).
+#define MAXPB 512
+struct CamRuns {
+  int beg[MAXPB];
+  int pre[MAXPB + 1];
+  __device__ __forceinline__ int load(int c, int C, int nPB, const int32_t* __restrict__ runptr) {
+    for (int r = threadIdx.x; r < nPB; r += blockDim.x) {
+      const int b = __ldg(runptr + (size_t)r * C + c);
+      beg[r] = b;
+      pre[r + 1] = __ldg(runptr + (size_t)r * C + c + 1) - b;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      const int lane = threadIdx.x;
+      int carry = 0;
+      for (int base = 0; base < nPB; base += 32) {
+        const int r = base + lane;
+        int v = r < nPB ? pre[r + 1] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, v, o);
+          if (lane >= o) v += t;
+        }
+        if (r < nPB) pre[r + 1] = carry + v;
+        carry += __shfl_sync(0xffffffffu, v, 31);
+      }
+      if (lane == 0) pre[0] = 0;
+    }
+    __syncthreads();
+    return pre[nPB];
+  }
+  __device__ __forceinline__ size_t locate(int l, int& r) const {
+    while (l >= pre[r + 1]) ++r;
+    return (size_t)beg[r] + (size_t)(l - pre[r]);
+  }
+};
+
 // ---------------------------------------------------------------- K0: camera tables
 __global__ void k_cam_table(int C, const double* __restrict__ cam8, const double* __restrict__ k3,
                             double* __restrict__ tab) {
@@ -65,18 +128,18 @@ __global__ void k_cam_table(int C, const double* __restrict__ cam8, const double
 // camera tables are fetched COOPERATIVELY: for each of the warp's 32 rows the whole warp issues one
 // coalesced 256 B load of that row's table into shared memory (row stride 33 doubles: conflict-free
 // per-lane reads afterwards) instead of 26 scattered 8 B loads per lane.
-// Writes r and the Jacobian row in ps order (SoA, coalesced) and the camera part again at the
-// row's cs position (64 B aligned scatter = whole sectors), which the camera-side reductions then
-// stream.  cost_part[block] = sum r^2 of the block.
+// Writes r and the point part of the Jacobian row in A order (SoA, coalesced) and the camera part at the
+// row's B position (32/64 B aligned scatter = whole sectors, inside the L2 window of the point block),
+// which the camera-side kernels then stream.  cost_part[block] = sum r^2 of the block.
 #define RJ_THREADS 128
 #define RJ_TSTRIDE 33
 template <typename JT, bool WITH_JAC>
 __global__ void __launch_bounds__(RJ_THREADS)
 k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
          const double2* __restrict__ obs_ps, const double* __restrict__ tab,
-         const double* __restrict__ pts, double inv_w2, const int32_t* __restrict__ inv_cs,
-         double* __restrict__ r_ps, JT* __restrict__ Jc_ps, JT* __restrict__ Jp_ps,
-         JT* __restrict__ Jc_cs, double* __restrict__ r_cs, double* __restrict__ cost_part) {
+         const double* __restrict__ pts, double inv_w2, const int32_t* __restrict__ posB,
+         double* __restrict__ r_ps, JT* __restrict__ Jp_ps,
+         JT* __restrict__ Jc_B, double* __restrict__ r_B, double* __restrict__ cost_part) {
   __shared__ double sm[32];
   __shared__ double stab[RJ_THREADS / 32][32][RJ_TSTRIDE];
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -105,12 +168,10 @@ k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restric
       jac_row(T, pr, X, Y, Z, 2.0 * dx * inv_w2, 2.0 * dy * inv_w2, a, b);
       r_ps[i] = r;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) jput<JT>(Jc_ps, (size_t)N, k, (size_t)i, a[k]);
-#pragma unroll
       for (int k = 0; k < 3; ++k) jput<JT>(Jp_ps, (size_t)N, k, (size_t)i, b[k]);
-      const int64_t j = __ldg(inv_cs + i);
-      store8<JT>(Jc_cs + 8 * j, a);
-      r_cs[j] = r;
+      const int64_t j = __ldg(posB + i);
+      store8<JT>(Jc_B + 8 * j, a);
+      r_B[j] = r;
     } else if (r_ps) {
       r_ps[i] = r;
     }
@@ -159,32 +220,33 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __
 }
 
 // ---------------------------------------------------------------- K2b: 8x8 camera blocks
-// One CTA per camera streams its cs rows.  Each thread keeps 36 + 8 fp64 accumulators; ordered
-// CTA reduction.  If beta != nullptr the rows are weighted: out = -sum beta_i a a^T and
+// One CTA per camera streams its B-order runs.  Each thread keeps 36 + 8 fp64 accumulators; ordered
+// CTA reduction.  If beta_B != nullptr the rows are weighted: out = -sum beta_i a a^T and
 // -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs); otherwise
 // U_c = sum a a^T and g_c = sum a r.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_cam_blocks(const int32_t* __restrict__ cam_ptr, const JT* __restrict__ Jc_cs,
-             const double* __restrict__ s_cs, const int32_t* __restrict__ perm_cs,
-             const double* __restrict__ w_ps, const double* __restrict__ beta_ps,
+k_cam_blocks(int C, int nPB, const int32_t* __restrict__ runptr, const JT* __restrict__ Jc_B,
+             const double* __restrict__ s_B, const double* __restrict__ w_B, const double* __restrict__ beta_B,
              double* __restrict__ U, double* __restrict__ gc) {
   __shared__ double sm[44 * 32];
+  __shared__ CamRuns runs;
   const int c = blockIdx.x;
-  const int beg = cam_ptr[c], end = cam_ptr[c + 1];
+  const int L = runs.load(c, C, nPB, runptr);
   double acc[44];
 #pragma unroll
   for (int k = 0; k < 44; ++k) acc[k] = 0.0;
-  for (int j = beg + threadIdx.x; j < end; j += blockDim.x) {
+  int rr = 0;
+  for (int l = threadIdx.x; l < L; l += blockDim.x) {
+    const size_t j = runs.locate(l, rr);
     double a[8];
-    load8<JT>(Jc_cs + 8 * (size_t)j, a);
+    load8<JT>(Jc_B + 8 * j, a);
     double s, wgt;
-    if (beta_ps) {
-      const int i = __ldg(perm_cs + j);
-      s = -__ldg(w_ps + i);
-      wgt = -__ldg(beta_ps + i);
+    if (beta_B) {
+      s = -__ldg(w_B + j);
+      wgt = -__ldg(beta_B + j);
     } else {
-      s = __ldg(s_cs + j);
+      s = __ldg(s_B + j);
       wgt = 1.0;
     }
     int t = 0;
@@ -192,7 +254,7 @@ k_cam_blocks(const int32_t* __restrict__ cam_ptr, const JT* __restrict__ Jc_cs,
     for (int k = 0; k < 8; ++k) {
       const double ak = a[k] * wgt;
 #pragma unroll
-      for (int l = k; l < 8; ++l) acc[t++] += ak * a[l];
+      for (int l2 = k; l2 < 8; ++l2) acc[t++] += ak * a[l2];
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[36 + k] += a[k] * s;
@@ -239,13 +301,14 @@ __device__ __forceinline__ void inv3_sym(const double* v, double mu, double* o) 
 }
 
 // ---------------------------------------------------------------- K3a: point-block inverses
-// Vinv_p = (V_p + mu I)^-1; per row w_i = b_i . (Vinv g_p) and beta_i = b_i^T Vinv b_i.
+// Vinv_p = (V_p + mu I)^-1; per row w_i = b_i . (Vinv g_p) and beta_i = b_i^T Vinv b_i, scattered to the
+// row's B position (the camera-side Schur corrections stream them).
 template <typename JT>
 __global__ void __launch_bounds__(256)
 k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_t* __restrict__ pt_ptr,
-                const JT* __restrict__ Jp_ps, const double* __restrict__ V,
-                const double* __restrict__ gp, double* __restrict__ Vinv, double* __restrict__ w_ps,
-                double* __restrict__ beta_ps) {
+                const int32_t* __restrict__ posB, const JT* __restrict__ Jp_ps, const double* __restrict__ V,
+                const double* __restrict__ gp, double* __restrict__ Vinv, double* __restrict__ w_B,
+                double* __restrict__ beta_B) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const double mu = *mu_ptr;
@@ -264,11 +327,12 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
     double b[3];
     #pragma unroll
     for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, (size_t)i);
-    w_ps[i] = b[0] * z0 + b[1] * z1 + b[2] * z2;
+    const int j = __ldg(posB + i);
+    w_B[j] = b[0] * z0 + b[1] * z1 + b[2] * z2;
     const double t0 = vi[0] * b[0] + vi[1] * b[1] + vi[2] * b[2];
     const double t1 = vi[1] * b[0] + vi[3] * b[1] + vi[4] * b[2];
     const double t2 = vi[2] * b[0] + vi[4] * b[1] + vi[5] * b[2];
-    beta_ps[i] = b[0] * t0 + b[1] * t1 + b[2] * t2;
+    beta_B[j] = b[0] * t0 + b[1] * t1 + b[2] * t2;
   }
 }
 
@@ -320,6 +384,7 @@ k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __r
     const size_t o = 8 * (size_t)c + k;
     rhs[o] = rr[k]; x[o] = 0.0; r[o] = rr[k]; z[o] = zz[k]; pv[o] = 0.0; sv[o] = 0.0;
   }
-  part[2 * c] = rz;
-  part[2 * c + 1] = r2;
+  part[4 * (size_t)c] = rz;
+  part[4 * (size_t)c + 1] = 0.0;
+  part[4 * (size_t)c + 2] = r2;
 }

@@ -1,47 +1,332 @@
-// Implicit-Schur matvec, block-Jacobi PCG vector kernels, back-substitution, trial step and the
-// LM accept/reject logic (K3b-K3d of SURVEY.md §7.2b).  Device-side control: every kernel reads
-// the SolverState flags, so the host never has to synchronise inside an iteration.
+// Implicit-Schur matvec + pipelined block-Jacobi PCG, back-substitution, trial step and the LM
+// accept/reject logic (K3b-K3d of SURVEY.md §7.2b).  Device-side control: every kernel reads the
+// SolverState flags, so the host never has to synchronise inside an iteration.
+//
+// Row orders (see b200ba.cu, plan construction):
+//   A = (point, camera)                 — the point-side kernels stream it
+//   B = (point block, camera, point)    — the camera-side kernels stream it: per camera nPB RUNS
+// A and B are permutations of each other INSIDE a point block (a few 100 K rows), so the per-row
+// scalars exchanged between the two sides (sigma: B->A, omega: A->B) are gathered / scattered
+// within an L2-resident window instead of across the whole 5 M-row array.
+//
+// One PCG iteration is TWO launches (Ghysels & Vanroose 2014, pipelined PCG: the matvec input
+// m = Minv w is camera-local, so the camera kernel can finish matvec i, update all vectors and
+// start matvec i+1 while its rows are still on chip):
+//   k_ps : (block 0: reduce the dot partials -> alpha, beta, convergence flag)
+//          omega_i = b_i . Vinv_p sum_{j in p} b_j sigma_j
+//   k_cs : n_c = (U_c + mu) m_c - sum_{i in c} a_i omega_i        [rows read from HBM ONCE,
+//          z,q,s,p,x,r,u,w recurrences; dot partials; m_c = Minv_c w_c    stashed in shared memory]
+//          sigma_i = a_i . m_c
 #pragma once
 #include "ba_kernels.cuh"
 
-// ---------------------------------------------------------------- K3b pass 1 (point side)
-// Rows are processed in CHUNKS of whole points (<= MV_T*RPT rows and <= MV_T points, built once per
-// plan), one CTA per chunk, RPT rows per thread (row = r0 + tid + j*MV_T: coalesced SoA loads, all
-// issued before the first barrier so a CTA costs ~one DRAM round trip + the x gather):
-//   phase 1  s_i = a_i . x_c(i);  b_i s_i -> shared memory
-//   phase 2  one thread per point sums its run in order, z_p = Vinv_p t_p
-//   phase 3  w_i = b_i . z_p, written at the row's CAMERA-SORTED position (w_cs[inv_cs[i]]) so that
-//            pass 2 is a pure stream; the 40 MB/5M-row w array stays L2 resident between the passes.
-// BACKSUB: phase 2 instead does v_p = Vinv_p (g_p - t_p) -> vp; part[2*chunk] = v_p.g_p, [+1] = |v_p|^2
-#define MV_T 256
-template <typename JT> struct MvCfg;
-#ifndef MV_RPT_F32
-#define MV_RPT_F32 2
-#endif
-template <> struct MvCfg<float>  { static constexpr int RPT = MV_RPT_F32; static constexpr int MINB = MV_RPT_F32 == 1 ? 5 : 3; };
-template <> struct MvCfg<double> { static constexpr int RPT = 2; static constexpr int MINB = 3; };
+struct PcgVecs {
+  double *x, *r, *u, *w, *z, *q, *s, *p, *m;
+};
 
-template <typename JT, bool BACKSUB, bool WSCAT>
-__global__ void __launch_bounds__(MV_T, MvCfg<JT>::MINB)
-k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restrict__ chunk_row,
-          const int32_t* __restrict__ chunk_pt, const int32_t* __restrict__ pt_ptr,
-          const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
-          const int32_t* __restrict__ inv_cs, const JT* __restrict__ Jc_ps, const JT* __restrict__ Jp_ps,
-          const double* __restrict__ Vinv, const double* __restrict__ x, double* __restrict__ w_cs,
-          const double* __restrict__ gp, double* __restrict__ vp, double* __restrict__ part) {
-  constexpr int RPT = MvCfg<JT>::RPT;
-  constexpr int CAP = MV_T * RPT;
+enum {
+  CS_C = 1,        // accumulate -sum a_i omega_i over the camera's rows
+  CS_UX = 2,       // add (U_c + mu I) vin_c
+  CS_WRITE_Y = 4,  // y_c = n_c
+  CS_READ_Y = 8,   // n_c = y_c (multi-rank: after the all-reduce of the partial sums)
+  CS_INIT = 16,    // PCG (re)start: w = n, z=q=s=p=0, x kept, dots, m = Minv w
+  CS_ITER = 32,    // pipelined PCG recurrences with st->alpha/beta, dots, m = Minv w
+  CS_A = 64,       // sigma_i = a_i . v  (v = m after INIT/ITER, else vin)
+  CS_IGNORE_DONE = 128
+};
+
+#define PCG_STAG 25
+#define CS_T 512
+#define CS_NW (CS_T / 32)
+
+// ---------------------------------------------------------------- K3b camera side (fused)
+template <typename JT>
+__global__ void __launch_bounds__(CS_T, 2)
+k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ st,
+     const int32_t* __restrict__ runptr, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
+     double* __restrict__ sig, const double* __restrict__ U, const double* __restrict__ Minv,
+     const double* __restrict__ vin, double* __restrict__ y, PcgVecs v, double* __restrict__ part) {
+  extern __shared__ __align__(32) unsigned char stash_raw[];
+  JT* stash = reinterpret_cast<JT*>(stash_raw);
+  __shared__ CamRuns runs;
+  __shared__ double sred[8 * 32];
+  __shared__ __align__(16) double svec[9 * 8 + 128];  // z q s p x r u w vin | U_c | Minv_c
+  __shared__ double sm_m[8];
+  if (!(flags & CS_IGNORE_DONE) && st->pcg_done) return;
+  const int c = blockIdx.x, tid = threadIdx.x;
+  const bool upd = flags & (CS_INIT | CS_ITER);
+  // asynchronous prefetch of everything the camera-local vector update needs
+  if (tid < 200) {
+    const double* src = nullptr;
+    if (tid < 72) {
+      const int a = tid >> 3, k = tid & 7;
+      const double* base = a == 0 ? v.z : a == 1 ? v.q : a == 2 ? v.s : a == 3 ? v.p : a == 4 ? v.x : a == 5 ? v.r
+                           : a == 6 ? v.u : a == 7 ? v.w : vin;
+      const bool need = (a == 8) ? (vin != nullptr) : (upd && (a >= 4 || (flags & CS_ITER)));
+      if (need) src = base + 8 * (size_t)c + k;
+    } else if (tid < 136) {
+      if (flags & CS_UX) src = U + 64 * (size_t)c + (tid - 72);
+    } else if (upd) {
+      src = Minv + 64 * (size_t)c + (tid - 136);
+    }
+    if (src) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(&svec[tid]);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src));
+    } else {
+      svec[tid] = 0.0;
+    }
+  }
+  asm volatile("cp.async.commit_group;");
+  const int L = runs.load(c, C, nPB, runptr);  // includes a __syncthreads
+  double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (flags & CS_C) {
+    int r0 = 0, r1 = 0;
+    for (int l0 = tid; l0 < L; l0 += 2 * CS_T) {
+      const int l1 = l0 + CS_T;
+      const bool h1 = l1 < L;
+      const size_t j0 = runs.locate(l0, r0);
+      r1 = r0;
+      const size_t j1 = h1 ? runs.locate(l1, r1) : j0;
+      JT a0[8], a1[8];
+      ldrow(Jc_B + 8 * j0, a0);
+      const double w0 = __ldg(omg + j0);
+      double w1 = 0.0;
+      if (h1) { ldrow(Jc_B + 8 * j1, a1); w1 = __ldg(omg + j1); }
+      if (l0 < stash_rows) strow(stash + 8 * (size_t)l0, a0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] -= (double)a0[k] * w0;
+      if (h1) {
+        if (l1 < stash_rows) strow(stash + 8 * (size_t)l1, a1);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] -= (double)a1[k] * w1;
+      }
+      r0 = r1;
+    }
+    block_sum<8>(acc, sred);
+  }
+  asm volatile("cp.async.wait_all;");
+  __syncthreads();
+  if (tid < 32) {
+    const int k = tid & 7;
+    double nk = 0.0;
+    if (flags & CS_C) {
+#pragma unroll
+      for (int l = 0; l < 8; ++l)
+        if (l == k) nk = acc[l];
+    }
+    if (flags & CS_READ_Y) nk = y[8 * (size_t)c + k];
+    const double vk = svec[64 + k];
+    if (flags & CS_UX) {
+      double s = st->mu * vk;
+#pragma unroll
+      for (int l = 0; l < 8; ++l) s += svec[72 + 8 * k + l] * svec[64 + l];
+      nk += s;
+    }
+    if ((flags & CS_WRITE_Y) && tid < 8) y[8 * (size_t)c + k] = nk;
+    if (upd) {
+      double zk, qk, sk, pk, xk = svec[32 + k], rk = svec[40 + k], uk = svec[48 + k], wk = svec[56 + k];
+      if (flags & CS_INIT) {
+        wk = nk; zk = qk = sk = pk = 0.0;
+      } else {
+        const double alpha = st->alpha, beta = st->beta;
+        zk = nk + beta * svec[k];
+        qk = vk + beta * svec[8 + k];
+        sk = wk + beta * svec[16 + k];
+        pk = uk + beta * svec[24 + k];
+        xk += alpha * pk;
+        rk -= alpha * sk;
+        uk -= alpha * qk;
+        wk -= alpha * zk;
+      }
+      // m = Minv_c w : w of the camera lives in the 8-lane group
+      double mk = 0.0;
+      const int base = tid & ~7;
+#pragma unroll
+      for (int l = 0; l < 8; ++l) mk += svec[136 + 8 * k + l] * __shfl_sync(0xffffffffu, wk, base + l);
+      double g = rk * uk, d = wk * uk, q2 = rk * rk;
+#pragma unroll
+      for (int o = 4; o > 0; o >>= 1) {
+        g += __shfl_xor_sync(0xffffffffu, g, o);
+        d += __shfl_xor_sync(0xffffffffu, d, o);
+        q2 += __shfl_xor_sync(0xffffffffu, q2, o);
+      }
+      if (tid < 8) {
+        const size_t e = 8 * (size_t)c + k;
+        v.z[e] = zk; v.q[e] = qk; v.s[e] = sk; v.p[e] = pk;
+        v.x[e] = xk; v.r[e] = rk; v.u[e] = uk; v.w[e] = wk; v.m[e] = mk;
+        sm_m[k] = mk;
+        if (k == 0) { part[4 * (size_t)c] = g; part[4 * (size_t)c + 1] = d; part[4 * (size_t)c + 2] = q2; }
+      }
+    } else if (tid < 8) {
+      sm_m[k] = vk;
+    }
+  }
+  if (!(flags & CS_A)) return;
+  __syncthreads();
+  double m[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) m[k] = sm_m[k];
+  int r0 = 0;
+  const bool stashed = flags & CS_C;
+  for (int l = tid; l < L; l += CS_T) {
+    const size_t j = runs.locate(l, r0);
+    JT a[8];
+    if (stashed && l < stash_rows) ldrow_shared(stash + 8 * (size_t)l, a);
+    else ldrow(Jc_B + 8 * j, a);
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += (double)a[k] * m[k];
+    sig[j] = s;
+  }
+}
+
+// ---------------------------------------------------------------- PCG scalars (one CTA)
+// gamma = (r,u), delta = (w,u), rr = (r,r) from the per-camera partials of the last k_cs;
+// beta = gamma/gamma_old, alpha = gamma/(delta - beta gamma/alpha_old)  (first iteration: 0, gamma/delta).
+// Ordered reduction: the result does not depend on the launch geometry of anything else.
+__device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restrict__ st,
+                                            const double* __restrict__ part, double rtol, int maxiter,
+                                            double* sm3 /*3*32*/) {
+  double v3[3] = {0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    v3[0] += part[4 * (size_t)i];
+    v3[1] += part[4 * (size_t)i + 1];
+    v3[2] += part[4 * (size_t)i + 2];
+  }
+  block_sum<3>(v3, sm3);
+  if (threadIdx.x == 0) {
+    const double gamma = v3[0], delta = v3[1], rr = v3[2];
+    const bool conv = rr <= rtol * rtol * st->rhs2;
+    const bool bad = !(rr == rr) || !(delta == delta);
+    // the recurrences of pipelined CG lose accuracy before the classical method does: no new minimum of
+    // |r|^2 for PCG_STAG iterations = stagnation; the host then verifies / restarts from the true residual
+    int since = st->since_best + 1;
+    if (rr < st->rr_best) { st->rr_best = rr; since = 0; }
+    st->since_best = since;
+    const bool stag = since >= PCG_STAG;
+    st->rr = rr;
+    st->pcg_iters = it;
+    if (conv || bad || stag || it >= maxiter) {
+      st->pcg_done = 1;
+      st->pcg_stop = bad ? 2 : conv ? 0 : stag ? 3 : 1;
+      if (!conv && !bad && !stag) st->status |= 4;
+    } else {
+      double alpha, beta;
+      if (st->pcg_first) {
+        beta = 0.0;
+        alpha = gamma / delta;
+        st->pcg_first = 0;
+      } else {
+        beta = gamma / st->cg[0][0];
+        alpha = gamma / (delta - beta * gamma / st->cg[0][1]);
+      }
+      st->cg[0][0] = gamma;
+      st->cg[0][1] = alpha;
+      st->alpha = alpha;
+      st->beta = beta;
+    }
+  }
+}
+
+// After y = S x (plain matvec): true residual r = rhs - y, u = Minv r; part[4c+2] = |r_c|^2.
+// 8 threads per camera.
+__global__ void __launch_bounds__(256)
+k_pcg_true_residual(int C, const double* __restrict__ rhs, const double* __restrict__ y, const double* __restrict__ Minv,
+                    double* __restrict__ r, double* __restrict__ u, double* __restrict__ part) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = e >> 3, k = e & 7;
+  const bool act = c < C;
+  const double rk = act ? rhs[e] - y[e] : 0.0;
+  double uk = 0.0;
+  const int base = (threadIdx.x & 31) & ~7;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) {
+    const double rl = __shfl_sync(0xffffffffu, rk, base + l);
+    if (act) uk += Minv[64 * (size_t)c + 8 * k + l] * rl;
+  }
+  double q = rk * rk;
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  if (act) {
+    r[e] = rk;
+    u[e] = uk;
+    if (k == 0) { part[4 * (size_t)c] = 0.0; part[4 * (size_t)c + 1] = 0.0; part[4 * (size_t)c + 2] = q; }
+  }
+}
+// verdict on the true residual: converged -> done stays set (pcg_stop 0); else restart PCG from x
+__global__ void __launch_bounds__(256)
+k_pcg_verify(int C, SolverState* __restrict__ st, const double* __restrict__ part, double rtol) {
+  __shared__ double sm[32];
+  double v[1] = {0.0};
+  for (int i = threadIdx.x; i < C; i += blockDim.x) v[0] += part[4 * (size_t)i + 2];
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) {
+    const double rr = v[0];
+    st->rr_true = rr;
+    if (rr <= rtol * rtol * st->rhs2 || !(rr == rr)) {
+      st->pcg_done = 1;
+      st->pcg_stop = (rr == rr) ? 0 : 2;
+    } else {
+      st->pcg_done = 0;
+      st->pcg_first = 1;
+      st->rr_best = rr;
+      st->since_best = 0;
+      st->rr = rr;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- K3b point side
+// Rows in A order are processed in CHUNKS of whole points (<= PS_T*PS_RPT rows and <= PS_T points,
+// built once per plan), one CTA per chunk, PS_RPT rows per thread (row = r0 + tid + j*PS_T):
+//   phase 1  sigma_i gathered from the B-ordered exchange array;  b_i sigma_i -> shared memory
+//   phase 2  one thread per point sums its run in order, z_p = Vinv_p t_p
+//   phase 3  omega_i = b_i . z_p scattered to the row's B position
+// BACKSUB: phase 2 instead does v_p = Vinv_p (g_p - t_p) -> vp; part[2*chunk] = v_p.g_p, [+1] = |v_p|^2
+// do_scalars bit 0: block 0 first turns the dot partials of the previous k_cs into alpha/beta/convergence;
+// bit 1: run even if the PCG-finished flag is set (plain matvec).
+#define PS_T 256
+#define PS_RPT 2
+template <typename JT, bool BACKSUB>
+__global__ void __launch_bounds__(PS_T)
+k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxiter, SolverState* __restrict__ st,
+     const double* __restrict__ cpart, const int32_t* __restrict__ chunk_row, const int32_t* __restrict__ chunk_pt,
+     const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ pt_A, const int32_t* __restrict__ posB,
+     const JT* __restrict__ Jp_A, const double* __restrict__ Vinv, const double* __restrict__ sig,
+     double* __restrict__ omg, const double* __restrict__ gp, double* __restrict__ vp, double* __restrict__ part) {
+  constexpr int CAP = PS_T * PS_RPT;
   __shared__ double sb[3][CAP];
-  __shared__ double sz[3][MV_T];
+  __shared__ double sz[3][PS_T];
   __shared__ double sred[3 * 32];
-  if (!BACKSUB && st->pcg_done) return;
+  if (!BACKSUB && !(do_scalars & 2) && st->pcg_done) return;
   const int ch = blockIdx.x, tid = threadIdx.x;
+  if (!BACKSUB && (do_scalars & 1) && ch == 0) {
+    pcg_scalars(C, it, st, cpart, rtol, maxiter, sred);
+    __syncthreads();
+  }
+  if (ch >= nchunks) return;
   const int r0 = chunk_row[ch], nrows = chunk_row[ch + 1] - r0;
   const int p0 = chunk_pt[ch], npts = chunk_pt[ch + 1] - p0;
   double acc[2] = {0.0, 0.0};
   if (nrows <= CAP) {
     double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
     int beg = 0, end = 0;
+    JT b[PS_RPT][3];
+    int dst[PS_RPT], lp[PS_RPT];
+    double s[PS_RPT];
+#pragma unroll
+    for (int j = 0; j < PS_RPT; ++j) {
+      const int i = tid + j * PS_T;
+      const size_t row = (size_t)r0 + i;
+      dst[j] = 0; lp[j] = 0; s[j] = 0.0;
+      b[j][0] = b[j][1] = b[j][2] = (JT)0;
+      if (i < nrows) {
+        dst[j] = __ldg(posB + row);
+        if (!BACKSUB) lp[j] = __ldg(pt_A + row) - p0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) b[j][k] = __ldg(Jp_A + (size_t)k * N + row);
+      }
+    }
     if (tid < npts) {
       const int p = p0 + tid;
       beg = __ldg(pt_ptr + p) - r0;
@@ -50,34 +335,13 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
       for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
       if (BACKSUB) { g0 = gp[3 * (size_t)p]; g1 = gp[3 * (size_t)p + 1]; g2 = gp[3 * (size_t)p + 2]; }
     }
-    JT a[RPT][8], b[RPT][3];  // kept in storage precision until used (register budget)
-    int cam[RPT], lp[RPT], dst[RPT];
 #pragma unroll
-    for (int j = 0; j < RPT; ++j) {
-      const int i = tid + j * MV_T;
-      const size_t row = (size_t)r0 + i;
-      cam[j] = 0; lp[j] = 0; dst[j] = 0;
-      if (i < nrows) {
-        cam[j] = __ldg(cam_ps + row);
-        if (!BACKSUB) { lp[j] = __ldg(pt_ps + row) - p0; dst[j] = WSCAT ? __ldg(inv_cs + row) : (int)row; }
+    for (int j = 0; j < PS_RPT; ++j)
+      if (tid + j * PS_T < nrows) s[j] = __ldg(sig + dst[j]);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a[j][k] = __ldg(Jc_ps + (size_t)k * N + row);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) b[j][k] = __ldg(Jp_ps + (size_t)k * N + row);
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < RPT; ++j) {
-      const int i = tid + j * MV_T;
-      if (i < nrows) {
-        double xv[8];
-        ld256(x + 8 * (size_t)cam[j], xv);
-        ld256(x + 8 * (size_t)cam[j] + 4, xv + 4);
-        double s = 0.0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += (double)a[j][k] * xv[k];
-        sb[0][i] = (double)b[j][0] * s; sb[1][i] = (double)b[j][1] * s; sb[2][i] = (double)b[j][2] * s;
-      }
+    for (int j = 0; j < PS_RPT; ++j) {
+      const int i = tid + j * PS_T;
+      if (i < nrows) { sb[0][i] = (double)b[j][0] * s[j]; sb[1][i] = (double)b[j][1] * s[j]; sb[2][i] = (double)b[j][2] * s[j]; }
     }
     __syncthreads();
     if (tid < npts) {
@@ -101,27 +365,21 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
     if (!BACKSUB) {
       __syncthreads();
 #pragma unroll
-      for (int j = 0; j < RPT; ++j) {
-        const int i = tid + j * MV_T;
+      for (int j = 0; j < PS_RPT; ++j) {
+        const int i = tid + j * PS_T;
         if (i < nrows)
-          w_cs[dst[j]] = (double)b[j][0] * sz[0][lp[j]] + (double)b[j][1] * sz[1][lp[j]] + (double)b[j][2] * sz[2][lp[j]];
+          omg[dst[j]] = (double)b[j][0] * sz[0][lp[j]] + (double)b[j][1] * sz[1][lp[j]] + (double)b[j][2] * sz[2][lp[j]];
       }
     }
   } else {
     // a single point with more than CAP observations: CTA-wide loop + ordered reduction
     const int p = p0;
     double t[3] = {0, 0, 0};
-    for (int i = tid; i < nrows; i += MV_T) {
+    for (int i = tid; i < nrows; i += PS_T) {
       const size_t row = (size_t)r0 + i;
-      const double2* xc = reinterpret_cast<const double2*>(x + 8 * (size_t)__ldg(cam_ps + row));
-      double s = 0.0;
+      const double s = __ldg(sig + __ldg(posB + row));
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const double2 xv = xc[k];
-        s += jget<JT>(Jc_ps, N, 2 * k, row) * xv.x + jget<JT>(Jc_ps, N, 2 * k + 1, row) * xv.y;
-      }
-#pragma unroll
-      for (int k = 0; k < 3; ++k) t[k] += jget<JT>(Jp_ps, N, k, row) * s;
+      for (int k = 0; k < 3; ++k) t[k] += jget<JT>(Jp_A, N, k, row) * s;
     }
     block_sum<3>(t, sred);
     if (tid == 0) { sz[0][0] = t[0]; sz[1][0] = t[1]; sz[2][0] = t[2]; }
@@ -145,10 +403,10 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
       const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
       const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
       const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
-      for (int i = tid; i < nrows; i += MV_T) {
+      for (int i = tid; i < nrows; i += PS_T) {
         const size_t row = (size_t)r0 + i;
-        w_cs[WSCAT ? (size_t)__ldg(inv_cs + row) : row] = jget<JT>(Jp_ps, N, 0, row) * z0 + jget<JT>(Jp_ps, N, 1, row) * z1 +
-                                    jget<JT>(Jp_ps, N, 2, row) * z2;
+        omg[__ldg(posB + row)] = jget<JT>(Jp_A, N, 0, row) * z0 + jget<JT>(Jp_A, N, 1, row) * z1 +
+                                 jget<JT>(Jp_A, N, 2, row) * z2;
       }
     }
   }
@@ -161,74 +419,26 @@ k_mv_rows(size_t N, const SolverState* __restrict__ st, const int32_t* __restric
   }
 }
 
-// ---------------------------------------------------------------- K3b pass 2 (camera side)
-// ypart_c = - sum_{j in cs run of c} a_j w_cs[j]  (pure stream).  FUSE (single rank): y_c = (U_c + mu I) x_c +
-// ypart_c and part[c] = x_c . y_c, so no separate vector kernel is needed.
-template <typename JT, bool FUSE, bool WGATHER>
+// PCG start-up reduction: rhs2 = |rhs|^2 from part[4c+2]
 __global__ void __launch_bounds__(256)
-k_mv_cam(const SolverState* __restrict__ st, const int32_t* __restrict__ cam_ptr,
-         const int32_t* __restrict__ perm_cs, const JT* __restrict__ Jc_cs,
-         const double* __restrict__ w_cs, const double* __restrict__ U, const double* __restrict__ xin,
-         double* __restrict__ y, double* __restrict__ part) {
-  __shared__ double sm[8 * 32];
-  if (st->pcg_done) return;
-  const int c = blockIdx.x;
-  const int beg = cam_ptr[c], end = cam_ptr[c + 1];
-  double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 4
-  for (int j = beg + threadIdx.x; j < end; j += blockDim.x) {
-    double a[8];
-    load8<JT>(Jc_cs + 8 * (size_t)j, a);
-    const double w = WGATHER ? __ldg(w_cs + __ldg(perm_cs + j)) : __ldg(w_cs + j);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] -= a[k] * w;
-  }
-  block_sum<8>(acc, sm);
-  if (threadIdx.x < 32) {
-    if (FUSE) {
-      const int k = threadIdx.x & 7;  // lanes 0..7: row k of (U + mu I) x
-      const double mu = st->mu;
-      double s = 0.0;
-#pragma unroll
-      for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * xin[8 * (size_t)c + l];
-      const double xk = xin[8 * (size_t)c + k];
-      s += mu * xk;
-      double yk = 0.0;
-#pragma unroll
-      for (int l = 0; l < 8; ++l)
-        if (l == k) yk = acc[l];
-      yk += s;
-      double d = (threadIdx.x < 8) ? yk * xk : 0.0;
-      d = warp_sum(d);
-      if (threadIdx.x < 8) y[8 * (size_t)c + k] = yk;
-      if (threadIdx.x == 0) part[c] = d;
-    } else if (threadIdx.x == 0) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) y[8 * (size_t)c + k] = acc[k];
-    }
+k_pcg_init(int C, SolverState* __restrict__ st, const double* __restrict__ part) {
+  __shared__ double sm[32];
+  double v[1] = {0.0};
+  for (int i = threadIdx.x; i < C; i += blockDim.x) v[0] += part[4 * (size_t)i + 2];
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) {
+    const double rr = v[0];
+    st->rr = rr;
+    st->rhs2 = rr;
+    st->pcg_iters = 0;
+    st->pcg_done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
+    st->pcg_stop = (rr == rr) ? 0 : 2;
+    st->pcg_first = 1;
+    st->rr_best = rr;
+    st->since_best = 0;
+    st->rr_true = rr;
   }
 }
-
-// multi-rank variant of the fused epilogue, run after the all-reduce of ypart
-__global__ void k_pcg_y(int C, const SolverState* __restrict__ st, const double* __restrict__ U,
-                        const double* __restrict__ xin, double* __restrict__ y, double* __restrict__ part) {
-  if (st->pcg_done) return;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  const double mu = st->mu;
-  double d = 0.0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    double s = mu * xin[8 * (size_t)c + k];
-#pragma unroll
-    for (int l = 0; l < 8; ++l) s += U[64 * (size_t)c + 8 * k + l] * xin[8 * (size_t)c + l];
-    const double yk = y[8 * (size_t)c + k] + s;
-    y[8 * (size_t)c + k] = yk;
-    d += yk * xin[8 * (size_t)c + k];
-  }
-  part[c] = d;
-}
-
 // deterministic sum of n values by one CTA (all threads get the result)
 __device__ __forceinline__ double cta_sum_strided(const double* __restrict__ in, int n, int stride,
                                                   double* sm) {
@@ -242,109 +452,6 @@ __device__ __forceinline__ double cta_sum_strided(const double* __restrict__ in,
   __syncthreads();
   return r;
 }
-
-// ---------------------------------------------------------------- K3c: PCG vector kernel
-// Chronopoulos-Gear form of preconditioned CG: ONE fused reduction point per iteration, so an
-// iteration is three launches (this kernel, matvec pass 1, matvec pass 2) with no grid sync:
-//   gamma = (r,u), delta = (w,u) with u = Minv r, w = S u        [partials from earlier kernels]
-//   beta = gamma/gamma_old, alpha = gamma / (delta - beta gamma / alpha_old)   (it 0: beta 0, alpha gamma/delta)
-//   p = u + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s;  u = Minv r
-// Every CTA re-reduces the per-camera partials in the same order (bit-identical alpha/beta in all
-// CTAs).  Scalars carried between iterations are double-buffered in st->cg[it & 1] so no CTA can
-// read a value another CTA of the same launch has already overwritten.  8 threads per camera.
-__global__ void __launch_bounds__(256)
-k_pcg_vec(int C, int it, SolverState* __restrict__ st, const double* __restrict__ part_gr /*2C: gamma_c, rr_c*/,
-          const double* __restrict__ part_d /*C: delta_c*/, const double* __restrict__ Minv,
-          const double* __restrict__ w, double* __restrict__ x, double* __restrict__ r, double* __restrict__ u,
-          double* __restrict__ pv, double* __restrict__ sv, double* __restrict__ part_out /*2C*/, double rtol,
-          int maxiter) {
-  __shared__ double sm[32];
-  if (st->pcg_done) return;
-  __shared__ double sm3[3 * 32];
-  __shared__ double bc3[3];
-  double v3[3] = {0.0, 0.0, 0.0};
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    v3[0] += part_gr[2 * (size_t)i];
-    v3[1] += part_gr[2 * (size_t)i + 1];
-    v3[2] += part_d[i];
-  }
-  block_sum<3>(v3, sm3);
-  if (threadIdx.x == 0) { bc3[0] = v3[0]; bc3[1] = v3[1]; bc3[2] = v3[2]; }
-  __syncthreads();
-  const double gamma = bc3[0], rr = bc3[1], delta = bc3[2];
-  (void)sm;
-  const bool conv = rr <= rtol * rtol * st->rhs2;
-  const bool bad = !(rr == rr) || !(delta == delta);
-  const bool stop = conv || bad || it >= maxiter;
-  double alpha, beta;
-  if (it == 0) {
-    beta = 0.0;
-    alpha = gamma / delta;
-  } else {
-    const double g_old = st->cg[it & 1][0], a_old = st->cg[it & 1][1];
-    beta = gamma / g_old;
-    alpha = gamma / (delta - beta * gamma / a_old);
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    st->rr = rr;
-    st->pcg_iters = it;
-    if (stop) {
-      st->pcg_done = 1;
-      if (!conv && !bad) st->status |= 4;
-    } else {
-      st->cg[(it + 1) & 1][0] = gamma;
-      st->cg[(it + 1) & 1][1] = alpha;
-      st->alpha = alpha;
-      st->beta = beta;
-    }
-  }
-  if (stop) return;
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;  // element index: camera e>>3, row e&7
-  const int c = e >> 3, k = e & 7;
-  double rk = 0.0, uk = 0.0;
-  const bool act = c < C;
-  if (act) {
-    const double pk = u[e] + beta * pv[e];
-    const double sk = w[e] + beta * sv[e];
-    pv[e] = pk;
-    sv[e] = sk;
-    x[e] += alpha * pk;
-    rk = r[e] - alpha * sk;
-    r[e] = rk;
-  }
-  // u_k = sum_l Minv[k][l] r_l : r of the camera lives in the 8-lane group
-  const int base = (threadIdx.x & 31) & ~7;
-#pragma unroll
-  for (int l = 0; l < 8; ++l) {
-    const double rl = __shfl_sync(0xffffffffu, rk, base + l);
-    if (act) uk += Minv[64 * (size_t)c + 8 * k + l] * rl;
-  }
-  if (act) u[e] = uk;
-  double g = rk * uk, q = rk * rk;
-#pragma unroll
-  for (int o = 4; o > 0; o >>= 1) {
-    g += __shfl_xor_sync(0xffffffffu, g, o);
-    q += __shfl_xor_sync(0xffffffffu, q, o);
-  }
-  if (act && k == 0) {
-    part_out[2 * c] = g;
-    part_out[2 * c + 1] = q;
-  }
-}
-
-// PCG start-up reduction: rhs2 = |rhs|^2
-__global__ void __launch_bounds__(256)
-k_pcg_init(int C, SolverState* __restrict__ st, const double* __restrict__ part_gr) {
-  __shared__ double sm[32];
-  const double rr = cta_sum_strided(part_gr + 1, C, 2, sm);
-  if (threadIdx.x == 0) {
-    st->rr = rr;
-    st->rhs2 = rr;
-    st->pcg_iters = 0;
-    st->pcg_done = (rr == 0.0 || !(rr == rr)) ? 1 : 0;
-  }
-}
-
 // ---------------------------------------------------------------- K3d: trial step + LM logic
 // trial = current - v; cam partials part[2c] = v_c.g_c, part[2c+1] = |v_c|^2
 __global__ void k_trial_cams(int C, const double* __restrict__ cam8, const double* __restrict__ vc,
@@ -431,4 +538,14 @@ __global__ void k_unpermute_rows(int64_t N, const int32_t* __restrict__ order_ps
   if (i >= N) return;
   const int64_t o = order_ps[i];
   for (int k = 0; k < w; ++k) out[o * w + k] = (double)in[(size_t)k * kstride + i];
+}
+
+// camera part of the rows back in the caller's order: out[order[i]*8 + k] = Jc_B[posB[i]*8 + k]
+template <typename TI>
+__global__ void k_unpermute_jc(int64_t N, const int32_t* __restrict__ order_ps, const int32_t* __restrict__ posB,
+                               const TI* __restrict__ Jc_B, double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int64_t o = order_ps[i], j = posB[i];
+  for (int k = 0; k < 8; ++k) out[o * 8 + k] = (double)Jc_B[j * 8 + k];
 }

@@ -11,7 +11,9 @@ struct SolverState {
   double mu, nu, loss, loss_trial, grad2, maxdiag, rho, denom;
   double rz, rz_new, pAp, rr, rhs2, alpha, beta, vg, vv;
   double cg[2][2];  // double-buffered (gamma, alpha) of the Chronopoulos-Gear recurrence
+  double rr_best, rr_true;
   int accepted, pcg_done, pcg_iters, status;
+  int pcg_first, pcg_stop /*0 converged, 1 maxiter, 2 NaN, 3 stagnated*/, since_best, pad_;
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
