@@ -110,12 +110,12 @@ def bytes_models(C, P, N, jsz):
     """Algorithmic bytes per launch of each kernel class (what the kernel MUST move given the
     stored-Jacobian formulation actually built; jsz = bytes per stored Jacobian value)."""
     return {
-        # read obs 16 + idx 8 + inv 4; write r 8+8, Jc twice 16*jsz, Jp 3*jsz; params once
-        "resjac": N * (16 + 8 + 4 + 16 + 16 * jsz + 3 * jsz) + 24 * P + 208 * C,
-        # pass 1: Jc 8*jsz + Jp 3*jsz + cam 4 -> w 8 ; per point Vinv 48 + ptr 4 ; x 64/cam
-        "mv_pt": N * (11 * jsz + 4 + 8) + 52 * P + 64 * C,
-        # pass 2: Jc_cs 8*jsz + perm 4 + w 8 ; per camera U 512 + p 64 + y 64
-        "mv_cam": N * (8 * jsz + 4 + 8) + 640 * C,
+        # read obs 16 + idx 8 + posB 4; write r 8+8 (A and B order), Jc once (B order) 8*jsz, Jp 3*jsz; params once
+        "resjac": N * (16 + 8 + 4 + 16 + 8 * jsz + 3 * jsz) + 24 * P + 208 * C,
+        # point kernel: Jp 3*jsz + posB 4 + pt 4 + sigma 8 -> omega 8 ; per point Vinv 48 + ptr 4
+        "mv_pt": N * (3 * jsz + 4 + 4 + 8 + 8) + 52 * P,
+        # camera kernel: Jc 8*jsz + omega 8 -> sigma 8 ; per camera PCG record 576 r+w, U 512, Minv 512, run table
+        "mv_cam": N * (8 * jsz + 8 + 8) + (2 * 576 + 1024 + 160) * C,
         "cost": N * (16 + 8) + 24 * P + 208 * C,
     }
 

@@ -6,7 +6,9 @@
 #include <cub/cub.cuh>
 #include <nccl.h>
 
+#include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -14,6 +16,7 @@
 #include <vector>
 
 #include "ba_pcg.cuh"
+#include "ba_cs_ring.cuh"
 #include "pose_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -57,7 +60,12 @@ struct b200ba_plan {
   // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
   int32_t *posB = nullptr;                                           // A row -> B position
-  int32_t *pt_ptr = nullptr, *runptr = nullptr;                      // A: CSR by point; B: nPB*C+1 run offsets
+  int32_t *pt_ptr = nullptr;                                         // A: CSR by point
+  int32_t *camtab = nullptr, *cam_order = nullptr;                   // B: per-camera run tables; cameras by descending rows
+  int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
+  int64_t NB = 0;                                                    // rows in B order incl. run padding
+  int ring_slots = 0, n_sm = 0;
+  size_t ring_smem = 0;
   int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
   int nchunks = 0, nPB = 1, block_rows = 0, max_cam_rows = 0, stash_rows = 0;
   size_t stash_bytes = 0;
@@ -68,7 +76,7 @@ struct b200ba_plan {
   double *tab = nullptr, *tab_trial = nullptr;
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
-  PcgVecs v = {};
+  double* cv = nullptr;  // PCG vectors, camera-major records (ba_pcg.cuh)
   double *y = nullptr, *vp = nullptr;
   double *cam_trial = nullptr, *pts_trial = nullptr;
   double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
@@ -148,6 +156,15 @@ __global__ void k_segment_ptr64(int64_t nseg, int64_t N, const int64_t* __restri
   }
   ptr[s] = (int32_t)lo;
 }
+// padded B position of every A row: runs start at run_start[key] (multiples of 4 rows)
+__global__ void k_posB(int64_t N, const int32_t* __restrict__ permBA, const int64_t* __restrict__ key_sorted,
+                       const int32_t* __restrict__ runptr_u, const int32_t* __restrict__ run_start,
+                       int32_t* __restrict__ posB) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= N) return;
+  const int64_t k = key_sorted[j];
+  posB[permBA[j]] = run_start[k] + (int32_t)(j - runptr_u[k]);
+}
 __global__ void k_gather_i32(int64_t N, const int32_t* __restrict__ idx, const int32_t* __restrict__ src,
                              int32_t* __restrict__ dst) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -193,6 +210,15 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   if (!out || C <= 0 || P < 0 || N < 0 || N >= (1LL << 31)) FAIL(B200BA_EINVAL, "plan_create: bad sizes");
   if (N > 0 && (!cam_idx || !pt_idx)) FAIL(B200BA_EINVAL, "plan_create: null index arrays");
   cudaStream_t s = (cudaStream_t)stream_;
+  const bool vtime = getenv("B200BA_VERBOSE") != nullptr;
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!vtime) return;
+    cudaDeviceSynchronize();
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[b200ba] plan_create %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+    t_last = now;
+  };
   b200ba_plan* p = new b200ba_plan();
   p->C = C; p->P = P; p->N = N; p->jac_f32 = jac_f32 ? 1 : 0; p->jsz = jac_f32 ? 4 : 8;
   // point blocks: ~160 rows per camera per block (long coalesced runs on the camera side), window of
@@ -210,13 +236,12 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   int rc = 0;
 #define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
   A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(posB, N)
-  A(pt_ptr, P + 1) A(runptr, nruns + 1) A(obs_ps, N)
-  A(r_ps, N) A(r_B, N) A(w_B, N) A(beta_B, N) A(sig, N) A(omg, N)
+  A(pt_ptr, P + 1) A(obs_ps, N) A(r_ps, N)
+  A(camtab, (size_t)C * (((p->nPB + 3) & ~3) + ((p->nPB + 4) & ~3))) A(cam_order, C) A(tickets, 2)
   A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
-  A(v.x, (size_t)C * 8) A(v.r, (size_t)C * 8) A(v.u, (size_t)C * 8) A(v.w, (size_t)C * 8) A(v.z, (size_t)C * 8)
-  A(v.q, (size_t)C * 8) A(v.s, (size_t)C * 8) A(v.p, (size_t)C * 8) A(v.m, (size_t)C * 8) A(y, (size_t)C * 8 + 8)
+  A(cv, (size_t)C * CV_STRIDE) A(y, (size_t)C * 8 + 8)
   A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts_trial, (size_t)P * 3)
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
@@ -227,8 +252,6 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
 #undef A
   {
     void* q = nullptr;
-    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 8 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jc_B"); }
-    p->allocs.push_back(q); p->Jc_B = q;
     if (cudaMalloc(&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
     p->allocs.push_back(q); p->Jp_ps = q;
   }
@@ -238,8 +261,11 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     FAIL(B200BA_ECUDA, "cudaMallocHost failed");
   }
   cudaMemsetAsync(p->st, 0, sizeof(SolverState), s);
+  cudaMemsetAsync(p->tickets, 0, 2 * sizeof(int), s);
   cudaMemsetAsync(p->vp, 0, (size_t)(P ? P : 1) * 3 * sizeof(double), s);
 
+  std::vector<int32_t> hrun, hstart;  // unpadded run offsets / padded run starts (B order, run-major)
+  lap("workspace alloc");
   if (N > 0) {
     // validate, then sort rows by (point, camera) [A] and by (point block, camera, point) [B] with CUB radix sort
     int* bad = nullptr;
@@ -268,35 +294,87 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, cam_idx, p->cam_ps);
     LAUNCH(k_gather_i32, cdiv(N, 256), 256, 0, s, N, p->order_ps, pt_idx, p->pt_ps);
     LAUNCH(k_segment_ptr, cdiv(P + 1, 256), 256, 0, s, P, N, p->pt_ps, p->pt_ptr);
+    lap("A order sort");
     // B order: stable sort of the A rows by (point block, camera) keeps the point order inside a run
+    int32_t* runptr_u = nullptr;
+    cudaMalloc(&runptr_u, (nruns + 1) * sizeof(int32_t));
     LAUNCH(k_make_keys_B, cdiv(N, 256), 256, 0, s, N, C, p->block_rows, p->cam_ps, p->pt_ps, p->pt_ptr, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, permBA, (int)N, 0, nbB, s);
-    LAUNCH(k_invert_perm, cdiv(N, 256), 256, 0, s, N, permBA, p->posB);
-    LAUNCH(k_segment_ptr64, cdiv((int64_t)nruns + 1, 256), 256, 0, s, (int64_t)nruns, N, keys2, p->runptr);
+    LAUNCH(k_segment_ptr64, cdiv((int64_t)nruns + 1, 256), 256, 0, s, (int64_t)nruns, N, keys2, runptr_u);
+    // run starts padded to multiples of 4 rows (host scan; also yields the per-camera tables)
+    hrun.resize(nruns + 1);
+    cudaMemcpyAsync(hrun.data(), runptr_u, (nruns + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
     cudaError_t e = cudaStreamSynchronize(s);
-    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(permBA); cudaFree(tmp);
+    if (e == cudaSuccess) {
+      hstart.resize(nruns + 1);
+      int64_t acc = 0;
+      for (size_t k = 0; k < nruns; ++k) {
+        hstart[k] = (int32_t)acc;
+        acc += (hrun[k + 1] - hrun[k] + 3) & ~3;
+      }
+      hstart[nruns] = (int32_t)acc;
+      p->NB = acc;
+      if (acc >= (1LL << 31)) e = cudaErrorInvalidValue;
+    }
+    int32_t* run_start = nullptr;
+    if (e == cudaSuccess) {
+      cudaMalloc(&run_start, (nruns + 1) * sizeof(int32_t));
+      cudaMemcpyAsync(run_start, hstart.data(), (nruns + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+      LAUNCH(k_posB, cdiv(N, 256), 256, 0, s, N, permBA, keys2, runptr_u, run_start, p->posB);
+      e = cudaStreamSynchronize(s);
+    }
+    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(permBA); cudaFree(tmp); cudaFree(runptr_u);
+    if (run_start) cudaFree(run_start);
     if (e != cudaSuccess || (e = cudaGetLastError()) != cudaSuccess) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, std::string("plan_create: ") + cudaGetErrorString(e));
     }
   } else {
     cudaMemsetAsync(p->pt_ptr, 0, (P + 1) * sizeof(int32_t), s);
-    cudaMemsetAsync(p->runptr, 0, (nruns + 1) * sizeof(int32_t), s);
     cudaStreamSynchronize(s);
+    hrun.assign(nruns + 1, 0);
+    hstart.assign(nruns + 1, 0);
   }
+  lap("B order sort + positions");
   {
-    // rows per camera -> size of the shared-memory row stash of the fused camera kernel
-    std::vector<int32_t> hrun(nruns + 1);
-    if (cudaMemcpy(hrun.data(), p->runptr, (nruns + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
-      b200ba_plan_destroy(p);
-      FAIL(B200BA_ECUDA, "plan_create: runptr readback");
-    }
+    // per-camera run tables (camera-major: beg[nPB] | pre[nPB+1], both padded to 4 ints), cameras sorted by
+    // descending row count (longest first for the ticket-driven ring kernel), B-order row arrays (zeroed:
+    // the padding rows of every run must stay all-zero for ever)
+    const int nPB = p->nPB, nb = (nPB + 3) & ~3, stride = nb + ((nPB + 4) & ~3);
+    std::vector<int32_t> tab((size_t)C * stride, 0), order(C);
     std::vector<int64_t> rows(C, 0);
-    for (int r = 0; r < p->nPB; ++r)
-      for (int c = 0; c < C; ++c) rows[c] += hrun[(size_t)r * C + c + 1] - hrun[(size_t)r * C + c];
+    for (int c = 0; c < C; ++c) {
+      int32_t* t = tab.data() + (size_t)c * stride;
+      int32_t pre = 0;
+      for (int r = 0; r < nPB; ++r) {
+        const size_t k = (size_t)r * C + c;
+        t[r] = hstart[k];
+        t[nb + r] = pre;
+        pre += (hrun[k + 1] - hrun[k] + 3) & ~3;
+      }
+      t[nb + nPB] = pre;
+      rows[c] = pre;
+      order[c] = c;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rows[a] > rows[b]; });
     int64_t mx = 0;
     for (int c = 0; c < C; ++c) mx = rows[c] > mx ? rows[c] : mx;
     p->max_cam_rows = (int)mx;
+    cudaMemcpy(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    cudaMemcpy(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice);
+    const size_t nb_rows = p->NB ? (size_t)p->NB : 1;
+    void* q = nullptr;
+    int bad_alloc = 0;
+    if (cudaMalloc(&q, nb_rows * 8 * p->jsz) != cudaSuccess) bad_alloc = 1; else { p->allocs.push_back(q); p->Jc_B = q; cudaMemset(q, 0, nb_rows * 8 * p->jsz); }
+    double** arr[5] = {&p->r_B, &p->w_B, &p->beta_B, &p->sig, &p->omg};
+    for (int i = 0; i < 5 && !bad_alloc; ++i) {
+      if (cudaMalloc(&q, nb_rows * sizeof(double)) != cudaSuccess) { bad_alloc = 1; break; }
+      p->allocs.push_back(q);
+      *arr[i] = (double*)q;
+      cudaMemset(q, 0, nb_rows * sizeof(double));
+    }
+    if (bad_alloc) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: B-order row arrays"); }
+    // generic camera kernel: shared-memory row stash; ring kernel: slots of RING_R rows
     size_t cap = 96 * 1024;
     if (const char* e = getenv("B200BA_STASH_KB")) cap = (size_t)atol(e) * 1024;
     const size_t row_bytes = 8 * p->jsz;
@@ -305,13 +383,31 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     sr = (sr + 3) & ~(size_t)3;
     p->stash_rows = (int)sr;
     p->stash_bytes = sr * row_bytes;
+    int dev = 0, smem_max = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaError_t e1 = cudaFuncSetAttribute(k_cs<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
     cudaError_t e2 = cudaFuncSetAttribute(k_cs<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
     if (e1 != cudaSuccess || e2 != cudaSuccess || p->stash_bytes > 100 * 1024) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, "plan_create: shared-memory stash configuration");
     }
+    const size_t budget = (size_t)smem_max - 1024;
+    const size_t slotb = p->jac_f32 ? RingCfg<float>::slot_bytes : RingCfg<double>::slot_bytes;
+    const size_t fixedb = p->jac_f32 ? RingCfg<float>::fixed_bytes : RingCfg<double>::fixed_bytes;
+    int slots = budget > fixedb ? (int)((budget - fixedb) / slotb) : 0;
+    if (const char* e = getenv("B200BA_RING_SLOTS")) { const int v = atoi(e); if (v >= 0 && v < slots) slots = v; }
+    p->ring_slots = 0;
+    if (slots >= 2 && (int64_t)slots * RING_R >= mx && nPB <= MAXPB) {
+      p->ring_slots = slots;
+      p->ring_smem = fixedb + (size_t)slots * slotb;
+      e1 = cudaFuncSetAttribute(k_cs_ring<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->ring_smem);
+      e2 = cudaFuncSetAttribute(k_cs_ring<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->ring_smem);
+      if (e1 != cudaSuccess || e2 != cudaSuccess) p->ring_slots = 0;
+    }
   }
+  lap("camera tables, B arrays, smem config");
   {
     // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk)
     const int cap = PS_T * PS_RPT;
@@ -345,6 +441,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaMemcpy(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
     cudaMemcpy(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
   }
+  lap("point chunks");
   *out = p;
   return B200BA_OK;
 }
@@ -441,7 +538,7 @@ struct Ops {
     if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
-    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, C, p->nPB, p->runptr, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
+    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
            p->U, p->gc);
     int rc;
     if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
@@ -452,11 +549,19 @@ struct Ops {
     return 0;
   }
 
-  // camera-side kernel (see ba_pcg.cuh): flags select matvec tail / vector update / matvec head
-  static void cs(b200ba_plan* p, int cls, int flags, const double* vin, cudaStream_t s) {
+  // camera-side kernel (see ba_pcg.cuh): flags select matvec tail / vector update / matvec head.
+  // vin_slot: which vector of the camera-major PCG record is the matvec input (CV_*).
+  static void cs(b200ba_plan* p, int cls, int flags, int vin_slot, cudaStream_t s) {
+    const int fused = CS_C | CS_UX | CS_A;
+    if (p->ring_slots && (flags & fused) == fused && (flags & (CS_INIT | CS_ITER)) && !(flags & (CS_WRITE_Y | CS_READ_Y | CS_IGNORE_DONE))) {
+      const int grid = p->C < p->n_sm ? p->C : p->n_sm;
+      PLAUNCH(p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, p->camtab,
+              p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->cv, p->part2);
+      return;
+    }
     const size_t smem = (flags & CS_C) && (flags & CS_A) ? p->stash_bytes : 0;
-    PLAUNCH(p, cls, (k_cs<JT>), p->C, CS_T, smem, s, p->C, p->nPB, flags, smem ? p->stash_rows : 0, p->st, p->runptr,
-            (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin, p->y, p->v, p->part2);
+    PLAUNCH(p, cls, (k_cs<JT>), p->C, CS_T, smem, s, p->C, p->nPB, flags, smem ? p->stash_rows : 0, p->st, p->camtab,
+            (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->y, p->cv, p->part2);
   }
   // point-side kernel: omega from sigma (and the PCG scalars of iteration `it` when do_scalars)
   static void ps(b200ba_plan* p, int it, int do_scalars, double rtol, int maxiter, cudaStream_t s) {
@@ -465,11 +570,11 @@ struct Ops {
             (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr);
   }
   // matvec tail + vector update + next matvec head; multi-rank: partial sums are all-reduced in between
-  static int cs_step(b200ba_plan* p, int upd_flag, const double* vin, cudaStream_t s) {
+  static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
     if (p->nranks == 1) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
     } else {
-      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, nullptr, s);
+      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, -1, s);
       int rc;
       if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
       cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | upd_flag | CS_A, vin, s);
@@ -483,28 +588,28 @@ struct Ops {
     const int C = p->C, P = p->P;
     if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, p->posB,
                   (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->w_B, p->beta_B);
-    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, C, p->nPB, p->runptr, (const JT*)p->Jc_B, nullptr, p->w_B,
+    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, nullptr, p->w_B,
            p->beta_B, p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
     PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
-            p->Minv, p->rhs, p->v.x, p->v.r, p->v.u, p->v.p, p->v.s, p->part2);
+            p->Minv, p->rhs, p->cv, p->part2);
     PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
-    cs(p, PC_MV_CAM, CS_A, p->v.u, s);
+    cs(p, PC_MV_CAM, CS_A, CV_U, s);
     ps(p, 0, 0, 0.0, 0, s);
-    if ((rc = cs_step(p, CS_INIT, p->v.u, s))) return rc;
+    if ((rc = cs_step(p, CS_INIT, CV_U, s))) return rc;
     CK(cudaGetLastError());
     return 0;
   }
 
-  // y = S xin (xin: C x 8 device vector) — building block for tests; clobbers sigma/omega
-  static int matvec(b200ba_plan* p, const double* xin, cudaStream_t s) {
+  // y = S v for v = slot `xin` of the PCG record — verification / tests; clobbers sigma/omega
+  static int matvec(b200ba_plan* p, int xin, cudaStream_t s) {
     cs(p, PC_MV_CAM, CS_A | CS_IGNORE_DONE, xin, s);
     ps(p, 0, 2, 0.0, 0, s);
     if (p->nranks == 1) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
     } else {
-      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y | CS_IGNORE_DONE, nullptr, s);
+      cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y | CS_IGNORE_DONE, -1, s);
       int rc;
       if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
       cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
@@ -515,7 +620,7 @@ struct Ops {
   // one pipelined PCG iteration: point kernel (scalars of iteration `it` + omega) then camera kernel
   static int pcg_iteration(b200ba_plan* p, int it, double rtol, int maxiter, cudaStream_t s) {
     ps(p, it, 1, rtol, maxiter, s);
-    return cs_step(p, CS_ITER, p->v.m, s);
+    return cs_step(p, CS_ITER, CV_M, s);
   }
 
   // run PCG to convergence; device-side flag, host polls every `chunk` iterations.  When the recurrence
@@ -544,12 +649,12 @@ struct Ops {
       if (restarts >= 6) { p->st_host->status |= 4; break; }
       launched = p->st_host->pcg_iters;
       // verify: y = S x, r = rhs - y, u = Minv r, |r|^2 -> done (true residual small) or restart state
-      if ((rc = matvec(p, p->v.x, s))) return rc;
-      PLAUNCH(p, PC_PCG_VEC, k_pcg_true_residual, cdiv(8 * (int64_t)p->C, 256), 256, 0, s, p->C, p->rhs, p->y, p->Minv, p->v.r, p->v.u, p->part2);
+      if ((rc = matvec(p, CV_X, s))) return rc;
+      PLAUNCH(p, PC_PCG_VEC, k_pcg_true_residual, cdiv(8 * (int64_t)p->C, 256), 256, 0, s, p->C, p->rhs, p->y, p->Minv, p->cv, p->part2);
       PLAUNCH(p, PC_PCG_VEC, k_pcg_verify, 1, 256, 0, s, p->C, p->st, p->part2, rtol);
-      cs(p, PC_MV_CAM, CS_A, p->v.u, s);
+      cs(p, PC_MV_CAM, CS_A, CV_U, s);
       ps(p, 0, 0, 0.0, 0, s);
-      if ((rc = cs_step(p, CS_INIT, p->v.u, s))) return rc;
+      if ((rc = cs_step(p, CS_INIT, CV_U, s))) return rc;
       if ((rc = read_state(p, s))) return rc;
       if (p->st_host->pcg_done) break;
       ++restarts;
@@ -560,7 +665,7 @@ struct Ops {
   }
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
-    cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, p->v.x, s);
+    cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, CV_X, s);
     if (p->N) PLAUNCH(p, PC_BACKSUB, (k_ps<JT, true>), p->nchunks, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, 0, 0, 0.0, 0, p->st,
                       nullptr, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB, (const JT*)p->Jp_ps, p->Vinv, p->sig,
                       nullptr, p->gp, p->vp, p->partN);
@@ -661,9 +766,9 @@ extern "C" int b200ba_schur_matvec(b200ba_plan* p, const double* x, double* y, v
   if (!p || !x || !y) FAIL(B200BA_EINVAL, "null");
   cudaStream_t s = (cudaStream_t)stream_;
   // the PCG state is clobbered (call schur_prepare again before a solve)
-  CK(cudaMemcpyAsync(p->v.q, x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  CK(cudaMemcpy2DAsync(p->cv + 8 * CV_Q, CV_STRIDE * sizeof(double), x, 64, 64, p->C, cudaMemcpyDeviceToDevice, s));
   int rc;
-  if ((rc = DISPATCH(p, matvec, p, p->v.q, s))) return rc;
+  if ((rc = DISPATCH(p, matvec, p, CV_Q, s))) return rc;
   CK(cudaMemcpyAsync(y, p->y, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return B200BA_OK;
@@ -676,7 +781,7 @@ extern "C" int b200ba_schur_solve(b200ba_plan* p, double rtol, int maxiter, doub
   int rc;
   if ((rc = DISPATCH(p, pcg_solve, p, rtol, maxiter, 0, iters_host, s))) return rc;
   if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-  if (vc) CK(cudaMemcpyAsync(vc, p->v.x, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
+  if (vc) CK(cudaMemcpy2DAsync(vc, 64, p->cv + 8 * CV_X, CV_STRIDE * sizeof(double), 64, p->C, cudaMemcpyDeviceToDevice, s));
   if (vp) CK(cudaMemcpyAsync(vp, p->vp, (size_t)p->P * 3 * 8, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return B200BA_OK;
@@ -731,7 +836,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
     res->n_pcg_iters_total += pcg_iters;
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->v.x, p->gc, p->cam_trial, p->part);
+    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
     if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
     if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts_trial, inv_w2, p->scal + 8, s))) return rc;

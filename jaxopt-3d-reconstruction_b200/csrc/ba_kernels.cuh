@@ -77,36 +77,20 @@ __device__ __forceinline__ void ldrow_shared(const double* p, double* v) {
   for (int k = 0; k < 4; ++k) { const double2 a = q[k]; v[2 * k] = a.x; v[2 * k + 1] = a.y; }
 }
 
-// Rows of one camera in B order = nPB runs [runptr[r*C+c], runptr[r*C+c+1]).  The CTA flattens them:
+// Rows of one camera in B order = nPB runs (each padded to a multiple of 4 rows with all-zero rows, so every
+// run is 16 B-aligned in all per-row arrays and can be moved by bulk copies).  A CTA flattens them:
 // logical row l in [0, L) -> B position via the run prefix kept in shared memory (locate() scans
 // forward from the caller's previous run, l only grows).
-#define MAXPB 512
+#define MAXPB 256
 struct CamRuns {
   int beg[MAXPB];
-  int pre[MAXPB + 1];
-  __device__ __forceinline__ int load(int c, int C, int nPB, const int32_t* __restrict__ runptr) {
-    for (int r = threadIdx.x; r < nPB; r += blockDim.x) {
-      const int b = __ldg(runptr + (size_t)r * C + c);
-      beg[r] = b;
-      pre[r + 1] = __ldg(runptr + (size_t)r * C + c + 1) - b;
-    }
-    __syncthreads();
-    if (threadIdx.x < 32) {
-      const int lane = threadIdx.x;
-      int carry = 0;
-      for (int base = 0; base < nPB; base += 32) {
-        const int r = base + lane;
-        int v = r < nPB ? pre[r + 1] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int t = __shfl_up_sync(0xffffffffu, v, o);
-          if (lane >= o) v += t;
-        }
-        if (r < nPB) pre[r + 1] = carry + v;
-        carry += __shfl_sync(0xffffffffu, v, 31);
-      }
-      if (lane == 0) pre[0] = 0;
-    }
+  int pre[MAXPB + 4];
+  // camtab: per camera CAMTAB_STRIDE(nPB) ints = beg[nPB] (padded to 4) | pre[nPB+1] (padded to 4), built on the host
+  __device__ __forceinline__ int load(int c, int nPB, const int32_t* __restrict__ camtab) {
+    const int nb = (nPB + 3) & ~3;
+    const int32_t* t = camtab + (size_t)c * (nb + ((nPB + 4) & ~3));
+    for (int r = threadIdx.x; r < nPB; r += blockDim.x) beg[r] = __ldg(t + r);
+    for (int r = threadIdx.x; r <= nPB; r += blockDim.x) pre[r] = __ldg(t + nb + r);
     __syncthreads();
     return pre[nPB];
   }
@@ -226,13 +210,13 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __
 // U_c = sum a a^T and g_c = sum a r.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_cam_blocks(int C, int nPB, const int32_t* __restrict__ runptr, const JT* __restrict__ Jc_B,
+k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__ Jc_B,
              const double* __restrict__ s_B, const double* __restrict__ w_B, const double* __restrict__ beta_B,
              double* __restrict__ U, double* __restrict__ gc) {
   __shared__ double sm[44 * 32];
   __shared__ CamRuns runs;
   const int c = blockIdx.x;
-  const int L = runs.load(c, C, nPB, runptr);
+  const int L = runs.load(c, nPB, camtab);
   double acc[44];
 #pragma unroll
   for (int k = 0; k < 44; ++k) acc[k] = 0.0;
@@ -337,13 +321,12 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
 }
 
 // rhs = g_c + rhs_part; Minv_c = (U_c + mu I + Sd_part)^-1 (8x8, Cholesky, one thread per camera);
-// PCG start: x = 0, r = rhs, u = Minv r, p = s = 0; part[2c] = r.u, part[2c+1] = r.r
+// PCG start: x = 0, r = rhs, u = Minv r, all other vectors 0; part[4c+2] = r.r
 __global__ void __launch_bounds__(64)
 k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __restrict__ U,
                      const double* __restrict__ gc, const double* __restrict__ Sd_part,
                      const double* __restrict__ rhs_part, double* __restrict__ Minv,
-                     double* __restrict__ rhs, double* __restrict__ x, double* __restrict__ r,
-                     double* __restrict__ z, double* __restrict__ pv, double* __restrict__ sv, double* __restrict__ part) {
+                     double* __restrict__ rhs, double* __restrict__ cv, double* __restrict__ part) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const double mu = *mu_ptr;
@@ -381,8 +364,10 @@ k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __r
     for (int l = 0; l < 8; ++l) Minv[64 * (size_t)c + 8 * k + l] = 0.5 * (Mi[8 * k + l] + Mi[8 * l + k]);
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    const size_t o = 8 * (size_t)c + k;
-    rhs[o] = rr[k]; x[o] = 0.0; r[o] = rr[k]; z[o] = zz[k]; pv[o] = 0.0; sv[o] = 0.0;
+    double* v = cv + (size_t)72 * c;  // camera-major PCG record: x r u w z q s p m
+    rhs[8 * (size_t)c + k] = rr[k];
+    v[k] = 0.0; v[8 + k] = rr[k]; v[16 + k] = zz[k]; v[24 + k] = 0.0; v[32 + k] = 0.0; v[40 + k] = 0.0; v[48 + k] = 0.0;
+    v[56 + k] = 0.0; v[64 + k] = 0.0;
   }
   part[4 * (size_t)c] = rz;
   part[4 * (size_t)c + 1] = 0.0;

@@ -20,9 +20,10 @@
 #pragma once
 #include "ba_kernels.cuh"
 
-struct PcgVecs {
-  double *x, *r, *u, *w, *z, *q, *s, *p, *m;
-};
+// PCG vectors live camera-major: cv[c][slot][8] (CV_STRIDE doubles per camera), so everything the
+// camera-local update needs is one contiguous 576 B record (one bulk copy in the ring kernel).
+enum { CV_X = 0, CV_R, CV_U, CV_W, CV_Z, CV_Q, CV_S, CV_P, CV_M, CV_SLOTS };
+#define CV_STRIDE (8 * CV_SLOTS)
 
 enum {
   CS_C = 1,        // accumulate -sum a_i omega_i over the camera's rows
@@ -40,17 +41,67 @@ enum {
 #define CS_NW (CS_T / 32)
 
 // ---------------------------------------------------------------- K3b camera side (fused)
+// Generic version (any camera size, fp32 or fp64 rows, also the split multi-rank variants): one CTA per
+// camera, rows through registers, optional shared-memory stash.  The hot single-rank path uses the
+// TMA ring kernel in ba_cs_ring.cuh instead.
+// Camera-local update shared by both kernels; executed by the 8-lane groups of one warp (lane&7 = component).
+// sv: [0,72) the camera's cv record, [72,136) U_c, [136,200) Minv_c.  Returns m_k (the next matvec input).
+__device__ __forceinline__ double cs_update(int flags, int k, int lane, double nk, const double* sv, double mu,
+                                            double alpha, double beta, double* __restrict__ cvc,
+                                            double* __restrict__ part4, int vin_slot) {
+  const double vk = sv[8 * vin_slot + k];
+  if (flags & CS_UX) {
+    double s = mu * vk;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) s += sv[72 + 8 * k + l] * sv[8 * vin_slot + l];
+    nk += s;
+  }
+  double xk = sv[8 * CV_X + k], rk = sv[8 * CV_R + k], uk = sv[8 * CV_U + k], wk = sv[8 * CV_W + k];
+  double zk, qk, sk, pk;
+  if (flags & CS_INIT) {
+    wk = nk; zk = qk = sk = pk = 0.0;
+  } else {
+    zk = nk + beta * sv[8 * CV_Z + k];
+    qk = vk + beta * sv[8 * CV_Q + k];
+    sk = wk + beta * sv[8 * CV_S + k];
+    pk = uk + beta * sv[8 * CV_P + k];
+    xk += alpha * pk;
+    rk -= alpha * sk;
+    uk -= alpha * qk;
+    wk -= alpha * zk;
+  }
+  // m = Minv_c w : w of the camera lives in the 8-lane group
+  double mk = 0.0;
+  const int base = lane & ~7;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) mk += sv[136 + 8 * k + l] * __shfl_sync(0xffffffffu, wk, base + l);
+  double g = rk * uk, d = wk * uk, q2 = rk * rk;
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    g += __shfl_xor_sync(0xffffffffu, g, o);
+    d += __shfl_xor_sync(0xffffffffu, d, o);
+    q2 += __shfl_xor_sync(0xffffffffu, q2, o);
+  }
+  if (lane < 8) {
+    cvc[8 * CV_X + k] = xk; cvc[8 * CV_R + k] = rk; cvc[8 * CV_U + k] = uk; cvc[8 * CV_W + k] = wk;
+    cvc[8 * CV_Z + k] = zk; cvc[8 * CV_Q + k] = qk; cvc[8 * CV_S + k] = sk; cvc[8 * CV_P + k] = pk;
+    cvc[8 * CV_M + k] = mk;
+    if (k == 0) { part4[0] = g; part4[1] = d; part4[2] = q2; }
+  }
+  return mk;
+}
+
 template <typename JT>
 __global__ void __launch_bounds__(CS_T, 2)
 k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ st,
-     const int32_t* __restrict__ runptr, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
+     const int32_t* __restrict__ camtab, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
      double* __restrict__ sig, const double* __restrict__ U, const double* __restrict__ Minv,
-     const double* __restrict__ vin, double* __restrict__ y, PcgVecs v, double* __restrict__ part) {
-  extern __shared__ __align__(32) unsigned char stash_raw[];
+     int vin_slot, double* __restrict__ y, double* __restrict__ cv, double* __restrict__ part) {
+  extern __shared__ __align__(128) unsigned char stash_raw[];
   JT* stash = reinterpret_cast<JT*>(stash_raw);
   __shared__ CamRuns runs;
   __shared__ double sred[8 * 32];
-  __shared__ __align__(16) double svec[9 * 8 + 128];  // z q s p x r u w vin | U_c | Minv_c
+  __shared__ __align__(16) double svec[CV_STRIDE + 128];  // cv record | U_c | Minv_c
   __shared__ double sm_m[8];
   if (!(flags & CS_IGNORE_DONE) && st->pcg_done) return;
   const int c = blockIdx.x, tid = threadIdx.x;
@@ -58,17 +109,9 @@ k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ 
   // asynchronous prefetch of everything the camera-local vector update needs
   if (tid < 200) {
     const double* src = nullptr;
-    if (tid < 72) {
-      const int a = tid >> 3, k = tid & 7;
-      const double* base = a == 0 ? v.z : a == 1 ? v.q : a == 2 ? v.s : a == 3 ? v.p : a == 4 ? v.x : a == 5 ? v.r
-                           : a == 6 ? v.u : a == 7 ? v.w : vin;
-      const bool need = (a == 8) ? (vin != nullptr) : (upd && (a >= 4 || (flags & CS_ITER)));
-      if (need) src = base + 8 * (size_t)c + k;
-    } else if (tid < 136) {
-      if (flags & CS_UX) src = U + 64 * (size_t)c + (tid - 72);
-    } else if (upd) {
-      src = Minv + 64 * (size_t)c + (tid - 136);
-    }
+    if (tid < 72) src = cv + (size_t)CV_STRIDE * c + tid;
+    else if (tid < 136) { if (flags & CS_UX) src = U + 64 * (size_t)c + (tid - 72); }
+    else if (upd) src = Minv + 64 * (size_t)c + (tid - 136);
     if (src) {
       const unsigned dst = (unsigned)__cvta_generic_to_shared(&svec[tid]);
       asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src));
@@ -77,7 +120,7 @@ k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ 
     }
   }
   asm volatile("cp.async.commit_group;");
-  const int L = runs.load(c, C, nPB, runptr);  // includes a __syncthreads
+  const int L = runs.load(c, nPB, camtab);  // includes a __syncthreads
   double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (flags & CS_C) {
     int r0 = 0, r1 = 0;
@@ -115,51 +158,21 @@ k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ 
         if (l == k) nk = acc[l];
     }
     if (flags & CS_READ_Y) nk = y[8 * (size_t)c + k];
-    const double vk = svec[64 + k];
-    if (flags & CS_UX) {
-      double s = st->mu * vk;
+    if (upd) {
+      const double mk = cs_update(flags, k, tid, nk, svec, st->mu, st->alpha, st->beta, cv + (size_t)CV_STRIDE * c,
+                                  part + 4 * (size_t)c, vin_slot);
+      if (tid < 8) sm_m[k] = mk;
+    } else {
+      const double vk = vin_slot >= 0 ? svec[8 * vin_slot + k] : 0.0;
+      if (flags & CS_UX) {
+        double s = st->mu * vk;
 #pragma unroll
-      for (int l = 0; l < 8; ++l) s += svec[72 + 8 * k + l] * svec[64 + l];
-      nk += s;
+        for (int l = 0; l < 8; ++l) s += svec[72 + 8 * k + l] * svec[8 * vin_slot + l];
+        nk += s;
+      }
+      if (tid < 8) sm_m[k] = vk;
     }
     if ((flags & CS_WRITE_Y) && tid < 8) y[8 * (size_t)c + k] = nk;
-    if (upd) {
-      double zk, qk, sk, pk, xk = svec[32 + k], rk = svec[40 + k], uk = svec[48 + k], wk = svec[56 + k];
-      if (flags & CS_INIT) {
-        wk = nk; zk = qk = sk = pk = 0.0;
-      } else {
-        const double alpha = st->alpha, beta = st->beta;
-        zk = nk + beta * svec[k];
-        qk = vk + beta * svec[8 + k];
-        sk = wk + beta * svec[16 + k];
-        pk = uk + beta * svec[24 + k];
-        xk += alpha * pk;
-        rk -= alpha * sk;
-        uk -= alpha * qk;
-        wk -= alpha * zk;
-      }
-      // m = Minv_c w : w of the camera lives in the 8-lane group
-      double mk = 0.0;
-      const int base = tid & ~7;
-#pragma unroll
-      for (int l = 0; l < 8; ++l) mk += svec[136 + 8 * k + l] * __shfl_sync(0xffffffffu, wk, base + l);
-      double g = rk * uk, d = wk * uk, q2 = rk * rk;
-#pragma unroll
-      for (int o = 4; o > 0; o >>= 1) {
-        g += __shfl_xor_sync(0xffffffffu, g, o);
-        d += __shfl_xor_sync(0xffffffffu, d, o);
-        q2 += __shfl_xor_sync(0xffffffffu, q2, o);
-      }
-      if (tid < 8) {
-        const size_t e = 8 * (size_t)c + k;
-        v.z[e] = zk; v.q[e] = qk; v.s[e] = sk; v.p[e] = pk;
-        v.x[e] = xk; v.r[e] = rk; v.u[e] = uk; v.w[e] = wk; v.m[e] = mk;
-        sm_m[k] = mk;
-        if (k == 0) { part[4 * (size_t)c] = g; part[4 * (size_t)c + 1] = d; part[4 * (size_t)c + 2] = q2; }
-      }
-    } else if (tid < 8) {
-      sm_m[k] = vk;
-    }
   }
   if (!(flags & CS_A)) return;
   __syncthreads();
@@ -232,7 +245,7 @@ __device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restri
 // 8 threads per camera.
 __global__ void __launch_bounds__(256)
 k_pcg_true_residual(int C, const double* __restrict__ rhs, const double* __restrict__ y, const double* __restrict__ Minv,
-                    double* __restrict__ r, double* __restrict__ u, double* __restrict__ part) {
+                    double* __restrict__ cv, double* __restrict__ part) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   const int c = e >> 3, k = e & 7;
   const bool act = c < C;
@@ -248,8 +261,8 @@ k_pcg_true_residual(int C, const double* __restrict__ rhs, const double* __restr
 #pragma unroll
   for (int o = 4; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
   if (act) {
-    r[e] = rk;
-    u[e] = uk;
+    cv[(size_t)CV_STRIDE * c + 8 * CV_R + k] = rk;
+    cv[(size_t)CV_STRIDE * c + 8 * CV_U + k] = uk;
     if (k == 0) { part[4 * (size_t)c] = 0.0; part[4 * (size_t)c + 1] = 0.0; part[4 * (size_t)c + 2] = q; }
   }
 }
@@ -454,7 +467,7 @@ __device__ __forceinline__ double cta_sum_strided(const double* __restrict__ in,
 }
 // ---------------------------------------------------------------- K3d: trial step + LM logic
 // trial = current - v; cam partials part[2c] = v_c.g_c, part[2c+1] = |v_c|^2
-__global__ void k_trial_cams(int C, const double* __restrict__ cam8, const double* __restrict__ vc,
+__global__ void k_trial_cams(int C, const double* __restrict__ cam8, const double* __restrict__ vc, int vc_stride,
                              const double* __restrict__ gc, double* __restrict__ cam8_trial,
                              double* __restrict__ part) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -463,7 +476,7 @@ __global__ void k_trial_cams(int C, const double* __restrict__ cam8, const doubl
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const size_t o = 8 * (size_t)c + k;
-    const double v = vc[o];
+    const double v = vc[(size_t)vc_stride * c + k];
     cam8_trial[o] = cam8[o] - v;
     vg += v * gc[o];
     vv += v * v;

@@ -60,7 +60,7 @@ k_pose_lm(int B, int npts, int stage_smem, double* __restrict__ params, const do
           double inv_w2, int maxiter, double tol, double damping, int32_t* __restrict__ iter_num,
           double* __restrict__ loss_out, double* __restrict__ grad_out, double* __restrict__ mu_out,
           int32_t* __restrict__ status) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   PoseShared& S = *reinterpret_cast<PoseShared*>(smem_raw);
   double* stage = reinterpret_cast<double*>(smem_raw + sizeof(PoseShared));
   const int pose = blockIdx.x;

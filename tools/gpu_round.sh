@@ -6,10 +6,10 @@ out=gpurun_out/$tag
 mkdir -p $out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $out/smi.txt 2>&1
 if [ -z "$SKIP_TESTS" ]; then
-  timeout 900 python -m pytest tests -m gpu -x -q > $out/pytest.log 2>&1; echo "pytest exit $?" >> $out/pytest.log
+  timeout 400 python -m pytest tests -m gpu -x -q > $out/pytest.log 2>&1; echo "pytest exit $?" >> $out/pytest.log
   tail -3 $out/pytest.log
 fi
-timeout 600 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
+timeout 300 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
 tail -c 600 $out/bench.json
 if [ -n "$VARIANTS" ]; then bash tools/mv_variants.sh > $out/variants.txt 2>&1; cat $out/variants.txt; fi
 if [ -z "$SKIP_NCU" ]; then
@@ -17,7 +17,7 @@ if [ -z "$SKIP_NCU" ]; then
   timeout 300 $CMD > $out/plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 500 --csv --log-file $out/launches.csv $CMD > $out/ncu_list.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
-      -k regex:"k_cs|k_ps" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
+      -k regex:"k_cs_ring|k_ps" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
       -k regex:"k_resjac|k_cam_blocks|k_point" -s 5 -c 7 -f -o $out/prof_lin $CMD > $out/ncu_full_lin.log 2>&1
   echo "ncu exit $?"; ls -la $out
