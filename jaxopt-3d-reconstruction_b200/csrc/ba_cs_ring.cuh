@@ -30,7 +30,64 @@ struct RingCfg {
   __host__ __device__ static constexpr int slots(size_t smem_budget) { return (int)((smem_budget - fixed_bytes) / slot_bytes); }
 };
 
+#ifndef RING_EXP
+#define RING_EXP 0  // timing experiments only: 1 no pass-A math, 2 no update, 4 no pass-C math, 8 no cross-lane reduce
+#endif
+// slots of rows a consumer thread keeps in registers between pass C and pass A (fp32 rows: 6 x 8 regs; fp64 rows: 3 x 16)
+template <typename JT> struct RingKeep { static constexpr int N = sizeof(JT) == 4 ? 6 : 3; };
+#define RING_KEEP (RingKeep<JT>::N)
 #define RING_NCAM 3  // camera records in flight: consumers on i, rows streaming for i+1, record/table of i+2 landing
+
+// Compile-time unrolled per-slot steps of the consumer (recursion instead of `#pragma unroll`: the bodies
+// contain mbarrier wait loops, and the row stash must be indexed by constants to live in registers).
+struct RingCtx {
+  int ring, ring_ph, nslots, nchunks, L, tid, lane;
+  const int *beg, *pre, *run0;
+  uint64_t *bar_full, *bar_empty;
+};
+template <typename JT, int K>
+struct RingSteps {
+  static __device__ __forceinline__ void pass_c(RingCtx& cx, const JT* s_rows, const double* s_omg, JT (&keep)[RING_KEEP][8],
+                                                int (&pos)[RING_KEEP], double (&acc)[8]) {
+    RingSteps<JT, K - 1>::pass_c(cx, s_rows, s_omg, keep, pos, acc);
+    constexpr int k = K - 1;
+    pos[k] = -1;
+    if (k < cx.nchunks) {
+      mbar_wait(cx.bar_full + cx.ring, cx.ring_ph);
+      const int l = k * RING_R + cx.tid;
+      if (l < cx.L) {
+        ldrow_shared(s_rows + 8 * ((size_t)cx.ring * RING_R + cx.tid), keep[k]);
+        const double w = s_omg[(size_t)cx.ring * RING_R + cx.tid];
+        int r = cx.run0[cx.ring];
+        while (l >= cx.pre[r + 1]) ++r;
+        pos[k] = cx.beg[r] + (l - cx.pre[r]);
+        if (!(RING_EXP & 4)) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] -= (double)keep[k][j] * w;
+        }
+      }
+      __syncwarp();
+      if (cx.lane == 0) mbar_arrive(cx.bar_empty + cx.ring);
+      if (++cx.ring == cx.nslots) { cx.ring = 0; cx.ring_ph ^= 1; }
+    }
+  }
+  static __device__ __forceinline__ void pass_a(const JT (&keep)[RING_KEEP][8], const int (&pos)[RING_KEEP], const double (&m)[8],
+                                                double* __restrict__ sig) {
+    RingSteps<JT, K - 1>::pass_a(keep, pos, m, sig);
+    constexpr int k = K - 1;
+    if (pos[k] >= 0) {
+      double s0 = 0.0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s0 += (double)keep[k][j] * m[j];
+      sig[pos[k]] = s0;
+    }
+  }
+};
+template <typename JT>
+struct RingSteps<JT, 0> {
+  static __device__ __forceinline__ void pass_c(RingCtx&, const JT*, const double*, JT (&)[RING_KEEP][8], int (&)[RING_KEEP], double (&)[8]) {}
+  static __device__ __forceinline__ void pass_a(const JT (&)[RING_KEEP][8], const int (&)[RING_KEEP], const double (&)[8], double* __restrict__) {}
+};
 
 template <typename JT>
 __global__ void __launch_bounds__(RING_T, 1)
@@ -49,6 +106,7 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   uint64_t* bar_empty = bar_full + nslots;
   uint64_t* bar_cfull = bar_empty + nslots;
   uint64_t* bar_cempty = bar_cfull + RING_NCAM;
+  int* s_run0 = reinterpret_cast<int*>(bar_cempty + RING_NCAM);  // first run of the chunk held by each slot
   if (st->pcg_done) return;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   if (tid == 0) {
@@ -97,15 +155,22 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
       for (int k = 0; k < nchunks; ++k) {
         mbar_wait(bar_empty + ring, ring_ph ^ 1);
         const int l_lo = k * RING_R, l_hi = min(L, l_lo + RING_R);
-        if (lane == 0) mbar_arrive_expect_tx(bar_full + ring, (uint32_t)(l_hi - l_lo) * (ROWB + 8));
+        int first_run = nPB;
         for (int r = lane; r < nPB; r += 32) {
           const int lo = max(pre[r], l_lo), hi = min(pre[r + 1], l_hi);
           if (lo < hi) {
+            first_run = min(first_run, r);
             const size_t src = (size_t)beg[r] + (size_t)(lo - pre[r]);
             const size_t dst = (size_t)ring * RING_R + (size_t)(lo - l_lo);
             bulk_g2s(s_rows + 8 * dst, Jc_B + 8 * src, (uint32_t)(hi - lo) * ROWB, bar_full + ring);
             bulk_g2s(s_omg + dst, omg + src, (uint32_t)(hi - lo) * 8, bar_full + ring);
           }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) first_run = min(first_run, __shfl_xor_sync(0xffffffffu, first_run, o));
+        if (lane == 0) {
+          s_run0[ring] = first_run;  // published by the arrive below
+          mbar_arrive_expect_tx(bar_full + ring, (uint32_t)(l_hi - l_lo) * (ROWB + 8));
         }
         if (++ring == nslots) { ring = 0; ring_ph ^= 1; }
       }
@@ -114,6 +179,9 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   }
 
   // -------------------------------------------------------------- consumer warps
+  // Each thread keeps the rows it met in pass C in REGISTERS (RING_KEEP slots' worth), so a slot goes back
+  // to the producer as soon as pass C has read it: the ring is pure prefetch depth (~2 cameras ahead) and
+  // HBM streaming never waits for the serial reduce / update / pass-A phases of a camera.
   int ring = 0, ring_ph = 0;
   const double mu = st->mu, alpha = st->alpha, beta = st->beta;
   for (int i = 0; i < ncam; ++i) {
@@ -125,9 +193,16 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
     const int* pre = B.tab + nb;
     const int L = pre[nPB];
     const int nchunks = (L + RING_R - 1) / RING_R;
-    const int ring0 = ring;
     double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int k = 0; k < nchunks; ++k) {
+    JT keep[RING_KEEP][8];
+    int pos[RING_KEEP];
+    {
+      RingCtx cx{ring, ring_ph, nslots, nchunks, L, tid, lane, beg, pre, s_run0, bar_full, bar_empty};
+      RingSteps<JT, RING_KEEP>::pass_c(cx, s_rows, s_omg, keep, pos, acc);
+      ring = cx.ring; ring_ph = cx.ring_ph;
+    }
+    // cameras with more rows than the register stash holds: pass C from the slot, pass A re-reads from HBM
+    for (int k = RING_KEEP; k < nchunks; ++k) {
       mbar_wait(bar_full + ring, ring_ph);
       const int l = k * RING_R + tid;
       if (l < L) {
@@ -137,11 +212,40 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] -= (double)a[j] * w;
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + ring);
       if (++ring == nslots) { ring = 0; ring_ph ^= 1; }
     }
+    // cross-lane sum of 8 values: halve the number of live values at every butterfly level
+    // (18 shuffles instead of 80); lane l ends up holding component (l >> 2) & 7 summed over the warp
+    if (!(RING_EXP & 8)) {
+      double v4[4], v2[2], v1;
+      {
+        const bool up = lane & 16;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = warp_sum(acc[j]);
-    if (lane == 0) {
+        for (int j = 0; j < 4; ++j) {
+          const double send = up ? acc[j] : acc[j + 4], keepv = up ? acc[j + 4] : acc[j];
+          v4[j] = keepv + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+      }
+      {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const double send = up ? v4[j] : v4[j + 2], keepv = up ? v4[j + 2] : v4[j];
+          v2[j] = keepv + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+      }
+      {
+        const bool up = lane & 4;
+        const double send = up ? v2[0] : v2[1], keepv = up ? v2[1] : v2[0];
+        v1 = keepv + __shfl_xor_sync(0xffffffffu, send, 4);
+      }
+      v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+      v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+      // component index held by this lane: bit4 -> +4, bit3 -> +2, bit2 -> +1
+      if ((lane & 3) == 0) s_red[wid * 8 + ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)] = v1;
+    } else if (lane == 0) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) s_red[wid * 8 + j] = acc[j];
     }
@@ -151,30 +255,31 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
       double n0 = 0.0, n1 = 0.0;
 #pragma unroll
       for (int w = 0; w < RING_CW; w += 2) { n0 += s_red[w * 8 + k]; n1 += s_red[(w + 1) * 8 + k]; }  // fixed order
-      const double mk = cs_update(flags, k, lane, n0 + n1, B.sv, mu, alpha, beta, cv + (size_t)CV_STRIDE * c,
-                                  part + 4 * (size_t)c, vin_slot);
+      const double mk = (RING_EXP & 2) ? n0 + n1 + B.sv[k]
+                                       : cs_update(flags, k, lane, n0 + n1, B.sv, mu, alpha, beta, cv + (size_t)CV_STRIDE * c,
+                                                   part + 4 * (size_t)c, vin_slot);
       if (lane < 8) s_m[k] = mk;
     }
     named_bar_sync<RING_CW * 32>(1);
     double m[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) m[j] = s_m[j];
-    int r = 0, slot = ring0;
-    for (int k = 0; k < nchunks; ++k) {
-      const int l = k * RING_R + tid;
-      if (l < L) {
-        while (l >= pre[r + 1]) ++r;
-        const size_t pos = (size_t)beg[r] + (size_t)(l - pre[r]);
-        JT a[8];
-        ldrow_shared(s_rows + 8 * ((size_t)slot * RING_R + tid), a);
-        double s = 0.0;
+    if (!(RING_EXP & 1)) {
+      RingSteps<JT, RING_KEEP>::pass_a(keep, pos, m, sig);
+      int r = 0;
+      for (int k = RING_KEEP; k < nchunks; ++k) {
+        const int l = k * RING_R + tid;
+        if (l < L) {
+          while (l >= pre[r + 1]) ++r;
+          const size_t p = (size_t)beg[r] + (size_t)(l - pre[r]);
+          JT a[8];
+          ldrow(Jc_B + 8 * p, a);
+          double s0 = 0.0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s += (double)a[j] * m[j];
-        sig[pos] = s;
+          for (int j = 0; j < 8; ++j) s0 += (double)a[j] * m[j];
+          sig[p] = s0;
+        }
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_empty + slot);
-      if (++slot == nslots) slot = 0;
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_cempty + cb);
