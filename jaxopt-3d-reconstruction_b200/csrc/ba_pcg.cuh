@@ -298,8 +298,15 @@ k_pcg_verify(int C, SolverState* __restrict__ st, const double* __restrict__ par
 // BACKSUB: phase 2 instead does v_p = Vinv_p (g_p - t_p) -> vp; part[2*chunk] = v_p.g_p, [+1] = |v_p|^2
 // do_scalars bit 0: block 0 first turns the dot partials of the previous k_cs into alpha/beta/convergence;
 // bit 1: run even if the PCG-finished flag is set (plain matvec).
-#define PS_T 256
-#define PS_RPT 2
+#ifndef PS_T
+#define PS_T 128
+#endif
+#ifndef PS_RPT
+#define PS_RPT 4
+#endif
+#ifndef PS_OWN
+#define PS_OWN 1  // row -> local point through a shared-memory byte/short map written by the point lanes (no pt_A load)
+#endif
 template <typename JT, bool BACKSUB>
 __global__ void __launch_bounds__(PS_T)
 k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxiter, SolverState* __restrict__ st,
@@ -310,9 +317,11 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
   constexpr int CAP = PS_T * PS_RPT;
   __shared__ double sb[3][CAP];
   __shared__ double sz[3][PS_T];
+  __shared__ unsigned short sown[PS_OWN ? CAP : 1];
   __shared__ double sred[3 * 32];
-  if (!BACKSUB && !(do_scalars & 2) && st->pcg_done) return;
   const int ch = blockIdx.x, tid = threadIdx.x;
+  // CTA-uniform early exit: block 0 of this very launch may set the flag while other CTAs are starting
+  if (!BACKSUB && !(do_scalars & 2) && __syncthreads_or(tid == 0 ? st->pcg_done : 0)) return;
   if (!BACKSUB && (do_scalars & 1) && ch == 0) {
     pcg_scalars(C, it, st, cpart, rtol, maxiter, sred);
     __syncthreads();
@@ -335,7 +344,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
       b[j][0] = b[j][1] = b[j][2] = (JT)0;
       if (i < nrows) {
         dst[j] = __ldg(posB + row);
-        if (!BACKSUB) lp[j] = __ldg(pt_A + row) - p0;
+        if (!BACKSUB && !PS_OWN) lp[j] = __ldg(pt_A + row) - p0;
 #pragma unroll
         for (int k = 0; k < 3; ++k) b[j][k] = __ldg(Jp_A + (size_t)k * N + row);
       }
@@ -360,7 +369,10 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     if (tid < npts) {
       const int p = p0 + tid;
       double t0 = 0, t1 = 0, t2 = 0;
-      for (int i = beg; i < end; ++i) { t0 += sb[0][i]; t1 += sb[1][i]; t2 += sb[2][i]; }
+      for (int i = beg; i < end; ++i) {
+        t0 += sb[0][i]; t1 += sb[1][i]; t2 += sb[2][i];
+        if (!BACKSUB && PS_OWN) sown[i] = (unsigned short)tid;
+      }
       if (BACKSUB) {
         t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
         const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
@@ -380,8 +392,13 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
 #pragma unroll
       for (int j = 0; j < PS_RPT; ++j) {
         const int i = tid + j * PS_T;
-        if (i < nrows)
-          omg[dst[j]] = (double)b[j][0] * sz[0][lp[j]] + (double)b[j][1] * sz[1][lp[j]] + (double)b[j][2] * sz[2][lp[j]];
+        if (i < nrows) {
+          int q = PS_OWN ? (int)sown[i] : lp[j];
+#ifdef PS_DEBUG
+          if (q < 0 || q >= npts || dst[j] < 0) { printf("k_ps: ch %d tid %d i %d q %d npts %d nrows %d dst %d\n", ch, tid, i, q, npts, nrows, dst[j]); q = 0; }
+#endif
+          omg[dst[j]] = (double)b[j][0] * sz[0][q] + (double)b[j][1] * sz[1][q] + (double)b[j][2] * sz[2][q];
+        }
       }
     }
   } else {

@@ -1,6 +1,7 @@
 // Shared device helpers for the b200ba kernels (sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdio.h>
 #include <stdint.h>
 
 #define TAB_STRIDE 32  // doubles per camera-table row (256 B, sector aligned)
