@@ -59,7 +59,7 @@ struct b200ba_plan {
   size_t jsz = 8;
   // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
-  int32_t *posB = nullptr;                                           // A row -> B position
+  int32_t *posB = nullptr, *posA = nullptr;                          // A row -> B position; B position -> A row (padding: N)
   int32_t *pt_ptr = nullptr;                                         // A: CSR by point
   int32_t *camtab = nullptr, *cam_order = nullptr;                   // B: per-camera run tables; cameras by descending rows
   int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
@@ -69,11 +69,12 @@ struct b200ba_plan {
   int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
   int nchunks = 0, nPB = 1, block_rows = 0, max_cam_rows = 0, stash_rows = 0;
   size_t stash_bytes = 0;
-  double2* obs_ps = nullptr;
+  int32_t* pt_B = nullptr;   // point of every B row (padding rows: -1)
+  double2* obs_B = nullptr;  // observations in B order
+  void* rec_A = nullptr;     // 32 B row records {b, r} in A order (K1 -> point blocks)
   // linearisation
   void *Jp_ps = nullptr, *Jc_B = nullptr;
-  double *r_ps = nullptr, *r_B = nullptr, *w_B = nullptr, *beta_B = nullptr, *sig = nullptr, *omg = nullptr;
-  double *tab = nullptr, *tab_trial = nullptr;
+  double *r_B = nullptr, *w_B = nullptr, *beta_B = nullptr, *sig = nullptr, *omg = nullptr;
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
   double* cv = nullptr;  // PCG vectors, camera-major records (ba_pcg.cuh)
@@ -165,6 +166,15 @@ __global__ void k_posB(int64_t N, const int32_t* __restrict__ permBA, const int6
   const int64_t k = key_sorted[j];
   posB[permBA[j]] = run_start[k] + (int32_t)(j - runptr_u[k]);
 }
+__global__ void k_fill_i32(int64_t n, int32_t v, int32_t* __restrict__ a) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = v;
+}
+__global__ void k_scatter_i32(int64_t N, const int32_t* __restrict__ idx, const int32_t* __restrict__ src,
+                              int32_t* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) dst[idx[i]] = src[i];
+}
 __global__ void k_gather_i32(int64_t N, const int32_t* __restrict__ idx, const int32_t* __restrict__ src,
                              int32_t* __restrict__ dst) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -190,12 +200,12 @@ __global__ void k_check_range(int64_t N, const int32_t* __restrict__ a, int hi, 
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < N && (a[i] < 0 || a[i] >= hi)) *bad = 1;
 }
-__global__ void k_permute_obs(int64_t N, const int32_t* __restrict__ order_ps, const double* __restrict__ obs,
-                              double2* __restrict__ out) {
+__global__ void k_permute_obs(int64_t N, const int32_t* __restrict__ order_ps, const int32_t* __restrict__ posB,
+                              const double* __restrict__ obs, double2* __restrict__ out_B) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < N) {
     const int64_t o = order_ps[i];
-    out[i] = make_double2(obs[2 * o], obs[2 * o + 1]);
+    out_B[posB[i]] = make_double2(obs[2 * o], obs[2 * o + 1]);
   }
 }
 
@@ -236,9 +246,8 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   int rc = 0;
 #define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
   A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(posB, N)
-  A(pt_ptr, P + 1) A(obs_ps, N) A(r_ps, N)
+  A(pt_ptr, P + 1)
   A(camtab, (size_t)C * (((p->nPB + 3) & ~3) + ((p->nPB + 4) & ~3))) A(cam_order, C) A(tickets, 2)
-  A(tab, (size_t)C * TAB_STRIDE) A(tab_trial, (size_t)C * TAB_STRIDE)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
   A(cv, (size_t)C * CV_STRIDE) A(y, (size_t)C * 8 + 8)
@@ -246,7 +255,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
   p->lin_scal = p->gc + (size_t)C * 8;
-  p->nblkN = (int)cdiv(N, RJ_THREADS); p->nblkP = (int)cdiv(P, 256);
+  p->nblkN = 0; p->nblkP = (int)cdiv(P, 256);
   A(part, 4 * (size_t)C + 16) A(part2, 4 * (size_t)C + 16)
   A(scal, 32) A(st, 1)
 #undef A
@@ -373,6 +382,19 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       *arr[i] = (double*)q;
       cudaMemset(q, 0, nb_rows * sizeof(double));
     }
+    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
+      p->allocs.push_back(q); p->pt_B = (int32_t*)q;
+      k_fill_i32<<<cdiv((int64_t)nb_rows, 256), 256, 0, s>>>((int64_t)nb_rows, -1, p->pt_B);
+      if (N) k_scatter_i32<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->pt_ps, p->pt_B);
+    } else bad_alloc = 1;
+    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(double2)) == cudaSuccess) { p->allocs.push_back(q); p->obs_B = (double2*)q; cudaMemsetAsync(q, 0, nb_rows * sizeof(double2), s); } else bad_alloc = 1;
+    if (!bad_alloc && cudaMalloc(&q, ((size_t)N + 1) * 32) == cudaSuccess) { p->allocs.push_back(q); p->rec_A = q; } else bad_alloc = 1;
+    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
+      p->allocs.push_back(q); p->posA = (int32_t*)q;
+      k_fill_i32<<<cdiv((int64_t)nb_rows, 256), 256, 0, s>>>((int64_t)nb_rows, (int32_t)N, p->posA);
+      if (N) k_invert_perm<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->posA);
+    } else bad_alloc = 1;
+    cudaStreamSynchronize(s);
     if (bad_alloc) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: B-order row arrays"); }
     // generic camera kernel: shared-memory row stash; ring kernel: slots of RING_R rows
     size_t cap = 96 * 1024;
@@ -459,7 +481,7 @@ extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
 extern "C" int b200ba_plan_set_observations(b200ba_plan* p, const double* obs_xy, void* stream_) {
   if (!p || (p->N > 0 && !obs_xy)) FAIL(B200BA_EINVAL, "set_observations: null");
   cudaStream_t s = (cudaStream_t)stream_;
-  if (p->N) LAUNCH(k_permute_obs, cdiv(p->N, 256), 256, 0, s, p->N, p->order_ps, obs_xy, p->obs_ps);
+  if (p->N) LAUNCH(k_permute_obs, cdiv(p->N, 256), 256, 0, s, p->N, p->order_ps, p->posB, obs_xy, p->obs_B);
   CK(cudaGetLastError());
   return B200BA_OK;
 }
@@ -529,13 +551,11 @@ struct Ops {
                        cudaStream_t s) {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
-    PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(C, 128), 128, 0, s, C, cam8, k3, p->tab);
-    if (N) {
-      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), p->nblkN, RJ_THREADS, 0, s, N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab, pts, inv_w2,
-             p->posB, p->r_ps, (JT*)p->Jp_ps, (JT*)p->Jc_B, p->r_B, p->partN);
-    }
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, p->lin_scal, 0);
-    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const JT*)p->Jp_ps, p->r_ps, p->V, p->gp, p->partN);
+    PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
+            inv_w2, (JT*)p->Jc_B, p->r_B, (RowRec<JT>*)p->rec_A, p->part);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 1, 1, p->lin_scal, 0);
+    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec<JT>*)p->rec_A,
+                  (JT*)p->Jp_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
     PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
@@ -675,11 +695,9 @@ struct Ops {
 
   static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
                   double* out_dev, cudaStream_t s) {
-    PLAUNCH(p, PC_OTHER, k_cam_table, cdiv(p->C, 128), 128, 0, s, p->C, cam8, k3, p->tab_trial);
-    if (p->N)
-      PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->nblkN, RJ_THREADS, 0, s, p->N, p->cam_ps, p->pt_ps, p->obs_ps, p->tab_trial, pts,
-             inv_w2, p->posB, nullptr, nullptr, nullptr, nullptr, p->partN);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkN, 1, 1, out_dev, 0);
+    PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
+            inv_w2, nullptr, nullptr, nullptr, p->part);
+    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, p->C, 1, 1, out_dev, 0);
     return 0;
   }
 };
@@ -727,7 +745,7 @@ extern "C" int b200ba_residual_jacobian(b200ba_plan* p, const double* cam8, cons
   cudaStream_t s = (cudaStream_t)stream_;
   const int64_t N = p->N;
   if (N) {
-    if (r) LAUNCH((k_unpermute_rows<double>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->r_ps, (size_t)0, 1, r);
+    if (r) LAUNCH(k_unpermute_rec_r, cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->rec_A, p->jac_f32 ? 2 : 3, r);
     if (p->jac_f32) {
       if (Jc) LAUNCH((k_unpermute_jc<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->posB, (const float*)p->Jc_B, Jc);
       if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, (size_t)N, 3, Jp);

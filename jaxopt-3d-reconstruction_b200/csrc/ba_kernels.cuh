@@ -100,6 +100,31 @@ struct CamRuns {
   }
 };
 
+// 32 B row records {b[3], r} of the A order: one 256-bit store / load each (one request per sector)
+template <typename JT> struct RowRec;
+template <> struct __align__(32) RowRec<float> { float b[3]; float pad0; double r; double pad1; };
+template <> struct __align__(32) RowRec<double> { double b[3]; double r; };
+static_assert(sizeof(RowRec<float>) == 32 && sizeof(RowRec<double>) == 32, "row record = one 32 B sector");
+__device__ __forceinline__ void st_rec(RowRec<float>* p, const double* b, double r) {
+  const unsigned lo = (unsigned)__double2loint(r), hi = (unsigned)__double2hiint(r);
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(__float_as_uint((float)b[0])),
+               "r"(__float_as_uint((float)b[1])), "r"(__float_as_uint((float)b[2])), "r"(0u), "r"(lo), "r"(hi), "r"(0u), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void st_rec(RowRec<double>* p, const double* b, double r) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(b[0]), "d"(b[1]), "d"(b[2]), "d"(r) : "memory");
+}
+__device__ __forceinline__ void ld_rec(const RowRec<float>* p, double* b, double& r) {
+  float v[8];
+  ld256(reinterpret_cast<const float*>(p), v);
+  b[0] = v[0]; b[1] = v[1]; b[2] = v[2];
+  r = __hiloint2double((int)__float_as_uint(v[5]), (int)__float_as_uint(v[4]));
+}
+__device__ __forceinline__ void ld_rec(const RowRec<double>* p, double* b, double& r) {
+  double v[4];
+  ld256(reinterpret_cast<const double*>(p), v);
+  b[0] = v[0]; b[1] = v[1]; b[2] = v[2]; r = v[3];
+}
+
 // ---------------------------------------------------------------- K0: camera tables
 __global__ void k_cam_table(int C, const double* __restrict__ cam8, const double* __restrict__ k3,
                             double* __restrict__ tab) {
@@ -107,71 +132,59 @@ __global__ void k_cam_table(int C, const double* __restrict__ cam8, const double
   if (c < C) build_cam_table(cam8 + 8 * c, k3 + 3 * c, tab + (size_t)TAB_STRIDE * c);
 }
 
-// ---------------------------------------------------------------- K1: residual + Jacobian rows
-// One thread per observation in ps order.  The camera of every row differs, so the 26-double
-// camera tables are fetched COOPERATIVELY: for each of the warp's 32 rows the whole warp issues one
-// coalesced 256 B load of that row's table into shared memory (row stride 33 doubles: conflict-free
-// per-lane reads afterwards) instead of 26 scattered 8 B loads per lane.
-// Writes r and the point part of the Jacobian row in A order (SoA, coalesced) and the camera part at the
-// row's B position (32/64 B aligned scatter = whole sectors, inside the L2 window of the point block),
-// which the camera-side kernels then stream.  cost_part[block] = sum r^2 of the block.
-#define RJ_THREADS 128
-#define RJ_TSTRIDE 33
+// ---------------------------------------------------------------- K0+K1: residual + Jacobian rows
+// One CTA per camera walks the camera's rows in B order (runs of consecutive points inside a point
+// block).  The 26-double camera table is built once per CTA in shared memory (every lane reads the same
+// entries: broadcasts), the only gather is the 24 B point, and it stays inside the block's point range
+// (L2-resident).  Per row it writes, coalesced in B order, the camera part of the Jacobian row
+// (8 x JT) and r, and SCATTERS one 32 B record {b (3 x JT), r} to the row's A position (a whole sector,
+// inside the L2 window of the point block) from which k_point_blocks builds V_p, g_p and the SoA point part.
+// cost_part[c] = sum r^2 over the camera.  WITH_JAC = false: trial cost only (reads 20 B/row, writes nothing).
+#define RJ_THREADS 256
 template <typename JT, bool WITH_JAC>
 __global__ void __launch_bounds__(RJ_THREADS)
-k_resjac(int64_t N, const int32_t* __restrict__ cam_ps, const int32_t* __restrict__ pt_ps,
-         const double2* __restrict__ obs_ps, const double* __restrict__ tab,
-         const double* __restrict__ pts, double inv_w2, const int32_t* __restrict__ posB,
-         double* __restrict__ r_ps, JT* __restrict__ Jp_ps,
-         JT* __restrict__ Jc_B, double* __restrict__ r_B, double* __restrict__ cost_part) {
+k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
+         const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
+         const double* __restrict__ pts, double inv_w2, JT* __restrict__ Jc_B, double* __restrict__ r_B,
+         RowRec<JT>* __restrict__ rec_A, double* __restrict__ cost_part) {
+  __shared__ CamRuns runs;
+  __shared__ double T[TAB_STRIDE];
   __shared__ double sm[32];
-  __shared__ double stab[RJ_THREADS / 32][32][RJ_TSTRIDE];
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const bool act = i < N;
-  const int c = act ? __ldg(cam_ps + i) : 0;
-#pragma unroll 8
-  for (int rr = 0; rr < 32; ++rr) {
-    const int cr = __shfl_sync(0xffffffffu, c, rr);
-    stab[wid][rr][lane] = __ldg(tab + (size_t)TAB_STRIDE * cr + lane);
-  }
-  __syncwarp();
+  const int c = blockIdx.x;
+  if (threadIdx.x == RJ_THREADS - 1) build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
+  const int L = runs.load(c, nPB, camtab);  // includes the __syncthreads that publishes T
   double v[1] = {0.0};
-  if (act) {
-    const int p = __ldg(pt_ps + i);
-    const double* T = &stab[wid][lane][0];
-    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1),
-                 Z = __ldg(pts + 3 * (size_t)p + 2);
-    const double2 o = __ldg(obs_ps + i);
+  int run = 0;
+  for (int l = threadIdx.x; l < L; l += RJ_THREADS) {
+    const size_t j = runs.locate(l, run);
+    const int p = __ldg(pt_B + j);
+    if (p < 0) continue;  // padding row of a run
+    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
+    const double2 o = __ldg(obs_B + j);
     const Proj pr = project(T, X, Y, Z);
     const double dx = pr.u - o.x, dy = pr.v - o.y;
     const double r = (dx * dx + dy * dy) * inv_w2;
-    v[0] = r * r;
+    v[0] += r * r;
     if (WITH_JAC) {
       double a[8], b[3];
       jac_row(T, pr, X, Y, Z, 2.0 * dx * inv_w2, 2.0 * dy * inv_w2, a, b);
-      r_ps[i] = r;
-#pragma unroll
-      for (int k = 0; k < 3; ++k) jput<JT>(Jp_ps, (size_t)N, k, (size_t)i, b[k]);
-      const int64_t j = __ldg(posB + i);
       store8<JT>(Jc_B + 8 * j, a);
       r_B[j] = r;
-    } else if (r_ps) {
-      r_ps[i] = r;
+      st_rec(rec_A + __ldg(posA + j), b, r);
     }
   }
   block_sum<1>(v, sm);
-  if (threadIdx.x == 0) cost_part[blockIdx.x] = v[0];
+  if (threadIdx.x == 0) cost_part[c] = v[0];
 }
 
 // ---------------------------------------------------------------- K2a: 3x3 point blocks
-// One thread per point walks its (short) ps run.  V_p = sum b b^T (6 unique), g_p = sum b r.
+// One thread per point walks its (short) A run of 32 B row records.  V_p = sum b b^T (6 unique),
+// g_p = sum b r; also writes the point part of the rows as SoA arrays (what the PCG point kernel streams).
 // part[2*block+0] = sum |g_p|^2, part[2*block+1] = max diag V.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __restrict__ Jp_ps,
-               const double* __restrict__ r_ps, double* __restrict__ V, double* __restrict__ gp,
-               double* __restrict__ part) {
+k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const RowRec<JT>* __restrict__ rec_A,
+               JT* __restrict__ Jp_ps, double* __restrict__ V, double* __restrict__ gp, double* __restrict__ part) {
   __shared__ double sm[32];
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   double g2[1] = {0.0};
@@ -179,14 +192,22 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __
   if (p < P) {
     double v[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
     const int e = pt_ptr[p + 1];
-    for (int i = pt_ptr[p]; i < e; ++i) {
-      double b[3];
-      #pragma unroll
-      for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, (size_t)i);
-      const double r = __ldg(r_ps + i);
-      v[0] += b[0] * b[0]; v[1] += b[0] * b[1]; v[2] += b[0] * b[2];
-      v[3] += b[1] * b[1]; v[4] += b[1] * b[2]; v[5] += b[2] * b[2];
-      g[0] += b[0] * r; g[1] += b[1] * r; g[2] += b[2] * r;
+    for (int i0 = pt_ptr[p]; i0 < e; i0 += 4) {  // 4 records in flight per thread, accumulated in row order
+      double b[4][3], r[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        b[u][0] = b[u][1] = b[u][2] = 0.0; r[u] = 0.0;
+        if (i0 + u < e) ld_rec(rec_A + i0 + u, b[u], r[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (i0 + u >= e) break;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) jput<JT>(Jp_ps, N, k, (size_t)(i0 + u), b[u][k]);
+        v[0] += b[u][0] * b[u][0]; v[1] += b[u][0] * b[u][1]; v[2] += b[u][0] * b[u][2];
+        v[3] += b[u][1] * b[u][1]; v[4] += b[u][1] * b[u][2]; v[5] += b[u][2] * b[u][2];
+        g[0] += b[u][0] * r[u]; g[1] += b[u][1] * r[u]; g[2] += b[u][2] * r[u];
+      }
     }
 #pragma unroll
     for (int k = 0; k < 6; ++k) V[6 * (size_t)p + k] = v[k];
@@ -204,10 +225,12 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const JT* __
 }
 
 // ---------------------------------------------------------------- K2b: 8x8 camera blocks
-// One CTA per camera streams its B-order runs.  Each thread keeps 36 + 8 fp64 accumulators; ordered
-// CTA reduction.  If beta_B != nullptr the rows are weighted: out = -sum beta_i a a^T and
-// -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs); otherwise
-// U_c = sum a a^T and g_c = sum a r.
+// One CTA per camera streams its B-order runs.  If beta_B != nullptr the rows are weighted:
+// out = -sum beta_i a a^T and -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs);
+// otherwise U_c = sum a a^T and g_c = sum a r.
+// (An fp64 tensor-core version — one mma.sync.m8n8k4.f64 per 4 rows, the SYRK mapped 1:1 onto the DMMA tile — was
+// measured at ~2.4 TFLOP/s on B200 and ran 2.3x SLOWER than this FMA kernel, see profiles/ncu_r1_v5_summary.md; a
+// variant with 4 lanes per row and 36 accumulators per lane was slower too: 146 us vs 114 us.)
 template <typename JT>
 __global__ void __launch_bounds__(256)
 k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__ Jc_B,
@@ -307,16 +330,27 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
   const double z1 = vi[1] * g0 + vi[3] * g1 + vi[4] * g2;
   const double z2 = vi[2] * g0 + vi[4] * g1 + vi[5] * g2;
   const int e = pt_ptr[p + 1];
-  for (int i = pt_ptr[p]; i < e; ++i) {
-    double b[3];
-    #pragma unroll
-    for (int k = 0; k < 3; ++k) b[k] = jget<JT>(Jp_ps, N, k, (size_t)i);
-    const int j = __ldg(posB + i);
-    w_B[j] = b[0] * z0 + b[1] * z1 + b[2] * z2;
-    const double t0 = vi[0] * b[0] + vi[1] * b[1] + vi[2] * b[2];
-    const double t1 = vi[1] * b[0] + vi[3] * b[1] + vi[4] * b[2];
-    const double t2 = vi[2] * b[0] + vi[4] * b[1] + vi[5] * b[2];
-    beta_B[j] = b[0] * t0 + b[1] * t1 + b[2] * t2;
+  for (int i0 = pt_ptr[p]; i0 < e; i0 += 4) {  // 4 rows in flight per thread
+    double b[4][3];
+    int j[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      j[u] = -1;
+      if (i0 + u < e) {
+        j[u] = __ldg(posB + i0 + u);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) b[u][k] = jget<JT>(Jp_ps, N, k, (size_t)(i0 + u));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (j[u] < 0) continue;
+      w_B[j[u]] = b[u][0] * z0 + b[u][1] * z1 + b[u][2] * z2;
+      const double t0 = vi[0] * b[u][0] + vi[1] * b[u][1] + vi[2] * b[u][2];
+      const double t1 = vi[1] * b[u][0] + vi[3] * b[u][1] + vi[4] * b[u][2];
+      const double t2 = vi[2] * b[u][0] + vi[4] * b[u][1] + vi[5] * b[u][2];
+      beta_B[j[u]] = b[u][0] * t0 + b[u][1] * t1 + b[u][2] * t2;
+    }
   }
 }
 

@@ -579,3 +579,10 @@ __global__ void k_unpermute_jc(int64_t N, const int32_t* __restrict__ order_ps, 
   const int64_t o = order_ps[i], j = posB[i];
   for (int k = 0; k < 8; ++k) out[o * 8 + k] = (double)Jc_B[j * 8 + k];
 }
+
+// residuals back in the caller's order from the A-order row records (4 doubles each; r at double index r_off)
+__global__ void k_unpermute_rec_r(int64_t N, const int32_t* __restrict__ order_ps, const double* __restrict__ rec, int r_off,
+                                  double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) out[order_ps[i]] = rec[4 * i + r_off];
+}
