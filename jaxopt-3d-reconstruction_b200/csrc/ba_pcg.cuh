@@ -320,6 +320,12 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
   __shared__ unsigned short sown[PS_OWN ? CAP : 1];
   __shared__ double sred[3 * 32];
   const int ch = blockIdx.x, tid = threadIdx.x;
+  // chunk geometry first: these loads overlap the round trip of the finished-flag below
+  int r0 = 0, nrows = 0, p0 = 0, npts = 0;
+  if (ch < nchunks) {
+    r0 = __ldg(chunk_row + ch); nrows = __ldg(chunk_row + ch + 1) - r0;
+    p0 = __ldg(chunk_pt + ch); npts = __ldg(chunk_pt + ch + 1) - p0;
+  }
   // CTA-uniform early exit: block 0 of this very launch may set the flag while other CTAs are starting
   if (!BACKSUB && !(do_scalars & 2) && __syncthreads_or(tid == 0 ? st->pcg_done : 0)) return;
   if (!BACKSUB && (do_scalars & 1) && ch == 0) {
@@ -327,8 +333,6 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     __syncthreads();
   }
   if (ch >= nchunks) return;
-  const int r0 = chunk_row[ch], nrows = chunk_row[ch + 1] - r0;
-  const int p0 = chunk_pt[ch], npts = chunk_pt[ch + 1] - p0;
   double acc[2] = {0.0, 0.0};
   if (nrows <= CAP) {
     double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;

@@ -17,7 +17,7 @@ if [ -z "$SKIP_NCU" ]; then
   timeout 300 $CMD > $out/plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 500 --csv --log-file $out/launches.csv $CMD > $out/ncu_list.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
-      -k regex:"k_cs_ring|k_ps" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
+      -k regex:"k_cs_ring|k_ps|k_cs<" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
       -k regex:"k_resjac|k_cam_blocks|k_point" -s 5 -c 7 -f -o $out/prof_lin $CMD > $out/ncu_full_lin.log 2>&1
   echo "ncu exit $?"; ls -la $out
