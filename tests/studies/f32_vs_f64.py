@@ -1,6 +1,6 @@
 """Default (fp32-stored rows, rtol 1e-10) vs fp64-row (rtol 1e-12) GPU trajectories at a large shape."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import b200ba
 shape = sys.argv[1] if len(sys.argv) > 1 else "venice1778"

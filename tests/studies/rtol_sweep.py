@@ -1,7 +1,7 @@
 """Parity vs PCG tolerance / Jacobian storage: max relative deviation of the per-iteration cost from
 the exact-solve oracle, and PCG iterations spent.  GPU required."""
 import sys, os, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import b200ba
 from oracle import ba_oracle as bo
@@ -13,8 +13,8 @@ for shape in sys.argv[1:] or ["small", "ladybug49"]:
     ref = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width)
     rl = np.array(ref.trace.loss)
     print(f"{shape}: oracle {ref.iter_num} its in {time.time()-t:.1f}s", flush=True)
-    for f32 in (False, True):
-        for rtol in (1e-4, 1e-6, 1e-8, 1e-10, 1e-12):
+    for f32 in (True,):
+        for rtol in (1e-7, 1e-8, 1e-9, 1e-10, 1e-11):
             ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=f32, pcg_rtol=rtol)
             prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
             p, st = ba.optimize(x0, prob, None, k3, None)
