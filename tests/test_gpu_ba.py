@@ -130,3 +130,64 @@ def test_fp32_rows_track_fp64_rows_at_scale():
     ra = bo.rms_reprojection_px(pa, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
     rb = bo.rms_reprojection_px(pb, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
     assert ra == pytest.approx(rb, rel=1e-4)
+
+
+@pytest.mark.parametrize("jac_f32", [True, False])
+@pytest.mark.parametrize("cpn", [(3, 4000, 11500), (2, 6000, 12000)])
+def test_heavy_cameras_take_the_tail_and_fallback_paths(cpn, jac_f32):
+    """Cameras with more rows than a thread's register stash (3072 fp32 / 1536 fp64 rows: ring tail path,
+    rows re-read in pass A) and more than the whole ring holds (5120 / 3072 rows: generic camera kernel)
+    must give the same trajectory as the exact oracle."""
+    C, P, N = cpn
+    sc = b200ba.synth.make_ba_scene(C=C, P=P, N=N, seed=2)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=jac_f32)
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+    ref = bo.lm_solve(x0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    rms = bo.rms_reprojection_px(params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    rms_ref = bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    assert rms == pytest.approx(rms_ref, rel=1e-4)
+
+
+def test_point_block_size_does_not_matter(monkeypatch):
+    """The point-block size only changes WHERE rows live (run boundaries, padding) and which thread slot sums
+    which row of a camera; 1 block and ~16 blocks must agree at the level a PCG solve to rtol 1e-10 pins the
+    step (measured 2.5e-7), far inside the 1e-5 parity bar."""
+    sc, ba, x0, k3 = _setup("ladybug49", jac_f32=True)
+    out = []
+    for rows in ("1000000", "2048"):
+        monkeypatch.setenv("B200BA_BLOCK_ROWS", rows)
+        out.append(ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None))
+    (pa, sa), (pb, sb) = out
+    assert sa.iter_num == sb.iter_num
+    np.testing.assert_allclose(sa.loss_trajectory, sb.loss_trajectory, rtol=2e-6)
+    np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
+
+
+def test_schur_matvec_matches_dense_schur_complement():
+    """b200ba_schur_matvec (camera head -> point kernel -> camera tail) against S formed densely by the oracle's
+    formulas: S = U + mu I - W (V + mu I)^-1 W^T."""
+    sc, ba, x0, k3 = _setup("small")
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    K = b200ba.BAKernels(prob, sc.avg_cam_width)
+    cam8, k3d, pts = _dev_params(x0, k3, sc.C)
+    K.linearize(cam8, k3d, pts)
+    ci, pi = sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)
+    r, _, a, b = bo.ba_eval(x0, sc.C, ci, pi, sc.obs, k3, sc.avg_cam_width ** 2)
+    U = np.zeros((sc.C, 8, 8)); np.add.at(U, ci, a[:, :, None] * a[:, None, :])
+    V = np.zeros((sc.P, 3, 3)); np.add.at(V, pi, b[:, :, None] * b[:, None, :])
+    mu = 1e-6 * max(np.einsum("cii->ci", U).max(), np.einsum("pii->pi", V).max())
+    Vinv = np.linalg.inv(V + mu * np.eye(3))
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((sc.C, 8))
+    s = np.einsum("nk,nk->n", a, x[ci])                      # a_i . x_c
+    t = np.zeros((sc.P, 3)); np.add.at(t, pi, b * s[:, None])  # sum b sigma
+    z = np.einsum("pij,pj->pi", Vinv, t)
+    w = np.einsum("nk,nk->n", b, z[pi])
+    y = np.einsum("cij,cj->ci", U + mu * np.eye(8), x)
+    np.add.at(y, ci, -a * w[:, None])
+    K.schur_prepare(mu)
+    yg = K.schur_matvec(torch.from_numpy(x).cuda()).cpu().numpy()
+    np.testing.assert_allclose(yg, y, rtol=1e-9, atol=1e-12 * np.abs(y).max())
