@@ -572,11 +572,14 @@ struct Ops {
   // camera-side kernel (see ba_pcg.cuh): flags select matvec tail / vector update / matvec head.
   // vin_slot: which vector of the camera-major PCG record is the matvec input (CV_*).
   static void cs(b200ba_plan* p, int cls, int flags, int vin_slot, cudaStream_t s) {
-    const int fused = CS_C | CS_UX | CS_A;
-    if (p->ring_slots && (flags & fused) == fused && (flags & (CS_INIT | CS_ITER)) && !(flags & (CS_WRITE_Y | CS_READ_Y | CS_IGNORE_DONE))) {
+    const int upd = flags & (CS_INIT | CS_ITER);
+    const bool fused = upd && (flags & ~upd) == (CS_C | CS_UX | CS_A);        // single rank: whole iteration
+    const bool half1 = flags == (CS_C | CS_WRITE_Y);                          // multi-rank: partial sums out
+    const bool half2 = upd && (flags & ~upd) == (CS_READ_Y | CS_UX | CS_A);   // multi-rank: update + next matvec head
+    if (p->ring_slots && (fused || half1 || half2)) {
       const int grid = p->C < p->n_sm ? p->C : p->n_sm;
       PLAUNCH(p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, p->camtab,
-              p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->cv, p->part2);
+              p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->y, p->cv, p->part2);
       return;
     }
     const size_t smem = (flags & CS_C) && (flags & CS_A) ? p->stash_bytes : 0;

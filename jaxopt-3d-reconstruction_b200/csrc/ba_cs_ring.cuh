@@ -20,6 +20,7 @@
 struct __align__(16) RingCam {  // everything about one in-flight camera
   double sv[CV_STRIDE + 128];   // cv record | U_c | Minv_c   (bulk copied)
   int tab[2 * MAXPB + 8];       // run table: beg[nPB] (padded to 4) | pre[nPB+1] (padded to 4)   (bulk copied)
+  double yv[8];                 // multi-rank: the all-reduced partial sums n_c   (bulk copied)
   int cam, pad[3];
 };
 
@@ -41,7 +42,7 @@ template <typename JT> struct RingKeep { static constexpr int N = sizeof(JT) == 
 // Compile-time unrolled per-slot steps of the consumer (recursion instead of `#pragma unroll`: the bodies
 // contain mbarrier wait loops, and the row stash must be indexed by constants to live in registers).
 struct RingCtx {
-  int ring, ring_ph, nslots, nchunks, L, tid, lane;
+  int ring, ring_ph, nslots, nchunks, L, tid, lane, do_c;
   const int *beg, *pre, *run0;
   uint64_t *bar_full, *bar_empty;
 };
@@ -57,11 +58,11 @@ struct RingSteps {
       const int l = k * RING_R + cx.tid;
       if (l < cx.L) {
         ldrow_shared(s_rows + 8 * ((size_t)cx.ring * RING_R + cx.tid), keep[k]);
-        const double w = s_omg[(size_t)cx.ring * RING_R + cx.tid];
+        const double w = cx.do_c ? s_omg[(size_t)cx.ring * RING_R + cx.tid] : 0.0;
         int r = cx.run0[cx.ring];
         while (l >= cx.pre[r + 1]) ++r;
         pos[k] = cx.beg[r] + (l - cx.pre[r]);
-        if (!(RING_EXP & 4)) {
+        if (!(RING_EXP & 4) && cx.do_c) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) acc[j] -= (double)keep[k][j] * w;
         }
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(RING_T, 1)
 k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
           const int32_t* __restrict__ cam_order, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
           double* __restrict__ sig, const double* __restrict__ U, const double* __restrict__ Minv, int vin_slot,
-          double* __restrict__ cv, double* __restrict__ part) {
+          double* __restrict__ y, double* __restrict__ cv, double* __restrict__ part) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   // layout: rows[nslots][RING_R][8] | omega[nslots][RING_R] | cams[RING_NCAM] | sred | sm_m | barriers
   JT* s_rows = reinterpret_cast<JT*>(smem_raw);
@@ -134,7 +135,9 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
         RingCam& B = s_cam[cb];
         const int c = i < 64 ? s_ids[i] : __ldg(cam_order + blockIdx.x + (size_t)i * gridDim.x);
         B.cam = c;
-        mbar_arrive_expect_tx(bar_cfull + cb, (uint32_t)((CV_STRIDE + 128) * sizeof(double) + tab_stride * sizeof(int32_t)));
+        mbar_arrive_expect_tx(bar_cfull + cb, (uint32_t)((CV_STRIDE + 128) * sizeof(double) + tab_stride * sizeof(int32_t) +
+                                                         ((flags & CS_READ_Y) ? 64 : 0)));
+        if (flags & CS_READ_Y) bulk_g2s(B.yv, y + 8 * (size_t)c, 64, bar_cfull + cb);
         bulk_g2s(B.sv, cv + (size_t)CV_STRIDE * c, CV_STRIDE * sizeof(double), bar_cfull + cb);
         bulk_g2s(B.sv + CV_STRIDE, U + 64 * (size_t)c, 64 * sizeof(double), bar_cfull + cb);
         bulk_g2s(B.sv + CV_STRIDE + 64, Minv + 64 * (size_t)c, 64 * sizeof(double), bar_cfull + cb);
@@ -163,14 +166,14 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
             const size_t src = (size_t)beg[r] + (size_t)(lo - pre[r]);
             const size_t dst = (size_t)ring * RING_R + (size_t)(lo - l_lo);
             bulk_g2s(s_rows + 8 * dst, Jc_B + 8 * src, (uint32_t)(hi - lo) * ROWB, bar_full + ring);
-            bulk_g2s(s_omg + dst, omg + src, (uint32_t)(hi - lo) * 8, bar_full + ring);
+            if (flags & CS_C) bulk_g2s(s_omg + dst, omg + src, (uint32_t)(hi - lo) * 8, bar_full + ring);
           }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) first_run = min(first_run, __shfl_xor_sync(0xffffffffu, first_run, o));
         if (lane == 0) {
           s_run0[ring] = first_run;  // published by the arrive below
-          mbar_arrive_expect_tx(bar_full + ring, (uint32_t)(l_hi - l_lo) * (ROWB + 8));
+          mbar_arrive_expect_tx(bar_full + ring, (uint32_t)(l_hi - l_lo) * (ROWB + ((flags & CS_C) ? 8 : 0)));
         }
         if (++ring == nslots) { ring = 0; ring_ph ^= 1; }
       }
@@ -197,7 +200,7 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
     JT keep[RING_KEEP][8];
     int pos[RING_KEEP];
     {
-      RingCtx cx{ring, ring_ph, nslots, nchunks, L, tid, lane, beg, pre, s_run0, bar_full, bar_empty};
+      RingCtx cx{ring, ring_ph, nslots, nchunks, L, tid, lane, flags & CS_C, beg, pre, s_run0, bar_full, bar_empty};
       RingSteps<JT, RING_KEEP>::pass_c(cx, s_rows, s_omg, keep, pos, acc);
       ring = cx.ring; ring_ph = cx.ring_ph;
     }
@@ -205,7 +208,7 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
     for (int k = RING_KEEP; k < nchunks; ++k) {
       mbar_wait(bar_full + ring, ring_ph);
       const int l = k * RING_R + tid;
-      if (l < L) {
+      if (l < L && (flags & CS_C)) {
         JT a[8];
         ldrow_shared(s_rows + 8 * ((size_t)ring * RING_R + tid), a);
         const double w = s_omg[(size_t)ring * RING_R + tid];
@@ -218,7 +221,9 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
     }
     // cross-lane sum of 8 values: halve the number of live values at every butterfly level
     // (18 shuffles instead of 80); lane l ends up holding component (l >> 2) & 7 summed over the warp
-    if (!(RING_EXP & 8)) {
+    if (!(flags & CS_C)) {
+      // multi-rank second half: n_c arrives all-reduced in the camera record
+    } else if (!(RING_EXP & 8)) {
       double v4[4], v2[2], v1;
       {
         const bool up = lane & 16;
@@ -249,16 +254,28 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
 #pragma unroll
       for (int j = 0; j < 8; ++j) s_red[wid * 8 + j] = acc[j];
     }
-    named_bar_sync<RING_CW * 32>(1);
+    if (flags & CS_C) named_bar_sync<RING_CW * 32>(1);
     if (wid == 0) {
       const int k = lane & 7;
       double n0 = 0.0, n1 = 0.0;
+      if (flags & CS_C) {
 #pragma unroll
-      for (int w = 0; w < RING_CW; w += 2) { n0 += s_red[w * 8 + k]; n1 += s_red[(w + 1) * 8 + k]; }  // fixed order
-      const double mk = (RING_EXP & 2) ? n0 + n1 + B.sv[k]
-                                       : cs_update(flags, k, lane, n0 + n1, B.sv, mu, alpha, beta, cv + (size_t)CV_STRIDE * c,
-                                                   part + 4 * (size_t)c, vin_slot);
-      if (lane < 8) s_m[k] = mk;
+        for (int w = 0; w < RING_CW; w += 2) { n0 += s_red[w * 8 + k]; n1 += s_red[(w + 1) * 8 + k]; }  // fixed order
+      } else {
+        n0 = B.yv[k];
+      }
+      if ((flags & CS_WRITE_Y) && lane < 8) y[8 * (size_t)c + k] = n0 + n1;  // multi-rank first half: partial sums out
+      if (flags & (CS_INIT | CS_ITER)) {
+        const double mk = (RING_EXP & 2) ? n0 + n1 + B.sv[k]
+                                         : cs_update(flags, k, lane, n0 + n1, B.sv, mu, alpha, beta, cv + (size_t)CV_STRIDE * c,
+                                                     part + 4 * (size_t)c, vin_slot);
+        if (lane < 8) s_m[k] = mk;
+      }
+    }
+    if (!(flags & CS_A)) {  // no matvec head in this launch: the camera is done
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_cempty + cb);
+      continue;
     }
     named_bar_sync<RING_CW * 32>(1);
     double m[8];
