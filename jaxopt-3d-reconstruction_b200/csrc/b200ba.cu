@@ -115,10 +115,29 @@ enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, 
     if ((p)->prof) { i1_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); (p)->recs.push_back({(cls), i0_, i1_}); } \
   } while (0)
 
+// Stream-ordered allocation from the device's default memory pool (release threshold = never): after the first
+// plan a new plan's ~40 workspaces are carved out of memory the pool already holds (a plan is rebuilt per problem).
+static cudaStream_t g_alloc_stream = nullptr;
+static cudaError_t pool_malloc(void** q, size_t bytes) {
+  static bool init = false;
+  if (!init) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      uint64_t thr = UINT64_MAX;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    init = true;
+  }
+  return cudaMallocAsync(q, bytes ? bytes : 1, g_alloc_stream);
+}
+static void pool_free(void* q) { if (q) cudaFreeAsync(q, g_alloc_stream); }
+
 template <typename T>
 static int dalloc(b200ba_plan* p, T** ptr, size_t n) {
   void* q = nullptr;
-  CK(cudaMalloc(&q, (n ? n : 1) * sizeof(T)));
+  CK(pool_malloc(&q, (n ? n : 1) * sizeof(T)));
   p->allocs.push_back(q);
   *ptr = (T*)q;
   return 0;
@@ -220,6 +239,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   if (!out || C <= 0 || P < 0 || N < 0 || N >= (1LL << 31)) FAIL(B200BA_EINVAL, "plan_create: bad sizes");
   if (N > 0 && (!cam_idx || !pt_idx)) FAIL(B200BA_EINVAL, "plan_create: null index arrays");
   cudaStream_t s = (cudaStream_t)stream_;
+  g_alloc_stream = s;
   const bool vtime = getenv("B200BA_VERBOSE") != nullptr;
   auto t_last = std::chrono::steady_clock::now();
   auto lap = [&](const char* what) {
@@ -261,7 +281,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
 #undef A
   {
     void* q = nullptr;
-    if (cudaMalloc(&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
+    if (pool_malloc((void**)&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
     p->allocs.push_back(q); p->Jp_ps = q;
   }
   if (cudaMallocHost((void**)&p->st_host, sizeof(SolverState)) != cudaSuccess ||
@@ -282,21 +302,21 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int32_t *vals = nullptr, *permBA = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
-    cudaMalloc(&bad, sizeof(int));
+    pool_malloc((void**)&bad, sizeof(int));
     cudaMemsetAsync(bad, 0, sizeof(int), s);
     LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, cam_idx, C, bad);
     LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, pt_idx, P, bad);
     int bad_h = 0;
     cudaMemcpyAsync(&bad_h, bad, sizeof(int), cudaMemcpyDeviceToHost, s);
     cudaStreamSynchronize(s);
-    cudaFree(bad);
+    pool_free(bad);
     if (bad_h) { b200ba_plan_destroy(p); FAIL(B200BA_EINVAL, "plan_create: index out of range"); }
-    cudaMalloc(&keys, N * sizeof(int64_t)); cudaMalloc(&keys2, N * sizeof(int64_t));
-    cudaMalloc(&vals, N * sizeof(int32_t)); cudaMalloc(&permBA, N * sizeof(int32_t));
+    pool_malloc((void**)&keys, N * sizeof(int64_t)); pool_malloc((void**)&keys2, N * sizeof(int64_t));
+    pool_malloc((void**)&vals, N * sizeof(int32_t)); pool_malloc((void**)&permBA, N * sizeof(int32_t));
     const int nb = bits_for((int64_t)P * C + C);
     const int nbB = bits_for((int64_t)nruns + 1);
     cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
-    cudaMalloc(&tmp, tmp_bytes);
+    pool_malloc((void**)&tmp, tmp_bytes);
     // A order
     LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, cam_idx, pt_idx, (int64_t)C, 0, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
@@ -306,7 +326,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     lap("A order sort");
     // B order: stable sort of the A rows by (point block, camera) keeps the point order inside a run
     int32_t* runptr_u = nullptr;
-    cudaMalloc(&runptr_u, (nruns + 1) * sizeof(int32_t));
+    pool_malloc((void**)&runptr_u, (nruns + 1) * sizeof(int32_t));
     LAUNCH(k_make_keys_B, cdiv(N, 256), 256, 0, s, N, C, p->block_rows, p->cam_ps, p->pt_ps, p->pt_ptr, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, permBA, (int)N, 0, nbB, s);
     LAUNCH(k_segment_ptr64, cdiv((int64_t)nruns + 1, 256), 256, 0, s, (int64_t)nruns, N, keys2, runptr_u);
@@ -327,13 +347,13 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     }
     int32_t* run_start = nullptr;
     if (e == cudaSuccess) {
-      cudaMalloc(&run_start, (nruns + 1) * sizeof(int32_t));
+      pool_malloc((void**)&run_start, (nruns + 1) * sizeof(int32_t));
       cudaMemcpyAsync(run_start, hstart.data(), (nruns + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s);
       LAUNCH(k_posB, cdiv(N, 256), 256, 0, s, N, permBA, keys2, runptr_u, run_start, p->posB);
       e = cudaStreamSynchronize(s);
     }
-    cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(permBA); cudaFree(tmp); cudaFree(runptr_u);
-    if (run_start) cudaFree(run_start);
+    pool_free(keys); pool_free(keys2); pool_free(vals); pool_free(permBA); pool_free(tmp); pool_free(runptr_u);
+    if (run_start) pool_free(run_start);
     if (e != cudaSuccess || (e = cudaGetLastError()) != cudaSuccess) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, std::string("plan_create: ") + cudaGetErrorString(e));
@@ -369,27 +389,27 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int64_t mx = 0;
     for (int c = 0; c < C; ++c) mx = rows[c] > mx ? rows[c] : mx;
     p->max_cam_rows = (int)mx;
-    cudaMemcpy(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
-    cudaMemcpy(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice);
+    cudaMemcpyAsync(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+    cudaMemcpyAsync(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     const size_t nb_rows = p->NB ? (size_t)p->NB : 1;
     void* q = nullptr;
     int bad_alloc = 0;
-    if (cudaMalloc(&q, nb_rows * 8 * p->jsz) != cudaSuccess) bad_alloc = 1; else { p->allocs.push_back(q); p->Jc_B = q; cudaMemset(q, 0, nb_rows * 8 * p->jsz); }
+    if (pool_malloc((void**)&q, nb_rows * 8 * p->jsz) != cudaSuccess) bad_alloc = 1; else { p->allocs.push_back(q); p->Jc_B = q; cudaMemsetAsync(q, 0, nb_rows * 8 * p->jsz, s); }
     double** arr[5] = {&p->r_B, &p->w_B, &p->beta_B, &p->sig, &p->omg};
     for (int i = 0; i < 5 && !bad_alloc; ++i) {
-      if (cudaMalloc(&q, nb_rows * sizeof(double)) != cudaSuccess) { bad_alloc = 1; break; }
+      if (pool_malloc((void**)&q, nb_rows * sizeof(double)) != cudaSuccess) { bad_alloc = 1; break; }
       p->allocs.push_back(q);
       *arr[i] = (double*)q;
-      cudaMemset(q, 0, nb_rows * sizeof(double));
+      cudaMemsetAsync(q, 0, nb_rows * sizeof(double), s);
     }
-    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
+    if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
       p->allocs.push_back(q); p->pt_B = (int32_t*)q;
       k_fill_i32<<<cdiv((int64_t)nb_rows, 256), 256, 0, s>>>((int64_t)nb_rows, -1, p->pt_B);
       if (N) k_scatter_i32<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->pt_ps, p->pt_B);
     } else bad_alloc = 1;
-    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(double2)) == cudaSuccess) { p->allocs.push_back(q); p->obs_B = (double2*)q; cudaMemsetAsync(q, 0, nb_rows * sizeof(double2), s); } else bad_alloc = 1;
-    if (!bad_alloc && cudaMalloc(&q, ((size_t)N + 1) * 32) == cudaSuccess) { p->allocs.push_back(q); p->rec_A = q; } else bad_alloc = 1;
-    if (!bad_alloc && cudaMalloc(&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
+    if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(double2)) == cudaSuccess) { p->allocs.push_back(q); p->obs_B = (double2*)q; cudaMemsetAsync(q, 0, nb_rows * sizeof(double2), s); } else bad_alloc = 1;
+    if (!bad_alloc && pool_malloc((void**)&q, ((size_t)N + 1) * 32) == cudaSuccess) { p->allocs.push_back(q); p->rec_A = q; } else bad_alloc = 1;
+    if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
       p->allocs.push_back(q); p->posA = (int32_t*)q;
       k_fill_i32<<<cdiv((int64_t)nb_rows, 256), 256, 0, s>>>((int64_t)nb_rows, (int32_t)N, p->posA);
       if (N) k_invert_perm<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->posA);
@@ -434,7 +454,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk)
     const int cap = PS_T * PS_RPT;
     std::vector<int32_t> hptr((size_t)P + 1), crow, cpt;
-    if (cudaMemcpy(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    if ((cudaMemcpyAsync(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s), cudaStreamSynchronize(s)) != cudaSuccess) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, "plan_create: pt_ptr readback");
     }
@@ -460,8 +480,9 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       b200ba_plan_destroy(p);
       return B200BA_ECUDA;
     }
-    cudaMemcpy(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
-    cudaMemcpy(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    cudaMemcpyAsync(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+    cudaMemcpyAsync(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+    cudaStreamSynchronize(s);
   }
   lap("point chunks");
   *out = p;
@@ -470,7 +491,8 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
 
 extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
   if (!p) return B200BA_OK;
-  for (void* q : p->allocs) cudaFree(q);
+  cudaDeviceSynchronize();  // frees are stream ordered on the allocation stream: nothing of this plan may still run
+  for (void* q : p->allocs) pool_free(q);
   if (p->st_host) cudaFreeHost(p->st_host);
   if (p->scal_host) cudaFreeHost(p->scal_host);
   for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
