@@ -17,6 +17,7 @@
 
 #include "ba_pcg.cuh"
 #include "ba_cs_ring.cuh"
+#include "ba_cs_warp.cuh"
 #include "pose_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -63,6 +64,10 @@ struct b200ba_plan {
   int32_t *pt_ptr = nullptr;                                         // A: CSR by point
   int32_t *camtab = nullptr, *cam_order = nullptr;                   // B: per-camera run tables; cameras by descending rows
   int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
+  WarpTask* wtask = nullptr; double* wpart = nullptr; int* wcount = nullptr; int nwtasks = 0;  // warp-task camera kernel
+  int cb_threads = 256;                                              // k_cam_blocks CTA size
+  int split = 0;                                                     // all-reduce points between matvec tail and head (nranks > 1, or forced)
+  int use_warp = 0;                                                  // route the split / sigma-only camera passes to it
   int64_t NB = 0;                                                    // rows in B order incl. run padding
   int ring_slots = 0, n_sm = 0;
   size_t ring_smem = 0;
@@ -391,6 +396,48 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     p->max_cam_rows = (int)mx;
     cudaMemcpyAsync(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaMemcpyAsync(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+    // warp tasks of the split camera passes: <= CW_ROWS local rows each, cameras in descending size, every camera
+    // at least one task (a camera without rows on this rank still has to publish a zero partial sum)
+    // Task size: about one resident wave of warps over the rank's rows, never so small that the fixed cost of a
+    // task dominates; a camera is cut into H near-equal parts only when it is well above that size.
+    std::vector<WarpTask> wt;
+    int target = (int)std::min<int64_t>(1024, std::max<int64_t>(256, p->NB / 3552));
+    if (const char* e = getenv("B200BA_TASK_ROWS")) { const int v = atoi(e); if (v >= 32) target = v; }
+    wt.reserve((size_t)C + (size_t)(p->NB / target) + 1);
+    for (int i = 0; i < C; ++i) {
+      const int c = order[i];
+      const int32_t* pre = tab.data() + (size_t)c * stride + nb;
+      const int L = (int)rows[c], H = std::max(1, (L + target / 2) / target), t0 = (int)wt.size();
+      const int part = ((L + H - 1) / H + 31) & ~31;
+      int r = 0;
+      for (int h = 0; h < H; ++h) {
+        WarpTask t{};
+        t.cam = c; t.lo = std::min(L, h * part); t.hi = std::min(L, t.lo + part);
+        while (r + 1 < nPB && t.lo >= pre[r + 1]) ++r;
+        t.run0 = r; t.nparts = H; t.t0 = t0;
+        wt.push_back(t);
+      }
+    }
+    p->nwtasks = (int)wt.size();
+    {
+      void* q = nullptr;
+      if (pool_malloc((void**)&q, wt.size() * sizeof(WarpTask)) == cudaSuccess) { p->allocs.push_back(q); p->wtask = (WarpTask*)q; }
+      if (pool_malloc((void**)&q, wt.size() * 8 * sizeof(double)) == cudaSuccess) { p->allocs.push_back(q); p->wpart = (double*)q; }
+      if (pool_malloc((void**)&q, (size_t)C * sizeof(int)) == cudaSuccess) { p->allocs.push_back(q); p->wcount = (int*)q; }
+      if (!p->wtask || !p->wpart || !p->wcount) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: warp task table"); }
+      cudaMemcpyAsync(p->wtask, wt.data(), wt.size() * sizeof(WarpTask), cudaMemcpyHostToDevice, s);
+      cudaMemsetAsync(p->wcount, 0, (size_t)C * sizeof(int), s);
+    }
+    {
+      // camera-block kernel: ~4 rows per thread, the CTA-wide reduction is a fixed cost per camera
+      const int64_t avg = p->NB / (C > 0 ? C : 1);
+      int th = (int)((avg / 4 + 31) & ~31);
+      p->cb_threads = th < 64 ? 64 : th > 256 ? 256 : th;
+      if (const char* e = getenv("B200BA_CB_THREADS")) { const int v = atoi(e); if (v >= 32 && v <= 256 && v % 32 == 0) p->cb_threads = v; }
+    }
+    p->use_warp = 1;
+    if (const char* e = getenv("B200BA_FORCE_SPLIT")) p->split = atoi(e) != 0;  // profiling / tests: multi-rank kernel sequence on one rank
+    if (const char* e = getenv("B200BA_CS_WARP")) p->use_warp = atoi(e);
     const size_t nb_rows = p->NB ? (size_t)p->NB : 1;
     void* q = nullptr;
     int bad_alloc = 0;
@@ -536,6 +583,7 @@ extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const 
   p->comm = g_comm;
   p->rank = rank;
   p->nranks = nranks;
+  p->split = 1;
   return B200BA_OK;
 }
 
@@ -580,7 +628,7 @@ struct Ops {
                   (JT*)p->Jp_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
-    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, 256, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
+    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, p->cb_threads, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
            p->U, p->gc);
     int rc;
     if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
@@ -598,6 +646,24 @@ struct Ops {
     const bool fused = upd && (flags & ~upd) == (CS_C | CS_UX | CS_A);        // single rank: whole iteration
     const bool half1 = flags == (CS_C | CS_WRITE_Y);                          // multi-rank: partial sums out
     const bool half2 = upd && (flags & ~upd) == (CS_READ_Y | CS_UX | CS_A);   // multi-rank: update + next matvec head
+    if (p->use_warp && !fused && !((flags & CS_C) && (flags & (CS_UX | CS_A | upd)))) {
+      // split passes: rows . omega partial sums | camera-local vector step | sigma = rows . v   (ba_cs_warp.cuh)
+      const int ign = flags & CS_IGNORE_DONE;
+      const int grid = (int)cdiv(p->nwtasks, CW_T / 32);
+      if (flags & CS_C)
+        PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_C | ign, p->st, p->camtab, p->wtask,
+                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, 0, p->y, p->wpart, p->wcount);
+      int vs = vin_slot;
+      if (flags & (CS_READ_Y | CS_UX | upd)) {
+        PLAUNCH(p, PC_PCG_VEC, k_cs_vec, (int)cdiv(p->C, CV_T / 8), CV_T, 0, s, p->C, flags & ~(CS_A | CS_C), p->st, p->U, p->Minv,
+                vin_slot, p->y, p->cv, p->part2);
+        if (upd) vs = CV_M;
+      }
+      if (flags & CS_A)
+        PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_A | ign, p->st, p->camtab, p->wtask,
+                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, vs, p->y, p->wpart, p->wcount);
+      return;
+    }
     if (p->ring_slots && (fused || half1 || half2)) {
       const int grid = p->C < p->n_sm ? p->C : p->n_sm;
       PLAUNCH(p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, p->camtab,
@@ -616,7 +682,7 @@ struct Ops {
   }
   // matvec tail + vector update + next matvec head; multi-rank: partial sums are all-reduced in between
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
-    if (p->nranks == 1) {
+    if (!p->split) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, -1, s);
@@ -633,7 +699,7 @@ struct Ops {
     const int C = p->C, P = p->P;
     if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, p->posB,
                   (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->w_B, p->beta_B);
-    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, 256, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, nullptr, p->w_B,
+    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, p->cb_threads, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, nullptr, p->w_B,
            p->beta_B, p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
@@ -651,7 +717,7 @@ struct Ops {
   static int matvec(b200ba_plan* p, int xin, cudaStream_t s) {
     cs(p, PC_MV_CAM, CS_A | CS_IGNORE_DONE, xin, s);
     ps(p, 0, 2, 0.0, 0, s);
-    if (p->nranks == 1) {
+    if (!p->split) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y | CS_IGNORE_DONE, -1, s);

@@ -1,0 +1,230 @@
+// Camera side of the Schur matvec when the rows of a camera are FEW per launch: the multi-rank (point-sharded)
+// PCG iteration, where the all-reduce of the partial sums separates matvec tail and head, and the plain
+// sigma = rows . v passes of prepare / back-substitution / verification.
+//
+// The ring kernel (ba_cs_ring.cuh) walks one camera at a time per CTA; with 1/8 of the rows per rank its
+// per-camera latency chain (record wait, reduce, barrier, update) is all that is left.  Here the unit of work is
+// a WARP TASK: <= CW_ROWS consecutive local rows of one camera (cameras in descending size, tasks of a camera
+// adjacent), thousands of tasks in flight, no block-level synchronisation at all:
+//   k_cs_warp  CS_C  : partial n_c = -sum a_i omega_i  (cameras cut into several tasks: ordered last-arriver sum)
+//              CS_A  : sigma_i = a_i . v_c,  v = slot vin_slot of the camera record
+//   k_cs_vec         : the camera-local vector work between the two (8 lanes per camera): n_c from y (all-reduced),
+//                      + (U_c + mu) v_c, PCG recurrences / start, dot partials, m_c = Minv_c w_c
+#pragma once
+#include "ba_pcg.cuh"
+
+#define CW_T 256
+#ifndef CW_ROWS
+#define CW_ROWS 512
+#endif
+#define CW_U 4
+
+// 8 per-lane accumulators -> lane (l & ~3 == component pattern) holds the warp total of ONE component:
+// 18 shuffles instead of 40.  Returns the total of component comp8(lane) (valid in every lane).
+__device__ __forceinline__ int comp8(int lane) { return ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1); }
+__device__ __forceinline__ double warp_tsum8(const double (&acc)[8], int lane) {
+  double v4[4], v2[2], v1;
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const double send = up ? acc[j] : acc[j + 4], keepv = up ? acc[j + 4] : acc[j];
+      v4[j] = keepv + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const double send = up ? v4[j] : v4[j + 2], keepv = up ? v4[j + 2] : v4[j];
+      v2[j] = keepv + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+  }
+  {
+    const bool up = lane & 4;
+    const double send = up ? v2[0] : v2[1], keepv = up ? v2[1] : v2[0];
+    v1 = keepv + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+  v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+  return v1;
+}
+
+// One 32 B descriptor per task; wpart: 8 doubles per task; wcount: one arrival counter per camera (zero between
+// launches: the last arriver resets it).
+struct __align__(32) WarpTask {
+  int cam, lo, hi;  // local rows [lo, hi) of the camera (B order, padded runs flattened)
+  int run0;         // run that holds row lo
+  int nparts, t0;   // tasks of this camera, index of its first task
+  int pad[2];
+};
+template <typename JT>
+__global__ void __launch_bounds__(CW_T)
+k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
+          const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
+          double* __restrict__ sig, const double* __restrict__ cv, int vin_slot, double* __restrict__ y,
+          double* __restrict__ wpart, int* __restrict__ wcount) {
+  if (!(flags & CS_IGNORE_DONE) && st->pcg_done) return;
+  const int lane = threadIdx.x & 31;
+  const int t = blockIdx.x * (CW_T / 32) + (threadIdx.x >> 5);
+  if (t >= ntasks) return;
+  int tk[8];
+  {
+    const int4* q = reinterpret_cast<const int4*>(wtask + t);
+    const int4 a = __ldg(q), b = __ldg(q + 1);
+    tk[0] = a.x; tk[1] = a.y; tk[2] = a.z; tk[3] = a.w; tk[4] = b.x; tk[5] = b.y;
+  }
+  const int c = tk[0], lo = tk[1], hi = tk[2], run0 = tk[3], H = tk[4];
+  const int nb = (nPB + 3) & ~3;
+  const int32_t* __restrict__ beg = camtab + (size_t)c * (nb + ((nPB + 4) & ~3));
+  const int32_t* __restrict__ pre = beg + nb;
+  // current run of this lane: local rows [pr0, pr1) start at B position bg
+  int r = run0, pr0 = __ldg(pre + run0), pr1 = __ldg(pre + run0 + 1), bg = __ldg(beg + run0);
+  auto locate = [&](int l) -> size_t {
+    while (l >= pr1) { ++r; pr0 = pr1; pr1 = __ldg(pre + r + 1); bg = __ldg(beg + r); }
+    return (size_t)bg + (size_t)(l - pr0);
+  };
+  if (flags & CS_C) {
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int l0 = lo + lane; l0 < hi; l0 += 32 * CW_U) {
+      size_t j[CW_U];
+      bool h[CW_U];
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u) {
+        const int l = l0 + 32 * u;
+        h[u] = l < hi;
+        j[u] = h[u] ? locate(l) : 0;
+      }
+      JT a[CW_U][8];
+      double w[CW_U];
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u) {
+        if (h[u]) { ldrow(Jc_B + 8 * j[u], a[u]); w[u] = __ldg(omg + j[u]); }
+        else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) a[u][k] = (JT)0;
+          w[u] = 0.0;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] -= (double)a[u][k] * w[u];
+    }
+    const double v = warp_tsum8(acc, lane);
+    const int k = comp8(lane);
+    if (H <= 1) {
+      if ((lane & 3) == 0) y[8 * (size_t)c + k] = v;
+    } else {
+      if ((lane & 3) == 0) wpart[8 * (size_t)t + k] = v;
+      __threadfence();
+      __syncwarp();
+      int old = 0;
+      if (lane == 0) old = atomicAdd(wcount + c, 1);
+      old = __shfl_sync(0xffffffffu, old, 0);
+      if (old == H - 1) {  // every part of this camera is in: sum them in task order
+        __threadfence();
+        const size_t t0 = (size_t)tk[5];
+        if (lane < 8) {
+          double s = 0.0;
+          for (int hh = 0; hh < H; ++hh) s += __ldcg(wpart + 8 * (t0 + hh) + lane);
+          y[8 * (size_t)c + lane] = s;
+        }
+        if (lane == 0) wcount[c] = 0;
+      }
+    }
+  }
+  if (flags & CS_A) {
+    double m[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = cv[(size_t)CV_STRIDE * c + 8 * vin_slot + k];
+    r = run0; pr0 = __ldg(pre + run0); pr1 = __ldg(pre + run0 + 1); bg = __ldg(beg + run0);
+    for (int l0 = lo + lane; l0 < hi; l0 += 32 * CW_U) {
+      size_t j[CW_U];
+      bool h[CW_U];
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u) {
+        const int l = l0 + 32 * u;
+        h[u] = l < hi;
+        j[u] = h[u] ? locate(l) : 0;
+      }
+      JT a[CW_U][8];
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u)
+        if (h[u]) ldrow(Jc_B + 8 * j[u], a[u]);
+#pragma unroll
+      for (int u = 0; u < CW_U; ++u) {
+        if (h[u]) {
+          double s = 0.0;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) s += (double)a[u][k] * m[k];
+          sig[j[u]] = s;
+        }
+      }
+    }
+  }
+}
+
+// Camera-local vector step, 8 lanes per camera (lane&7 = component), registers only: every load of the camera's
+// 200-double neighbourhood (own components of the 9 PCG vectors, row k of U_c and Minv_c) is issued up front, the
+// matvec inputs travel by shuffles inside the 8-lane group.  Same arithmetic and summation order as cs_update().
+#define CV_T 128
+__global__ void __launch_bounds__(CV_T)
+k_cs_vec(int C, int flags, const SolverState* __restrict__ st, const double* __restrict__ U, const double* __restrict__ Minv,
+         int vin_slot, double* __restrict__ y, double* __restrict__ cv, double* __restrict__ part) {
+  const int e = blockIdx.x * CV_T + threadIdx.x;
+  const int c = e >> 3, k = e & 7, lane = threadIdx.x & 31, base = lane & ~7;
+  const bool act = c < C;
+  const size_t cc = act ? c : C - 1;  // idle groups shadow the last camera (convergent shuffles), never write
+  const bool upd = flags & (CS_INIT | CS_ITER);
+  double* rec = cv + (size_t)CV_STRIDE * cc + k;
+  double v[CV_SLOTS], u8[8] = {0, 0, 0, 0, 0, 0, 0, 0}, m8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int sl = 0; sl < CV_SLOTS; ++sl) v[sl] = rec[8 * sl];
+  const double vk = vin_slot >= 0 ? rec[8 * vin_slot] : 0.0;
+  if (flags & CS_UX) load8<double>(U + 64 * cc + 8 * k, u8);
+  if (upd) load8<double>(Minv + 64 * cc + 8 * k, m8);
+  double nk = (flags & CS_READ_Y) ? y[8 * cc + k] : 0.0;
+  const int done = (flags & CS_IGNORE_DONE) ? 0 : st->pcg_done;  // set by an earlier launch: uniform over the grid
+  const double mu = st->mu, alpha = st->alpha, beta = st->beta;
+  if (done) return;
+  if (flags & CS_UX) {
+    double s = mu * vk;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) s += u8[l] * __shfl_sync(0xffffffffu, vk, base + l);
+    nk += s;
+  }
+  if (!upd) {
+    if ((flags & CS_WRITE_Y) && act) y[8 * cc + k] = nk;
+    return;
+  }
+  double xk = v[CV_X], rk = v[CV_R], uk = v[CV_U], wk = v[CV_W], zk, qk, sk, pk;
+  if (flags & CS_INIT) {
+    wk = nk; zk = qk = sk = pk = 0.0;
+  } else {
+    zk = nk + beta * v[CV_Z];
+    qk = vk + beta * v[CV_Q];
+    sk = wk + beta * v[CV_S];
+    pk = uk + beta * v[CV_P];
+    xk += alpha * pk;
+    rk -= alpha * sk;
+    uk -= alpha * qk;
+    wk -= alpha * zk;
+  }
+  double mk = 0.0;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) mk += m8[l] * __shfl_sync(0xffffffffu, wk, base + l);
+  double g = rk * uk, d = wk * uk, q2 = rk * rk;
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) {
+    g += __shfl_xor_sync(0xffffffffu, g, o);
+    d += __shfl_xor_sync(0xffffffffu, d, o);
+    q2 += __shfl_xor_sync(0xffffffffu, q2, o);
+  }
+  if (act) {
+    rec[8 * CV_X] = xk; rec[8 * CV_R] = rk; rec[8 * CV_U] = uk; rec[8 * CV_W] = wk;
+    rec[8 * CV_Z] = zk; rec[8 * CV_Q] = qk; rec[8 * CV_S] = sk; rec[8 * CV_P] = pk;
+    rec[8 * CV_M] = mk;
+    if (k == 0) { part[4 * cc] = g; part[4 * cc + 1] = d; part[4 * cc + 2] = q2; }
+  }
+}

@@ -225,7 +225,18 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const RowRec
 }
 
 // ---------------------------------------------------------------- K2b: 8x8 camera blocks
-// One CTA per camera streams its B-order runs.  If beta_B != nullptr the rows are weighted:
+// One step of a transpose-reduce: N values per lane -> N/2, the lanes with bit `off` set keep the upper half.
+template <int N>
+__device__ __forceinline__ void tr_fold(double* v, int lane, int off) {
+  const bool up = lane & off;
+#pragma unroll
+  for (int j = 0; j < N / 2; ++j) {
+    const double send = up ? v[j] : v[j + N / 2], keepv = up ? v[j + N / 2] : v[j];
+    v[j] = keepv + __shfl_xor_sync(0xffffffffu, send, off);
+  }
+}
+
+// One CTA per camera (64..256 threads, by the average camera size) streams its B-order runs.  If beta_B != nullptr the rows are weighted:
 // out = -sum beta_i a a^T and -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs);
 // otherwise U_c = sum a a^T and g_c = sum a r.
 // (An fp64 tensor-core version — one mma.sync.m8n8k4.f64 per 4 rows, the SYRK mapped 1:1 onto the DMMA tile — was
@@ -236,7 +247,7 @@ __global__ void __launch_bounds__(256)
 k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__ Jc_B,
              const double* __restrict__ s_B, const double* __restrict__ w_B, const double* __restrict__ beta_B,
              double* __restrict__ U, double* __restrict__ gc) {
-  __shared__ double sm[44 * 32];
+  __shared__ double sm[44 * 8];
   __shared__ CamRuns runs;
   const int c = blockIdx.x;
   const int L = runs.load(c, nPB, camtab);
@@ -266,19 +277,31 @@ k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[36 + k] += a[k] * s;
   }
-  block_sum<44>(acc, sm);
-  if (threadIdx.x == 0) {
-    int t = 0;
+  // transpose-reduce inside the warp (47 shuffles instead of 44 x 5): afterwards lane i holds the warp total of
+  // value i (i < 32) and lanes 2j, 2j+1 both hold value 32 + j (j < 12)
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  double hi[16];
 #pragma unroll
-    for (int k = 0; k < 8; ++k)
-#pragma unroll
-      for (int l = k; l < 8; ++l) {
-        U[64 * (size_t)c + 8 * k + l] = acc[t];
-        U[64 * (size_t)c + 8 * l + k] = acc[t];
-        ++t;
-      }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) gc[8 * (size_t)c + k] = acc[36 + k];
+  for (int k = 0; k < 16; ++k) hi[k] = k < 12 ? acc[32 + k] : 0.0;
+  tr_fold<32>(acc, lane, 16); tr_fold<16>(acc, lane, 8); tr_fold<8>(acc, lane, 4); tr_fold<4>(acc, lane, 2); tr_fold<2>(acc, lane, 1);
+  tr_fold<16>(hi, lane, 16); tr_fold<8>(hi, lane, 8); tr_fold<4>(hi, lane, 4); tr_fold<2>(hi, lane, 2);
+  hi[0] += __shfl_xor_sync(0xffffffffu, hi[0], 1);
+  sm[wid * 44 + lane] = acc[0];
+  if (!(lane & 1) && lane < 24) sm[wid * 44 + 32 + (lane >> 1)] = hi[0];
+  __syncthreads();
+  if (threadIdx.x < 44) {
+    double v = 0.0;
+    for (int w = 0; w < nw; ++w) v += sm[w * 44 + threadIdx.x];  // fixed order
+    const int t = threadIdx.x;
+    if (t >= 36) {
+      gc[8 * (size_t)c + (t - 36)] = v;
+    } else {
+      int k = 0, rem = t;
+      while (rem >= 8 - k) { rem -= 8 - k; ++k; }
+      const int l = k + rem;
+      U[64 * (size_t)c + 8 * k + l] = v;
+      U[64 * (size_t)c + 8 * l + k] = v;
+    }
   }
 }
 

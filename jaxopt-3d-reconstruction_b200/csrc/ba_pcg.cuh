@@ -200,11 +200,22 @@ k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ 
 __device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restrict__ st,
                                             const double* __restrict__ part, double rtol, int maxiter,
                                             double* sm3 /*3*32*/) {
+  // per-camera partials {gamma, delta, rr, -}: one 32 B load each, 8 in flight per thread (a serial loop over
+  // 13682 cameras made block 0 the tail of the whole point kernel); per-thread summation order unchanged
   double v3[3] = {0.0, 0.0, 0.0};
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    v3[0] += part[4 * (size_t)i];
-    v3[1] += part[4 * (size_t)i + 1];
-    v3[2] += part[4 * (size_t)i + 2];
+  const int bd = blockDim.x;
+  int i = threadIdx.x;
+  for (; i + 7 * bd < C; i += 8 * bd) {
+    double q[8][4];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) ld256(part + 4 * (size_t)(i + u * bd), q[u]);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { v3[0] += q[u][0]; v3[1] += q[u][1]; v3[2] += q[u][2]; }
+  }
+  for (; i < C; i += bd) {
+    double q[4];
+    ld256(part + 4 * (size_t)i, q);
+    v3[0] += q[0]; v3[1] += q[1]; v3[2] += q[2];
   }
   block_sum<3>(v3, sm3);
   if (threadIdx.x == 0) {

@@ -27,6 +27,10 @@ SHAPES = {
     "trafalgar257": (257, 65132, 225911),
     "venice1778": (1778, 993923, 5001946),
     "final13682": (13682, 4456117, 28987644),
+    # what ONE rank of a point-sharded Final-13682 solve holds at 4 / 8 ranks (all cameras, 1/4 or 1/8 of the points):
+    # single-GPU stand-ins for profiling the multi-rank kernels (B200BA_FORCE_SPLIT=1)
+    "final13682_r4": (13682, 1114029, 7246911),
+    "final13682_r8": (13682, 557015, 3623456),
 }
 
 WIDTH = 1000.0

@@ -166,6 +166,23 @@ def test_point_block_size_does_not_matter(monkeypatch):
     np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
 
 
+@pytest.mark.parametrize("task_rows", ["64", "100000"])
+def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows):
+    """The multi-rank kernel sequence (warp-task partial sums | all-reduce point | camera-local vector step |
+    warp-task sigma pass) forced onto one rank must reproduce the fused ring-kernel iteration; 64-row tasks cut
+    every camera into many parts (ordered last-arriver sum), 100000-row tasks keep cameras whole."""
+    sc, ba, x0, k3 = _setup("ladybug49", jac_f32=True)
+    out = []
+    for split in ("0", "1"):
+        monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
+        monkeypatch.setenv("B200BA_TASK_ROWS", task_rows)
+        out.append(ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None))
+    (pa, sa), (pb, sb) = out
+    assert sa.iter_num == sb.iter_num
+    np.testing.assert_allclose(sa.loss_trajectory, sb.loss_trajectory, rtol=2e-6)
+    np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
+
+
 def test_schur_matvec_matches_dense_schur_complement():
     """b200ba_schur_matvec (camera head -> point kernel -> camera tail) against S formed densely by the oracle's
     formulas: S = U + mu I - W (V + mu I)^-1 W^T."""
