@@ -66,6 +66,7 @@ struct b200ba_plan {
   int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
   WarpTask* wtask = nullptr; double* wpart = nullptr; int* wcount = nullptr; int nwtasks = 0;  // warp-task camera kernel
   int cb_threads = 256;                                              // k_cam_blocks CTA size
+  int xchg = 0; int xseq_last = 0;                                   // partial sums exchanged over peer memory (else NCCL)
   int split = 0;                                                     // all-reduce points between matvec tail and head (nranks > 1, or forced)
   int use_warp = 0;                                                  // route the split / sigma-only camera passes to it
   int64_t NB = 0;                                                    // rows in B order incl. run padding
@@ -423,10 +424,10 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       void* q = nullptr;
       if (pool_malloc((void**)&q, wt.size() * sizeof(WarpTask)) == cudaSuccess) { p->allocs.push_back(q); p->wtask = (WarpTask*)q; }
       if (pool_malloc((void**)&q, wt.size() * 8 * sizeof(double)) == cudaSuccess) { p->allocs.push_back(q); p->wpart = (double*)q; }
-      if (pool_malloc((void**)&q, (size_t)C * sizeof(int)) == cudaSuccess) { p->allocs.push_back(q); p->wcount = (int*)q; }
+      if (pool_malloc((void**)&q, ((size_t)C + 1) * sizeof(int)) == cudaSuccess) { p->allocs.push_back(q); p->wcount = (int*)q; }
       if (!p->wtask || !p->wpart || !p->wcount) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: warp task table"); }
       cudaMemcpyAsync(p->wtask, wt.data(), wt.size() * sizeof(WarpTask), cudaMemcpyHostToDevice, s);
-      cudaMemsetAsync(p->wcount, 0, (size_t)C * sizeof(int), s);
+      cudaMemsetAsync(p->wcount, 0, ((size_t)C + 1) * sizeof(int), s);
     }
     {
       // camera-block kernel: ~4 rows per thread, the CTA-wide reduction is a fixed cost per camera
@@ -568,10 +569,79 @@ extern "C" int b200ba_nccl_unique_id(char* out) {
 // problem).  unique_id_host == NULL re-uses the communicator created by an earlier call.
 static ncclComm_t g_comm = nullptr;
 static int g_rank = 0, g_nranks = 1;
+
+// Exchange block for the per-iteration partial sums (ba_cs_warp.cuh): one per process, mapped by every peer through
+// CUDA IPC, kept across plans (mapping costs milliseconds) and only rebuilt when a plan needs a larger one.
+static struct {
+  double* base = nullptr;   // own block: XF_INTS ints of flags | 2 x ycap doubles
+  size_t ycap = 0;
+  XPeers peers{};
+  int nranks = 0, ok = 0, seq = 0;
+} g_x;
+static void xchg_release() {
+  for (int r = 0; r < g_x.nranks; ++r)
+    if (g_x.peers.base[r] && g_x.peers.base[r] != g_x.base) cudaIpcCloseMemHandle(g_x.peers.base[r]);
+  if (g_x.base) cudaFree(g_x.base);
+  g_x = {};
+}
+// Collective over the communicator.  Leaves g_x.ok = 1 only if EVERY rank mapped every peer.
+static int xchg_setup(int rank, int nranks, size_t need, cudaStream_t s) {
+  if (g_x.ok && g_x.nranks == nranks && g_x.ycap >= need) return 0;
+  xchg_release();
+  if (nranks > X_MAXR) return 0;
+  if (const char* e = getenv("B200BA_P2P")) if (!atoi(e)) return 0;
+  const size_t ycap = (need + 511) & ~(size_t)511;
+  const size_t bytes = XF_INTS * sizeof(int) + 2 * ycap * sizeof(double);
+  int good = 1;
+  cudaIpcMemHandle_t mine{};
+  if (cudaMalloc((void**)&g_x.base, bytes) != cudaSuccess) { g_x.base = nullptr; good = 0; cudaGetLastError(); }
+  if (good) {
+    cudaMemsetAsync(g_x.base, 0, bytes, s);
+    if (cudaIpcGetMemHandle(&mine, g_x.base) != cudaSuccess) { good = 0; cudaGetLastError(); }
+  }
+  // all-gather the handles (and the per-rank verdicts) through the communicator
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  const size_t rec = 64 + 8;
+  unsigned char* d_all = nullptr;
+  std::vector<unsigned char> h_all(rec * nranks, 0);
+  if (cudaMalloc((void**)&d_all, rec * nranks) != cudaSuccess) return B200BA_ECUDA;
+  memcpy(h_all.data() + rec * rank, &mine, 64);
+  h_all[rec * rank + 64] = (unsigned char)good;
+  cudaMemcpyAsync(d_all + rec * rank, h_all.data() + rec * rank, rec, cudaMemcpyHostToDevice, s);
+  CKN(ncclAllGather(d_all + rec * rank, d_all, rec, ncclChar, g_comm, s));
+  cudaMemcpyAsync(h_all.data(), d_all, rec * nranks, cudaMemcpyDeviceToHost, s);
+  CK(cudaStreamSynchronize(s));
+  for (int r = 0; r < nranks; ++r) good &= h_all[rec * r + 64];
+  g_x.nranks = nranks;
+  if (good) {
+    for (int r = 0; r < nranks; ++r) {
+      if (r == rank) { g_x.peers.base[r] = g_x.base; continue; }
+      cudaIpcMemHandle_t h;
+      memcpy(&h, h_all.data() + rec * r, 64);
+      void* q = nullptr;
+      if (cudaIpcOpenMemHandle(&q, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { good = 0; cudaGetLastError(); break; }
+      g_x.peers.base[r] = (double*)q;
+    }
+  }
+  // second round: did everybody map everybody?  (also the barrier before the first use)
+  h_all[0] = (unsigned char)good;
+  cudaMemcpyAsync(d_all + rank, h_all.data(), 1, cudaMemcpyHostToDevice, s);
+  CKN(ncclAllGather(d_all + rank, d_all, 1, ncclChar, g_comm, s));
+  cudaMemcpyAsync(h_all.data(), d_all, nranks, cudaMemcpyDeviceToHost, s);
+  CK(cudaStreamSynchronize(s));
+  cudaFree(d_all);
+  for (int r = 0; r < nranks; ++r) good &= h_all[r];
+  if (!good) { xchg_release(); return 0; }
+  g_x.ycap = ycap;
+  g_x.ok = 1;
+  g_x.seq = 0;
+  return 0;
+}
 extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const char* uid) {
   if (!p || nranks < 1 || rank < 0 || rank >= nranks) FAIL(B200BA_EINVAL, "set_comm: bad args");
   if (nranks == 1) return B200BA_OK;
   if (uid) {
+    xchg_release();
     if (g_comm) { ncclCommDestroy(g_comm); g_comm = nullptr; }
     ncclUniqueId id;
     memcpy(&id, uid, 128);
@@ -584,6 +654,14 @@ extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const 
   p->rank = rank;
   p->nranks = nranks;
   p->split = 1;
+  {
+    cudaStream_t xs = nullptr;
+    int rc = xchg_setup(rank, nranks, (size_t)p->C * 8 + 8, xs);
+    if (rc) return rc;
+    p->xchg = g_x.ok && p->use_warp;
+    if (p->xchg) if (const char* e = getenv("B200BA_XSIGNAL")) if (!strcmp(e, "kernel")) p->xchg = 2;
+    if (getenv("B200BA_VERBOSE")) fprintf(stderr, "[b200ba] rank %d/%d: partial sums over %s\n", rank, nranks, p->xchg ? "peer memory" : "NCCL");
+  }
   return B200BA_OK;
 }
 
@@ -606,6 +684,16 @@ __global__ void k_lin_state(SolverState* st, const double* lin_scal, const doubl
 
 static int allreduce(b200ba_plan* p, double* buf, size_t n, ncclRedOp_t op, cudaStream_t s) {
   if (p->nranks > 1) CKN(ncclAllReduce(buf, buf, n, ncclDouble, op, p->comm, s));
+  return 0;
+}
+
+// partial sums y of all ranks -> everybody: NCCL all-reduce in place, or (peer memory) nothing to launch: the partial-sum
+// kernel signals the peers itself and k_cs_vec sums the R vectors with loads over NVLink
+static int exchange_y(b200ba_plan* p, cudaStream_t s) {
+  if (p->nranks <= 1) return 0;
+  if (!p->xchg) return allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s);
+  // normally the last CTA of the partial-sum kernel has already signalled the peers
+  if (p->xchg == 2) PLAUNCH(p, PC_OTHER, k_xsignal, 1, 32, 0, s, g_x.peers, p->rank, p->nranks, p->xseq_last);
   return 0;
 }
 
@@ -650,18 +738,23 @@ struct Ops {
       // split passes: rows . omega partial sums | camera-local vector step | sigma = rows . v   (ba_cs_warp.cuh)
       const int ign = flags & CS_IGNORE_DONE;
       const int grid = (int)cdiv(p->nwtasks, CW_T / 32);
+      // peer-memory exchange: partial sums of iteration seq go to buffer seq&1 of the own exchange block
+      double* xy = p->y;
+      if (p->xchg && (flags & CS_C)) { p->xseq_last = ++g_x.seq; xy = g_x.base + XF_INTS / 2 + (size_t)(g_x.seq & 1) * g_x.ycap; }
       if (flags & CS_C)
         PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_C | ign, p->st, p->camtab, p->wtask,
-                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, 0, p->y, p->wpart, p->wcount);
+                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, 0, xy, p->wpart, p->wcount, g_x.peers, p->rank, p->xchg == 1 ? p->nranks : 1,
+                p->xseq_last, p->wcount + p->C);
       int vs = vin_slot;
       if (flags & (CS_READ_Y | CS_UX | upd)) {
         PLAUNCH(p, PC_PCG_VEC, k_cs_vec, (int)cdiv(p->C, CV_T / 8), CV_T, 0, s, p->C, flags & ~(CS_A | CS_C), p->st, p->U, p->Minv,
-                vin_slot, p->y, p->cv, p->part2);
+                vin_slot, p->y, p->cv, p->part2, g_x.peers, p->rank, (p->xchg && (flags & CS_READ_Y)) ? p->nranks : 1, p->xseq_last,
+                (size_t)XF_INTS / 2 + (size_t)(p->xseq_last & 1) * g_x.ycap);
         if (upd) vs = CV_M;
       }
       if (flags & CS_A)
         PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_A | ign, p->st, p->camtab, p->wtask,
-                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, vs, p->y, p->wpart, p->wcount);
+                (const JT*)p->Jc_B, p->omg, p->sig, p->cv, vs, p->y, p->wpart, p->wcount, g_x.peers, p->rank, 1, 0, nullptr);
       return;
     }
     if (p->ring_slots && (fused || half1 || half2)) {
@@ -687,7 +780,7 @@ struct Ops {
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, -1, s);
       int rc;
-      if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
+      if ((rc = exchange_y(p, s))) return rc;
       cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | upd_flag | CS_A, vin, s);
     }
     return 0;
@@ -722,7 +815,7 @@ struct Ops {
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y | CS_IGNORE_DONE, -1, s);
       int rc;
-      if ((rc = allreduce(p, p->y, (size_t)p->C * 8, ncclSum, s))) return rc;
+      if ((rc = exchange_y(p, s))) return rc;
       cs(p, PC_MV_CAM, CS_READ_Y | CS_UX | CS_WRITE_Y | CS_IGNORE_DONE, xin, s);
     }
     return 0;

@@ -50,6 +50,50 @@ __device__ __forceinline__ double warp_tsum8(const double (&acc)[8], int lane) {
   return v1;
 }
 
+// ---------------------------------------------------------------- partial-sum exchange over peer memory
+// Every rank owns one exchange block that all peers map (CUDA IPC): XF_INTS arrival flags, then two buffers of
+// `ycap` doubles.  Iteration `seq`: the partial sums go to buffer seq&1 of the rank's OWN block, the LAST CTA of that
+// k_cs_warp launch publishes seq in every peer's flag slot of this rank, and k_cs_vec — once all flags show seq — adds the R partial vectors in
+// rank order with loads over NVLink (same order everywhere: all ranks get the same bits).  Two buffers are enough:
+// a rank can only reach the write of seq+2 after every peer has signalled seq+1, i.e. finished reading seq.
+#define XF_INTS 64
+#define X_MAXR 8
+struct XPeers { double* base[X_MAXR]; };  // exchange block of each rank as mapped into THIS process
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ double ld_relaxed_sys(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__global__ void k_xsignal(XPeers px, int rank, int nr, int seq) {  // stand-alone signal (A/B switch B200BA_XSIGNAL=kernel)
+  const int r = threadIdx.x;
+  if (r >= nr || r == rank) return;
+  __threadfence_system();
+  int* f = reinterpret_cast<int*>(px.base[r]) + rank;
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f), "r"(seq) : "memory");
+}
+// called by every thread of the CTA at the end of the partial-sum pass; ctr: zero between launches
+__device__ __forceinline__ void xchg_signal_when_last(const XPeers& px, int rank, int nr, int seq, int* __restrict__ ctr) {
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int old = atomicAdd(ctr, 1);
+    s_last = old == (int)gridDim.x - 1;
+    if (s_last) *ctr = 0;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x < nr && threadIdx.x != rank) {
+    __threadfence_system();
+    int* f = reinterpret_cast<int*>(px.base[threadIdx.x]) + rank;
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f), "r"(seq) : "memory");
+  }
+}
+
 // One 32 B descriptor per task; wpart: 8 doubles per task; wcount: one arrival counter per camera (zero between
 // launches: the last arriver resets it).
 struct __align__(32) WarpTask {
@@ -59,15 +103,11 @@ struct __align__(32) WarpTask {
   int pad[2];
 };
 template <typename JT>
-__global__ void __launch_bounds__(CW_T)
-k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
-          const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
-          double* __restrict__ sig, const double* __restrict__ cv, int vin_slot, double* __restrict__ y,
-          double* __restrict__ wpart, int* __restrict__ wcount) {
-  if (!(flags & CS_IGNORE_DONE) && st->pcg_done) return;
-  const int lane = threadIdx.x & 31;
-  const int t = blockIdx.x * (CW_T / 32) + (threadIdx.x >> 5);
-  if (t >= ntasks) return;
+__device__ __forceinline__ void
+k_cs_warp_task(int t, int lane, int nPB, int flags, const int32_t* __restrict__ camtab,
+               const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
+               double* __restrict__ sig, const double* __restrict__ cv, int vin_slot, double* __restrict__ y,
+               double* __restrict__ wpart, int* __restrict__ wcount) {
   int tk[8];
   {
     const int4* q = reinterpret_cast<const int4*>(wtask + t);
@@ -165,13 +205,29 @@ k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, co
   }
 }
 
+template <typename JT>
+__global__ void __launch_bounds__(CW_T)
+k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
+          const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
+          double* __restrict__ sig, const double* __restrict__ cv, int vin_slot, double* __restrict__ y,
+          double* __restrict__ wpart, int* __restrict__ wcount, XPeers px, int rank, int nr, int seq, int* __restrict__ xctr) {
+  const int lane = threadIdx.x & 31;
+  const int t = blockIdx.x * (CW_T / 32) + (threadIdx.x >> 5);
+  const bool work = ((flags & CS_IGNORE_DONE) || !st->pcg_done) && t < ntasks;  // warp-uniform
+  if (work) k_cs_warp_task<JT>(t, lane, nPB, flags, camtab, wtask, Jc_B, omg, sig, cv, vin_slot, y, wpart, wcount);
+  // multi-rank: tell the peers that this rank's partial sums of iteration seq are complete (also when the solve is
+  // finished and nothing was written: the receiving side waits for every seq)
+  if (nr > 1) xchg_signal_when_last(px, rank, nr, seq, xctr);
+}
+
 // Camera-local vector step, 8 lanes per camera (lane&7 = component), registers only: every load of the camera's
 // 200-double neighbourhood (own components of the 9 PCG vectors, row k of U_c and Minv_c) is issued up front, the
 // matvec inputs travel by shuffles inside the 8-lane group.  Same arithmetic and summation order as cs_update().
 #define CV_T 128
 __global__ void __launch_bounds__(CV_T)
-k_cs_vec(int C, int flags, const SolverState* __restrict__ st, const double* __restrict__ U, const double* __restrict__ Minv,
-         int vin_slot, double* __restrict__ y, double* __restrict__ cv, double* __restrict__ part) {
+k_cs_vec(int C, int flags, SolverState* __restrict__ st, const double* __restrict__ U, const double* __restrict__ Minv,
+         int vin_slot, double* __restrict__ y, double* __restrict__ cv, double* __restrict__ part,
+         XPeers px, int rank, int nr, int seq, size_t xoff) {
   const int e = blockIdx.x * CV_T + threadIdx.x;
   const int c = e >> 3, k = e & 7, lane = threadIdx.x & 31, base = lane & ~7;
   const bool act = c < C;
@@ -184,10 +240,33 @@ k_cs_vec(int C, int flags, const SolverState* __restrict__ st, const double* __r
   const double vk = vin_slot >= 0 ? rec[8 * vin_slot] : 0.0;
   if (flags & CS_UX) load8<double>(U + 64 * cc + 8 * k, u8);
   if (upd) load8<double>(Minv + 64 * cc + 8 * k, m8);
-  double nk = (flags & CS_READ_Y) ? y[8 * cc + k] : 0.0;
-  const int done = (flags & CS_IGNORE_DONE) ? 0 : st->pcg_done;  // set by an earlier launch: uniform over the grid
+  double nk = ((flags & CS_READ_Y) && nr <= 1) ? y[8 * cc + k] : 0.0;
+  const int done = (flags & CS_IGNORE_DONE) ? 0 : st->pcg_done;  // set by an earlier launch: uniform over grid and ranks
   const double mu = st->mu, alpha = st->alpha, beta = st->beta;
+  const bool xsum = (flags & CS_READ_Y) && nr > 1;
+  if (xsum) {
+    // wait for every peer's signal of this iteration — also when the solve is already finished, so that the
+    // two-buffer invariant above holds for whatever comes next (bounded: a lost peer must not hang the GPU)
+    if (threadIdx.x < nr && threadIdx.x != rank) {
+      const int* f = reinterpret_cast<const int*>(px.base[rank]) + threadIdx.x;
+      const long long t0 = clock64();
+      while (ld_acquire_sys(f) - seq < 0) {
+        if (clock64() - t0 > (5LL << 30)) { atomicOr(&st->status, 8); break; }
+        __nanosleep(100);
+      }
+    }
+    __syncthreads();
+  }
   if (done) return;
+  if (xsum) {
+    double pv[X_MAXR];
+#pragma unroll
+    for (int r = 0; r < X_MAXR; ++r)
+      if (r < nr) pv[r] = ld_relaxed_sys(px.base[r] + xoff + 8 * cc + k);
+#pragma unroll
+    for (int r = 0; r < X_MAXR; ++r)
+      if (r < nr) nk += pv[r];
+  }
   if (flags & CS_UX) {
     double s = mu * vk;
 #pragma unroll
