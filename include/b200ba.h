@@ -19,7 +19,8 @@ typedef struct b200ba_plan b200ba_plan;
 
 enum { B200BA_OK = 0, B200BA_EINVAL = 1, B200BA_ECUDA = 2, B200BA_ENCCL = 3 };
 /* per-solve status bits (b200ba_lm_result.status / pose status[]) */
-enum { B200BA_ST_CONVERGED = 0, B200BA_ST_MAXITER = 1, B200BA_ST_NAN = 2, B200BA_ST_PCG_MAXITER = 4 };
+enum { B200BA_ST_CONVERGED = 0, B200BA_ST_MAXITER = 1, B200BA_ST_NAN = 2, B200BA_ST_PCG_MAXITER = 4,
+       B200BA_ST_XCHG_TIMEOUT = 8 /* multi-rank: a peer's partial sums never arrived; the solve returns B200BA_ENCCL */ };
 enum { B200BA_LOSS_L2 = 0, B200BA_LOSS_CAUCHY = 1 }; /* loss.py:7-14 */
 
 const char* b200ba_last_error(void);

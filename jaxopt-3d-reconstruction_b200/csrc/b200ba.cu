@@ -1067,6 +1067,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
       fprintf(stderr, "[b200ba] it %d loss %.9e |g| %.3e mu %.3e rho %.3e acc %d pcg %d\n", it, p->st_host->loss, err,
               p->st_host->mu, p->st_host->rho, accepted, pcg_iters);
     status |= p->st_host->status;
+    if (status & B200BA_ST_XCHG_TIMEOUT) FAIL(B200BA_ENCCL, "lm_solve: timed out waiting for a peer's partial sums (peer-memory exchange)");
     if (!(it < opts->maxiter && err > opts->tol)) break;  // run(): NaN error also stops (NaN > tol is false)
   }
   if (err > opts->tol) status |= B200BA_ST_MAXITER;

@@ -10,12 +10,34 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _run(nproc, shape, env_extra):
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs >= {nproc} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr",
+           "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), shape]
+    env = dict(os.environ, **env_extra)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "MULTI_GPU_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    return r.stdout + r.stderr
+
+
 @pytest.mark.parametrize("shape", ["small", "ladybug49"])
 def test_point_sharded_solve_matches_single_gpu(shape):
-    n = torch.cuda.device_count()
-    if n < 2:
-        pytest.skip("needs >= 2 GPUs")
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-           "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "multi_gpu_worker.py"), shape]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0 and "MULTI_GPU_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    """Default path: per-iteration partial sums over peer memory (CUDA IPC), the rest over NCCL."""
+    out = _run(2, shape, {"B200BA_VERBOSE": "1"})
+    assert "partial sums over peer memory" in out, out[-2000:]
+
+
+def test_nccl_exchange_fallback_matches_single_gpu():
+    """B200BA_P2P=0: the 8C partial-sum vector goes through an NCCL all-reduce instead."""
+    out = _run(2, "ladybug49", {"B200BA_P2P": "0", "B200BA_VERBOSE": "1"})
+    assert "partial sums over NCCL" in out, out[-2000:]
+
+
+def test_cameras_cut_into_many_warp_tasks_multi_rank():
+    """64-row tasks: every camera's partial sum is assembled by the last-arriver path on every rank."""
+    _run(2, "trafalgar257", {"B200BA_TASK_ROWS": "64"})
+
+
+def test_four_ranks():
+    _run(4, "trafalgar257", {})
