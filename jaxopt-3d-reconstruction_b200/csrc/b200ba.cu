@@ -796,7 +796,7 @@ struct Ops {
            p->beta_B, p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
-    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(C, 64), 64, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
+    PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(8 * (int64_t)C, CF_T), CF_T, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
             p->Minv, p->rhs, p->cv, p->part2);
     PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
     cs(p, PC_MV_CAM, CS_A, CV_U, s);

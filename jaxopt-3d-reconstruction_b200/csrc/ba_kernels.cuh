@@ -377,56 +377,58 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
   }
 }
 
-// rhs = g_c + rhs_part; Minv_c = (U_c + mu I + Sd_part)^-1 (8x8, Cholesky, one thread per camera);
-// PCG start: x = 0, r = rhs, u = Minv r, all other vectors 0; part[4c+2] = r.r
-__global__ void __launch_bounds__(64)
+// rhs = g_c + rhs_part; Minv_c = (U_c + mu I + Sd_part)^-1 (8x8 Cholesky; 8 threads per camera, thread j factors
+// the block and solves for column j of the inverse — the arithmetic per column is what one thread per camera did,
+// 8x shorter); PCG start: x = 0, r = rhs, u = Minv r, all other vectors 0; part[4c+2] = r.r
+#define CF_T 256
+__global__ void __launch_bounds__(CF_T)
 k_cam_finish_prepare(int C, const double* __restrict__ mu_ptr, const double* __restrict__ U,
                      const double* __restrict__ gc, const double* __restrict__ Sd_part,
                      const double* __restrict__ rhs_part, double* __restrict__ Minv,
                      double* __restrict__ rhs, double* __restrict__ cv, double* __restrict__ part) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  __shared__ double sMi[CF_T / 8][64];
+  __shared__ double szz[CF_T / 8][8];
+  const int e0 = blockIdx.x * CF_T + threadIdx.x;
+  const int c = e0 >> 3, col = e0 & 7, g = threadIdx.x >> 3;
+  const bool act = c < C;
+  const size_t cc = act ? c : C - 1;
   const double mu = *mu_ptr;
-  double A[64], L[64], e[8], Mi[64];
+  double L[64], e[8];
 #pragma unroll
-  for (int k = 0; k < 64; ++k) A[k] = U[64 * (size_t)c + k] + Sd_part[64 * (size_t)c + k];
+  for (int k = 0; k < 64; ++k) L[k] = U[64 * cc + k] + Sd_part[64 * cc + k];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) A[9 * k] += mu;
+  for (int k = 0; k < 8; ++k) L[9 * k] += mu;
 #pragma unroll
-  for (int col = 0; col < 8; ++col) {
+  for (int k = 0; k < 8; ++k) e[k] = (k == col) ? 1.0 : 0.0;
+  chol8_solve(L, e);
 #pragma unroll
-    for (int k = 0; k < 64; ++k) L[k] = A[k];
+  for (int k = 0; k < 8; ++k) sMi[g][8 * k + col] = e[k];
+  __syncwarp();
+  // thread col -> row col of the symmetrised inverse
+  double row[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) e[k] = (k == col) ? 1.0 : 0.0;
-    chol8_solve(L, e);
+  for (int l = 0; l < 8; ++l) row[l] = 0.5 * (sMi[g][8 * col + l] + sMi[g][8 * l + col]);
+  double rr[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) Mi[8 * k + col] = e[k];
+  for (int k = 0; k < 8; ++k) rr[k] = gc[8 * cc + k] + rhs_part[8 * cc + k];
+  double zk = 0.0;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) zk += row[l] * rr[l];
+  szz[g][col] = zk;
+  __syncwarp();
+  if (!act) return;
+#pragma unroll
+  for (int l = 0; l < 8; ++l) Minv[64 * cc + 8 * col + l] = row[l];
+  double* v = cv + (size_t)72 * cc;  // camera-major PCG record: x r u w z q s p m
+  rhs[8 * cc + col] = gc[8 * cc + col] + rhs_part[8 * cc + col];
+  v[col] = 0.0; v[8 + col] = gc[8 * cc + col] + rhs_part[8 * cc + col]; v[16 + col] = zk;
+  v[24 + col] = 0.0; v[32 + col] = 0.0; v[40 + col] = 0.0; v[48 + col] = 0.0; v[56 + col] = 0.0; v[64 + col] = 0.0;
+  if (col == 0) {
+    double rz = 0.0, r2 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { rz += szz[g][k] * rr[k]; r2 += rr[k] * rr[k]; }
+    part[4 * cc] = rz;
+    part[4 * cc + 1] = 0.0;
+    part[4 * cc + 2] = r2;
   }
-  double rr[8], zz[8];
-  double rz = 0.0, r2 = 0.0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) rr[k] = gc[8 * (size_t)c + k] + rhs_part[8 * (size_t)c + k];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    double s = 0.0;
-#pragma unroll
-    for (int l = 0; l < 8; ++l) s += 0.5 * (Mi[8 * k + l] + Mi[8 * l + k]) * rr[l];
-    zz[k] = s;
-    rz += s * rr[k];
-    r2 += rr[k] * rr[k];
-  }
-#pragma unroll
-  for (int k = 0; k < 8; ++k)
-#pragma unroll
-    for (int l = 0; l < 8; ++l) Minv[64 * (size_t)c + 8 * k + l] = 0.5 * (Mi[8 * k + l] + Mi[8 * l + k]);
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    double* v = cv + (size_t)72 * c;  // camera-major PCG record: x r u w z q s p m
-    rhs[8 * (size_t)c + k] = rr[k];
-    v[k] = 0.0; v[8 + k] = rr[k]; v[16 + k] = zz[k]; v[24 + k] = 0.0; v[32 + k] = 0.0; v[40 + k] = 0.0; v[48 + k] = 0.0;
-    v[56 + k] = 0.0; v[64 + k] = 0.0;
-  }
-  part[4 * (size_t)c] = rz;
-  part[4 * (size_t)c + 1] = 0.0;
-  part[4 * (size_t)c + 2] = r2;
 }
