@@ -285,6 +285,11 @@ def run_b200(args):
     # ---- end to end through the public API with HOST buffers (H2D of rows+params, D2H of params)
     e2e = None
     if True:
+        # one untimed warm-up solve through the same API: the first plan built next to the resident one grows
+        # the stream-ordered memory pool (a one-off of tens of ms that is not part of the steady state)
+        pr = ba.build_problem_sparse(h_cam, h_pt, h_obs, sc.P)
+        ba.optimize(h_x0, pr, None, h_k3, None)
+        pr.close()
         barrier()
         t0 = time.perf_counter()
         its, h2d, d2h, nsolves = 0, 0, 0, 0
@@ -301,7 +306,7 @@ def run_b200(args):
         t_e2e = max_over_ranks(t_e2e * 1e3) * 1e-3
         e2e = {"value": its / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d / its),
                "d2h_bytes_per_step": int(d2h / its), "solves": nsolves, "lm_iterations": its,
-               "includes": "H2D of index/observation rows and parameters from pinned memory, plan build "
+               "includes": "after one untimed warm-up solve: H2D of index/observation rows and parameters from pinned memory, plan build "
                            "(GPU sort + workspace allocation), LM solve, D2H of optimised parameters"}
 
     if rank != 0:

@@ -318,8 +318,36 @@ k_pcg_verify(int C, SolverState* __restrict__ st, const double* __restrict__ par
 #ifndef PS_OWN
 #define PS_OWN 1  // row -> local point through a shared-memory byte/short map written by the point lanes (no pt_A load)
 #endif
+#ifndef PS_GATHER
+#define PS_GATHER 1  // sigma gather: 0 = ld.global.nc, 1 = ld.global.nc.L1::no_allocate (measured 72.5 -> 69.9 us at Venice)
+#endif
+#ifndef PS_SCATTER
+#define PS_SCATTER 2  // omega scatter: 0 = st.global, 1 = st.global.cg (L2 only), 2 = st.global.L1::no_allocate
+#endif
+__device__ __forceinline__ double ps_gather(const double* p) {
+#if PS_GATHER == 1
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+#else
+  return __ldg(p);
+#endif
+}
+__device__ __forceinline__ void ps_scatter(double* p, double v) {
+#if PS_SCATTER == 1
+  asm volatile("st.global.cg.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+#elif PS_SCATTER == 2
+  asm volatile("st.global.L1::no_allocate.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+#else
+  *p = v;
+#endif
+}
 template <typename JT, bool BACKSUB>
+#ifdef PS_MINB
+__global__ void __launch_bounds__(PS_T, PS_MINB)
+#else
 __global__ void __launch_bounds__(PS_T)
+#endif
 k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxiter, SolverState* __restrict__ st,
      const double* __restrict__ cpart, const int32_t* __restrict__ chunk_row, const int32_t* __restrict__ chunk_pt,
      const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ pt_A, const int32_t* __restrict__ posB,
@@ -374,7 +402,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     }
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j)
-      if (tid + j * PS_T < nrows) s[j] = __ldg(sig + dst[j]);
+      if (tid + j * PS_T < nrows) s[j] = ps_gather(sig + dst[j]);
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j) {
       const int i = tid + j * PS_T;
@@ -412,7 +440,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
 #ifdef PS_DEBUG
           if (q < 0 || q >= npts || dst[j] < 0) { printf("k_ps: ch %d tid %d i %d q %d npts %d nrows %d dst %d\n", ch, tid, i, q, npts, nrows, dst[j]); q = 0; }
 #endif
-          omg[dst[j]] = (double)b[j][0] * sz[0][q] + (double)b[j][1] * sz[1][q] + (double)b[j][2] * sz[2][q];
+          ps_scatter(omg + dst[j], (double)b[j][0] * sz[0][q] + (double)b[j][1] * sz[1][q] + (double)b[j][2] * sz[2][q]);
         }
       }
     }

@@ -183,6 +183,31 @@ def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows):
     np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
 
 
+def _drop_camera_rows(sc, cam, keep_point):
+    """Remove the observations of camera `cam` on the points where keep_point is False, as long as the point
+    keeps >= 2 observations.  Returns filtered (cam_idx, pt_idx, obs)."""
+    deg = np.bincount(sc.pt_idx, minlength=sc.P)
+    drop = (sc.cam_idx == cam) & ~keep_point[sc.pt_idx] & (deg[sc.pt_idx] > 2)
+    return sc.cam_idx[~drop], sc.pt_idx[~drop], sc.obs[~drop]
+
+
+@pytest.mark.parametrize("split", ["0", "1"])
+def test_camera_with_very_few_rows(monkeypatch, split):
+    """One camera keeps only a handful of rows (empty runs in most point blocks, a nearly empty warp task / ring
+    step): same trajectory as the exact oracle, on the fused and on the split camera path."""
+    monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
+    monkeypatch.setenv("B200BA_BLOCK_ROWS", "2048")
+    sc, ba, x0, k3 = _setup("ladybug49", jac_f32=True)
+    keep = np.zeros(sc.P, dtype=bool)
+    keep[:40] = True
+    ci, pi, ob = _drop_camera_rows(sc, 3, keep)
+    assert 0 < (ci == 3).sum() < 60
+    params, st = ba.optimize(x0, ba.build_problem_sparse(ci, pi, ob, sc.P), None, k3, None)
+    ref = bo.lm_solve(x0, sc.C, sc.P, ci, pi, ob, k3, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+
+
 def test_schur_matvec_matches_dense_schur_complement():
     """b200ba_schur_matvec (camera head -> point kernel -> camera tail) against S formed densely by the oracle's
     formulas: S = U + mu I - W (V + mu I)^-1 W^T."""

@@ -39,5 +39,9 @@ def test_cameras_cut_into_many_warp_tasks_multi_rank():
     _run(2, "trafalgar257", {"B200BA_TASK_ROWS": "64"})
 
 
+def test_camera_without_rows_on_one_rank():
+    _run(2, "ladybug49_gap", {})
+
+
 def test_four_ranks():
     _run(4, "trafalgar257", {})
