@@ -65,6 +65,7 @@ struct b200ba_plan {
   int32_t *camtab = nullptr, *cam_order = nullptr;                   // B: per-camera run tables; cameras by descending rows
   int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
   WarpTask* wtask = nullptr; double* wpart = nullptr; int* wcount = nullptr; int nwtasks = 0;  // warp-task camera kernel
+  int cw_u = 4;                                                      // k_cs_warp unroll (3 | 4 | 6)
   int cb_threads = 256;                                              // k_cam_blocks CTA size
   int xchg = 0; int xseq_last = 0;                                   // partial sums exchanged over peer memory (else NCCL)
   int split = 0;                                                     // all-reduce points between matvec tail and head (nranks > 1, or forced)
@@ -112,6 +113,13 @@ struct b200ba_plan {
 };
 enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, PC_CAM_FINISH, PC_MV_PT, PC_MV_CAM,
        PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_COUNT };
+// k_cs_warp with the plan's unroll (see ba_cs_warp.cuh)
+#define CW_LAUNCH(p, cls, grid, st, ...)                                                                   \
+  do {                                                                                                     \
+    if ((p)->cw_u == 3) PLAUNCH(p, cls, (k_cs_warp<JT, 3>), grid, CW_T, 0, st, __VA_ARGS__);               \
+    else if ((p)->cw_u == 6) PLAUNCH(p, cls, (k_cs_warp<JT, 6>), grid, CW_T, 0, st, __VA_ARGS__);          \
+    else PLAUNCH(p, cls, (k_cs_warp<JT, 4>), grid, CW_T, 0, st, __VA_ARGS__);                              \
+  } while (0)
 #define PLAUNCH(p, cls, kern, grid, block, smem, st, ...)                                \
   do {                                                                                   \
     size_t i0_ = 0, i1_ = 0;                                                             \
@@ -397,12 +405,23 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     p->max_cam_rows = (int)mx;
     cudaMemcpyAsync(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaMemcpyAsync(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice, s);
-    // warp tasks of the split camera passes: <= CW_ROWS local rows each, cameras in descending size, every camera
-    // at least one task (a camera without rows on this rank still has to publish a zero partial sum)
-    // Task size: about one resident wave of warps over the rank's rows, never so small that the fixed cost of a
-    // task dominates; a camera is cut into H near-equal parts only when it is well above that size.
+    // Warp tasks of the split camera passes: cameras in descending size, every camera at least one task (a camera
+    // without rows on this rank still has to publish a zero partial sum).  Measured rule (tools/cs_warp_probe.py,
+    // one rank's share of Venice-1778 / Final-13682 at 2, 4, 8 ranks): whole cameras as tasks whenever there are
+    // enough of them to fill the SMs; deep unroll (6 row loads in flight per lane, 16 warps/SM) when all cameras
+    // fit in one resident wave, otherwise more, lighter warps (unroll 4 at >= 400 rows per camera, else 3).
+    // Few cameras: cut them into H near-equal parts so that about one wave of warps is busy.
     std::vector<WarpTask> wt;
-    int target = (int)std::min<int64_t>(1024, std::max<int64_t>(256, p->NB / 3552));
+    {
+      int n_sm = 148;
+      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+      const int64_t avg = p->NB / (C > 0 ? C : 1);
+      p->cw_u = (C <= n_sm * 20) ? 6 : (avg >= 400 ? 4 : 3);
+      if (!p->jac_f32 && p->cw_u == 6) p->cw_u = 4;  // fp64 rows: 160 registers at unroll 6
+    }
+    if (const char* e = getenv("B200BA_CW_U")) { const int v = atoi(e); if (v == 3 || v == 4 || v == 6) p->cw_u = v; }
+    const int64_t wslots = (int64_t)148 * (p->cw_u == 6 ? 16 : p->cw_u == 4 ? 24 : 32);
+    int target = (int)std::min<int64_t>(4096, std::max<int64_t>(256, p->NB / wslots));
     if (const char* e = getenv("B200BA_TASK_ROWS")) { const int v = atoi(e); if (v >= 32) target = v; }
     wt.reserve((size_t)C + (size_t)(p->NB / target) + 1);
     for (int i = 0; i < C; ++i) {
@@ -742,7 +761,7 @@ struct Ops {
       double* xy = p->y;
       if (p->xchg && (flags & CS_C)) { p->xseq_last = ++g_x.seq; xy = g_x.base + XF_INTS / 2 + (size_t)(g_x.seq & 1) * g_x.ycap; }
       if (flags & CS_C)
-        PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_C | ign, p->st, p->camtab, p->wtask,
+        CW_LAUNCH(p, cls, grid, s, p->nwtasks, p->nPB, CS_C | ign, p->st, p->camtab, p->wtask,
                 (const JT*)p->Jc_B, p->omg, p->sig, p->cv, 0, xy, p->wpart, p->wcount, g_x.peers, p->rank, p->xchg == 1 ? p->nranks : 1,
                 p->xseq_last, p->wcount + p->C);
       int vs = vin_slot;
@@ -753,7 +772,7 @@ struct Ops {
         if (upd) vs = CV_M;
       }
       if (flags & CS_A)
-        PLAUNCH(p, cls, (k_cs_warp<JT>), grid, CW_T, 0, s, p->nwtasks, p->nPB, CS_A | ign, p->st, p->camtab, p->wtask,
+        CW_LAUNCH(p, cls, grid, s, p->nwtasks, p->nPB, CS_A | ign, p->st, p->camtab, p->wtask,
                 (const JT*)p->Jc_B, p->omg, p->sig, p->cv, vs, p->y, p->wpart, p->wcount, g_x.peers, p->rank, 1, 0, nullptr);
       return;
     }

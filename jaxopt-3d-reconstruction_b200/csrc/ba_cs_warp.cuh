@@ -17,7 +17,6 @@
 #ifndef CW_ROWS
 #define CW_ROWS 512
 #endif
-#define CW_U 4
 
 // 8 per-lane accumulators -> lane (l & ~3 == component pattern) holds the warp total of ONE component:
 // 18 shuffles instead of 40.  Returns the total of component comp8(lane) (valid in every lane).
@@ -102,7 +101,7 @@ struct __align__(32) WarpTask {
   int nparts, t0;   // tasks of this camera, index of its first task
   int pad[2];
 };
-template <typename JT>
+template <typename JT, int CW_U>
 __device__ __forceinline__ void
 k_cs_warp_task(int t, int lane, int nPB, int flags, const int32_t* __restrict__ camtab,
                const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
@@ -205,8 +204,10 @@ k_cs_warp_task(int t, int lane, int nPB, int flags, const int32_t* __restrict__ 
   }
 }
 
-template <typename JT>
-__global__ void __launch_bounds__(CW_T)
+// CW_U = row loads in flight per lane: 3 (<= 64 registers with fp32 rows, 4 CTAs/SM) for many small tasks, 6 (2 CTAs/SM)
+// for few large ones — the bytes in flight per SM are the same, the task granularity is not (tools/cs_warp_probe.py)
+template <typename JT, int CW_U>
+__global__ void __launch_bounds__(CW_T, sizeof(JT) == 4 ? (CW_U <= 3 ? 4 : CW_U == 4 ? 3 : 2) : (CW_U <= 4 ? 2 : 1))
 k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
           const WarpTask* __restrict__ wtask, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
           double* __restrict__ sig, const double* __restrict__ cv, int vin_slot, double* __restrict__ y,
@@ -214,7 +215,7 @@ k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, co
   const int lane = threadIdx.x & 31;
   const int t = blockIdx.x * (CW_T / 32) + (threadIdx.x >> 5);
   const bool work = ((flags & CS_IGNORE_DONE) || !st->pcg_done) && t < ntasks;  // warp-uniform
-  if (work) k_cs_warp_task<JT>(t, lane, nPB, flags, camtab, wtask, Jc_B, omg, sig, cv, vin_slot, y, wpart, wcount);
+  if (work) k_cs_warp_task<JT, CW_U>(t, lane, nPB, flags, camtab, wtask, Jc_B, omg, sig, cv, vin_slot, y, wpart, wcount);
   // multi-rank: tell the peers that this rank's partial sums of iteration seq are complete (also when the solve is
   // finished and nothing was written: the receiving side waits for every seq)
   if (nr > 1) xchg_signal_when_last(px, rank, nr, seq, xctr);

@@ -29,8 +29,12 @@ SHAPES = {
     "final13682": (13682, 4456117, 28987644),
     # what ONE rank of a point-sharded Final-13682 solve holds at 4 / 8 ranks (all cameras, 1/4 or 1/8 of the points):
     # single-GPU stand-ins for profiling the multi-rank kernels (B200BA_FORCE_SPLIT=1)
+    "final13682_r2": (13682, 2228058, 14493822),
     "final13682_r4": (13682, 1114029, 7246911),
     "final13682_r8": (13682, 557015, 3623456),
+    "venice1778_r2": (1778, 496962, 2500973),
+    "venice1778_r4": (1778, 248481, 1250487),
+    "venice1778_r8": (1778, 124240, 625243),
 }
 
 WIDTH = 1000.0
