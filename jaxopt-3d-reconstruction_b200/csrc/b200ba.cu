@@ -502,13 +502,16 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, "plan_create: shared-memory stash configuration");
     }
-    const size_t budget = (size_t)smem_max - 1024;
+    int smem_sm = 0;
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    size_t budget = (size_t)smem_max - 1024;
+    if (RING_MINB > 1) budget = std::min(budget, (size_t)smem_sm / RING_MINB - 1024 - 512);  // per-CTA reserve + static
     const size_t slotb = p->jac_f32 ? RingCfg<float>::slot_bytes : RingCfg<double>::slot_bytes;
     const size_t fixedb = p->jac_f32 ? RingCfg<float>::fixed_bytes : RingCfg<double>::fixed_bytes;
     int slots = budget > fixedb ? (int)((budget - fixedb) / slotb) : 0;
     if (const char* e = getenv("B200BA_RING_SLOTS")) { const int v = atoi(e); if (v >= 0 && v < slots) slots = v; }
     p->ring_slots = 0;
-    if (slots >= 2 && (int64_t)slots * RING_R >= mx && nPB <= MAXPB) {
+    if (slots >= 2 && ((int64_t)slots * RING_R >= mx || RING_MINB > 1) && nPB <= MAXPB) {
       p->ring_slots = slots;
       p->ring_smem = fixedb + (size_t)slots * slotb;
       e1 = cudaFuncSetAttribute(k_cs_ring<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->ring_smem);
@@ -777,7 +780,7 @@ struct Ops {
       return;
     }
     if (p->ring_slots && (fused || half1 || half2)) {
-      const int grid = p->C < p->n_sm ? p->C : p->n_sm;
+      const int grid = p->C < p->n_sm * RING_MINB ? p->C : p->n_sm * RING_MINB;
       PLAUNCH(p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, p->camtab,
               p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->y, p->cv, p->part2);
       return;

@@ -13,8 +13,13 @@
 #pragma once
 #include "ba_pcg.cuh"
 
-#define RING_R 512                 // rows per slot
-#define RING_CW 16                 // consumer warps (RING_R == 32 * RING_CW: one row per thread per slot)
+#ifndef RING_CW
+#define RING_CW 16                 // consumer warps
+#endif
+#ifndef RING_MINB
+#define RING_MINB 1                // CTAs per SM (2: two half-size CTAs interleave their per-camera reduce/update bubbles)
+#endif
+#define RING_R (32 * RING_CW)      // rows per slot: one row per consumer thread
 #define RING_T ((RING_CW + 1) * 32)
 
 struct __align__(16) RingCam {  // everything about one in-flight camera
@@ -35,7 +40,10 @@ struct RingCfg {
 #define RING_EXP 0  // timing experiments only: 1 no pass-A math, 2 no update, 4 no pass-C math, 8 no cross-lane reduce
 #endif
 // slots of rows a consumer thread keeps in registers between pass C and pass A (fp32 rows: 6 x 8 regs; fp64 rows: 3 x 16)
-template <typename JT> struct RingKeep { static constexpr int N = sizeof(JT) == 4 ? 6 : 3; };
+#ifndef RING_KEEP32
+#define RING_KEEP32 6
+#endif
+template <typename JT> struct RingKeep { static constexpr int N = sizeof(JT) == 4 ? RING_KEEP32 : RING_KEEP32 / 2; };
 #define RING_KEEP (RingKeep<JT>::N)
 #define RING_NCAM 3  // camera records in flight: consumers on i, rows streaming for i+1, record/table of i+2 landing
 
@@ -91,7 +99,7 @@ struct RingSteps<JT, 0> {
 };
 
 template <typename JT>
-__global__ void __launch_bounds__(RING_T, 1)
+__global__ void __launch_bounds__(RING_T, RING_MINB)
 k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
           const int32_t* __restrict__ cam_order, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
           double* __restrict__ sig, const double* __restrict__ U, const double* __restrict__ Minv, int vin_slot,
