@@ -118,7 +118,12 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   int* s_run0 = reinterpret_cast<int*>(bar_cempty + RING_NCAM);  // first run of the chunk held by each slot
   if (st->pcg_done) return;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  // PCG scalars once into shared memory: kept as plain `st->x` the compiler re-loads them from GLOBAL memory at
+  // their use inside every camera's serial update (register pressure) — two dependent round trips per camera,
+  // 68 -> 64 us for the whole kernel at Venice
+  __shared__ double s_scal[4];
   if (tid == 0) {
+    s_scal[0] = st->mu; s_scal[1] = st->alpha; s_scal[2] = st->beta;
     for (int i = 0; i < nslots; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, RING_CW); }
     for (int i = 0; i < RING_NCAM; ++i) { mbar_init(bar_cfull + i, 1); mbar_init(bar_cempty + i, RING_CW); }
     mbar_fence_init();
@@ -194,7 +199,6 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   // to the producer as soon as pass C has read it: the ring is pure prefetch depth (~2 cameras ahead) and
   // HBM streaming never waits for the serial reduce / update / pass-A phases of a camera.
   int ring = 0, ring_ph = 0;
-  const double mu = st->mu, alpha = st->alpha, beta = st->beta;
   for (int i = 0; i < ncam; ++i) {
     const int cb = i % RING_NCAM, ph = (i / RING_NCAM) & 1;
     mbar_wait(bar_cfull + cb, ph);
@@ -274,6 +278,7 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
       }
       if ((flags & CS_WRITE_Y) && lane < 8) y[8 * (size_t)c + k] = n0 + n1;  // multi-rank first half: partial sums out
       if (flags & (CS_INIT | CS_ITER)) {
+        const double mu = s_scal[0], alpha = s_scal[1], beta = s_scal[2];
         const double mk = (RING_EXP & 2) ? n0 + n1 + B.sv[k]
                                          : cs_update(flags, k, lane, n0 + n1, B.sv, mu, alpha, beta, cv + (size_t)CV_STRIDE * c,
                                                      part + 4 * (size_t)c, vin_slot);
