@@ -273,8 +273,8 @@ def run_b200(args):
                 kern[nm].update({"alg_bytes": int(bm[nm]), "gbs": round(gbs, 1), "frac": round(gbs / peak, 4)})
     dom = max((k for k in kern if k in bm), key=lambda k: kern[k]["total_ms"])
     # dram__bytes_read+write per launch of the dominant kernel from the committed ncu --set full capture of this
-    # workload (profiles/ncu_r1_v5_summary.md); other workloads / rank counts: not captured
-    ncu_traffic = {"mv_pt": 198.4e6, "mv_cam": 233.0e6} if (args.workload == "venice1778" and world == 1 and not args.jac_f64) else {}
+    # workload (profiles/ncu_r1_v8_summary.md); other workloads / rank counts: not captured
+    ncu_traffic = {"mv_pt": 208.1e6, "mv_cam": 232.9e6} if (args.workload == "venice1778" and world == 1 and not args.jac_f64) else {}
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s",
                 "frac": kern[dom]["frac"], "traffic": ncu_traffic.get(dom), "peak_source": peak_src,
                 "share_of_step": round(kern[dom]["total_ms"] / sum(v["total_ms"] for v in kern.values()), 4)}
