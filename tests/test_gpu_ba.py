@@ -166,8 +166,9 @@ def test_point_block_size_does_not_matter(monkeypatch):
     np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
 
 
+@pytest.mark.parametrize("cw_u", ["3", "4", "6"])
 @pytest.mark.parametrize("task_rows", ["64", "100000"])
-def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows):
+def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows, cw_u):
     """The multi-rank kernel sequence (warp-task partial sums | all-reduce point | camera-local vector step |
     warp-task sigma pass) forced onto one rank must reproduce the fused ring-kernel iteration; 64-row tasks cut
     every camera into many parts (ordered last-arriver sum), 100000-row tasks keep cameras whole."""
@@ -176,6 +177,7 @@ def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows):
     for split in ("0", "1"):
         monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
         monkeypatch.setenv("B200BA_TASK_ROWS", task_rows)
+        monkeypatch.setenv("B200BA_CW_U", cw_u)  # all three unroll instantiations of k_cs_warp
         out.append(ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None))
     (pa, sa), (pb, sb) = out
     assert sa.iter_num == sb.iter_num
