@@ -63,7 +63,6 @@ struct b200ba_plan {
   int32_t *posB = nullptr, *posA = nullptr;                          // A row -> B position; B position -> A row (padding: N)
   int32_t *pt_ptr = nullptr;                                         // A: CSR by point
   int32_t *camtab = nullptr, *cam_order = nullptr;                   // B: per-camera run tables; cameras by descending rows
-  int* tickets = nullptr;                                            // ring kernel: camera ticket counter, finished CTAs
   WarpTask* wtask = nullptr; double* wpart = nullptr; int* wcount = nullptr; int nwtasks = 0;  // warp-task camera kernel
   int cw_u = 4;                                                      // k_cs_warp unroll (3 | 4 | 6)
   int cb_threads = 256;                                              // k_cam_blocks CTA size
@@ -281,7 +280,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
 #define A(ptr, n) if ((rc = dalloc(p, &p->ptr, (n)))) { b200ba_plan_destroy(p); return rc; }
   A(cam_ps, N) A(pt_ps, N) A(order_ps, N) A(posB, N)
   A(pt_ptr, P + 1)
-  A(camtab, (size_t)C * (((p->nPB + 3) & ~3) + ((p->nPB + 4) & ~3))) A(cam_order, C) A(tickets, 2)
+  A(camtab, (size_t)C * (((p->nPB + 3) & ~3) + ((p->nPB + 4) & ~3))) A(cam_order, C)
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
   A(cv, (size_t)C * CV_STRIDE) A(y, (size_t)C * 8 + 8)
@@ -304,7 +303,6 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     FAIL(B200BA_ECUDA, "cudaMallocHost failed");
   }
   cudaMemsetAsync(p->st, 0, sizeof(SolverState), s);
-  cudaMemsetAsync(p->tickets, 0, 2 * sizeof(int), s);
   cudaMemsetAsync(p->vp, 0, (size_t)(P ? P : 1) * 3 * sizeof(double), s);
 
   std::vector<int32_t> hrun, hstart;  // unpadded run offsets / padded run starts (B order, run-major)

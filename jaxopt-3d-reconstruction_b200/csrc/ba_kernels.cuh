@@ -125,13 +125,6 @@ __device__ __forceinline__ void ld_rec(const RowRec<double>* p, double* b, doubl
   b[0] = v[0]; b[1] = v[1]; b[2] = v[2]; r = v[3];
 }
 
-// ---------------------------------------------------------------- K0: camera tables
-__global__ void k_cam_table(int C, const double* __restrict__ cam8, const double* __restrict__ k3,
-                            double* __restrict__ tab) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c < C) build_cam_table(cam8 + 8 * c, k3 + 3 * c, tab + (size_t)TAB_STRIDE * c);
-}
-
 // ---------------------------------------------------------------- K0+K1: residual + Jacobian rows
 // One CTA per camera walks the camera's rows in B order (runs of consecutive points inside a point
 // block).  The 26-double camera table is built once per CTA in shared memory (every lane reads the same

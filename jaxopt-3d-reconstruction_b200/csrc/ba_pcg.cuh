@@ -41,9 +41,9 @@ enum {
 #define CS_NW (CS_T / 32)
 
 // ---------------------------------------------------------------- K3b camera side (fused)
-// Generic version (any camera size, fp32 or fp64 rows, also the split multi-rank variants): one CTA per
-// camera, rows through registers, optional shared-memory stash.  The hot single-rank path uses the
-// TMA ring kernel in ba_cs_ring.cuh instead.
+// Generic version (any camera size, fp32 or fp64 rows): one CTA per camera, rows through registers, optional
+// shared-memory stash.  The hot single-rank path uses the TMA ring kernel in ba_cs_ring.cuh instead, the
+// multi-rank iteration and every sigma-only pass the warp-task kernels in ba_cs_warp.cuh.
 // Camera-local update shared by both kernels; executed by the 8-lane groups of one warp (lane&7 = component).
 // sv: [0,72) the camera's cv record, [72,136) U_c, [136,200) Minv_c.  Returns m_k (the next matvec input).
 __device__ __forceinline__ double cs_update(int flags, int k, int lane, double nk, const double* sv, double mu,
