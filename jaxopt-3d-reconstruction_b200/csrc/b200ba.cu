@@ -598,9 +598,20 @@ static struct {
   XPeers peers{};
   int nranks = 0, ok = 0, seq = 0;
 } g_x;
+// Collective when a communicator exists: every rank first unmaps its peers' blocks, then all ranks meet (a 1-byte
+// all-gather as the barrier), and only then each rank frees its own block — no block is freed while a peer still
+// has it mapped.
 static void xchg_release() {
   for (int r = 0; r < g_x.nranks; ++r)
     if (g_x.peers.base[r] && g_x.peers.base[r] != g_x.base) cudaIpcCloseMemHandle(g_x.peers.base[r]);
+  if (g_comm && g_x.nranks > 1 && g_x.nranks == g_nranks) {  // the same on every rank (never a local success flag)
+    unsigned char* d = nullptr;
+    if (cudaMalloc((void**)&d, (size_t)g_nranks) == cudaSuccess) {
+      ncclAllGather(d + g_rank, d, 1, ncclChar, g_comm, nullptr);
+      cudaStreamSynchronize(nullptr);
+      cudaFree(d);
+    }
+  }
   if (g_x.base) cudaFree(g_x.base);
   g_x = {};
 }

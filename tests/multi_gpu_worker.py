@@ -14,12 +14,23 @@ import b200ba  # noqa: E402
 
 
 def main():
-    shape = sys.argv[1] if len(sys.argv) > 1 else "ladybug49"
+    shapes = (sys.argv[1] if len(sys.argv) > 1 else "ladybug49").split("+")
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     rank, world = dist.get_rank(), dist.get_world_size()
+    # "a+b": several problems in ONE process (b with more cameras: the peer-memory exchange block is rebuilt)
+    flags = [solve_one(shape, dev, rank, world) for shape in shapes]
+    flag = torch.tensor([int(all(flags))], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    dist.destroy_process_group()
+    if rank == 0:
+        print("MULTI_GPU_OK" if flag.item() == 1 else "MULTI_GPU_FAIL", flush=True)
+    sys.exit(0 if flag.item() == 1 else 1)
+
+
+def solve_one(shape, dev, rank, world):
     gap = shape.endswith("_gap")
     sc = b200ba.synth.make_ba_scene(shape[:-4] if gap else shape, seed=0)
     if gap:
@@ -46,12 +57,7 @@ def main():
     ref = t.clone()
     dist.broadcast(ref, 0)
     same = bool(torch.equal(t, ref))
-    flag = torch.tensor([int(ok and same)], device=dev)
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    dist.destroy_process_group()
-    if rank == 0:
-        print("MULTI_GPU_OK" if flag.item() == 1 else "MULTI_GPU_FAIL", flush=True)
-    sys.exit(0 if flag.item() == 1 else 1)
+    return ok and same
 
 
 if __name__ == "__main__":

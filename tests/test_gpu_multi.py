@@ -43,5 +43,11 @@ def test_camera_without_rows_on_one_rank():
     _run(2, "ladybug49_gap", {})
 
 
+def test_exchange_block_grows_between_plans():
+    """Two problems in one process, the second with 17x the cameras: the IPC exchange block is released (peers unmap,
+    barrier, free) and rebuilt larger."""
+    _run(2, "small+trafalgar257", {})
+
+
 def test_four_ranks():
     _run(4, "trafalgar257", {})
