@@ -38,7 +38,9 @@ int b200ba_plan_destroy(b200ba_plan* plan);
 /* obs: N x 2 pixels in the SAME row order as cam_idx/pt_idx given to plan_create
  * (points_2d_all of bundle_adjustment.py:104-111 with mask==1 rows only). */
 int b200ba_plan_set_observations(b200ba_plan* plan, const double* obs_xy, void* stream);
-/* Optional: sum camera blocks / gradients / PCG dots across ranks (NCCL over NVLink).
+/* Optional: sum camera blocks / gradients across ranks (NCCL over NVLink) and exchange the per-PCG-iteration
+ * partial camera sums through peer memory (CUDA IPC block per rank; falls back to an NCCL all-reduce when a peer
+ * cannot be mapped).  Collective: every rank calls it for every plan.
  * unique_id_host: 128 bytes from b200ba_nccl_unique_id on rank 0, broadcast by the caller; the
  * communicator is created once per process and shared by later plans (pass NULL to re-use it). */
 int b200ba_nccl_unique_id(char* unique_id_host /*128 B*/);
