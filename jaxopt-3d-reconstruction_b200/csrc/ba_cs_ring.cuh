@@ -4,7 +4,8 @@
 // warp streams the cameras' Jacobian rows + omega values into a ring of shared-memory slots with 1-D
 // bulk async copies (cp.async.bulk, completion on mbarriers) — no registers and no warps are tied up
 // by loads in flight; the rows of the NEXT camera are already landing while the consumers finish the
-// current one, and the per-camera record (PCG vectors, U, Minv, run table) is fetched two cameras ahead.  16 CONSUMER warps do, per camera:
+// current one, and the per-camera record (PCG vectors, U, Minv, run table) is fetched two cameras ahead.
+// The CONSUMER warps (RING_CW = 12) do, per camera:
 //   pass C  n_c = -sum a_i omega_i over the camera's slots            (shared memory only)
 //   update  n_c += (U_c + mu) m_c; z,q,s,p,x,r,u,w recurrences; dot partials; m_c = Minv_c w_c
 //   pass A  sigma_i = a_i . m_c from the same slots -> global (coalesced per run), slots released
@@ -14,7 +15,10 @@
 #include "ba_pcg.cuh"
 
 #ifndef RING_CW
-#define RING_CW 16                 // consumer warps
+#define RING_CW 12                 // consumer warps.  12 warps x 128 registers (8 stashed rows per thread, no spills) beat
+#endif                             // 16 x 96 (6 rows, spills): 62.5 vs 64.1 us at Venice; 8 x 168 (12 rows): 74 us
+#ifndef RING_MAXREG
+#define RING_MAXREG 128            // 13 warps -> at most 4 on one SM sub-partition: 4 x 32 x 128 = its 16 K registers
 #endif
 #ifndef RING_MINB
 #define RING_MINB 1                // CTAs per SM (2: two half-size CTAs interleave their per-camera reduce/update bubbles)
@@ -39,9 +43,9 @@ struct RingCfg {
 #ifndef RING_EXP
 #define RING_EXP 0  // timing experiments only: 1 no pass-A math, 2 no update, 4 no pass-C math, 8 no cross-lane reduce
 #endif
-// slots of rows a consumer thread keeps in registers between pass C and pass A (fp32 rows: 6 x 8 regs; fp64 rows: 3 x 16)
+// slots of rows a consumer thread keeps in registers between pass C and pass A (fp32 rows: 8 x 8 regs; fp64 rows: 4 x 16)
 #ifndef RING_KEEP32
-#define RING_KEEP32 6
+#define RING_KEEP32 8
 #endif
 template <typename JT> struct RingKeep { static constexpr int N = sizeof(JT) == 4 ? RING_KEEP32 : RING_KEEP32 / 2; };
 #define RING_KEEP (RingKeep<JT>::N)
@@ -98,8 +102,13 @@ struct RingSteps<JT, 0> {
   static __device__ __forceinline__ void pass_a(const JT (&)[RING_KEEP][8], const int (&)[RING_KEEP], const double (&)[8], double* __restrict__) {}
 };
 
+#if RING_MAXREG > 0
+#define RING_BOUNDS __maxnreg__(RING_MAXREG)
+#else
+#define RING_BOUNDS __launch_bounds__(RING_T, RING_MINB)
+#endif
 template <typename JT>
-__global__ void __launch_bounds__(RING_T, RING_MINB)
+__global__ void RING_BOUNDS
 k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, const int32_t* __restrict__ camtab,
           const int32_t* __restrict__ cam_order, const JT* __restrict__ Jc_B, const double* __restrict__ omg,
           double* __restrict__ sig, const double* __restrict__ U, const double* __restrict__ Minv, int vin_slot,

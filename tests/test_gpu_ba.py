@@ -136,7 +136,7 @@ def test_fp32_rows_track_fp64_rows_at_scale():
 @pytest.mark.parametrize("cpn", [(3, 4000, 11500), (2, 6000, 12000)])
 def test_heavy_cameras_take_the_tail_and_fallback_paths(cpn, jac_f32):
     """Cameras with more rows than a thread's register stash (3072 fp32 / 1536 fp64 rows: ring tail path,
-    rows re-read in pass A) and more than the whole ring holds (5120 / 3072 rows: generic camera kernel)
+    rows re-read in pass A) and more than the whole ring holds (5376 / 2688 rows: generic camera kernel)
     must give the same trajectory as the exact oracle."""
     C, P, N = cpn
     sc = b200ba.synth.make_ba_scene(C=C, P=P, N=N, seed=2)
