@@ -3,7 +3,7 @@
 The directory name carries a hyphen (the contract's package name), so import it through the
 `b200ba` alias module at the repo root: `import b200ba`.
 """
-from . import synth  # noqa: F401
+from . import model_io, synth  # noqa: F401
 from .api import (B200BundleAdjustment, B200PoseOptimizer, BAKernels, BAProblem, LMState,  # noqa: F401
                   LossFunction, launch_count, pose_mat_to_vec, shard_points)
 from ._lib import B200BAError, LIB_PATH, SYMBOLS, load  # noqa: F401
