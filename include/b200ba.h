@@ -103,6 +103,16 @@ int b200ba_schur_solve(b200ba_plan* plan, double rtol, int maxiter, double* vc, 
 int b200ba_cost(b200ba_plan* plan, const double* cam8, const double* cam_const3,
                 const double* pts, double inv_w2, double* cost_host, void* stream);
 
+/* ---- reprojection-error evaluator: the step after the solve that feeds every metric and plot of the reference
+ * (Dataset.compute_reprojection_errors_alt, src/dataset/dataset.py:116-123, which calls
+ * Camera.compute_projection_errors_alt, src/dataset/camera.py:78-85, once per camera in a Python loop).
+ * Per observation e = loss(dx^2) + loss(dy^2) in pixels^2; loss 0 = TRIVIAL_LOSS (x), 1 = CAUCHY_LOSS (log(1 + x))
+ * (src/dataset/loss_functions.py:7-17).  err_rows: N values in the caller's ORIGINAL row order (or NULL);
+ * cam_sum: C ordered per-camera sums over this rank's rows (or NULL).  Asynchronous on `stream`. */
+int b200ba_reprojection_errors(b200ba_plan* plan, const double* cam8, const double* cam_const3,
+                               const double* pts, int loss, double* err_rows /*N*/, double* cam_sum /*C*/,
+                               void* stream);
+
 /* ---- K4: batched single-pose LM (JaxPoseOptimizer.optimize, pose_optimization.py:86-89 =
  * jit(vmap(LevenbergMarquardt(tol=1e-7, maxiter=100, solver="cholesky").run)) over
  * PoseOptimization.get_residuals :33-52).  One CTA per pose, early exit per pose.

@@ -1033,6 +1033,22 @@ extern "C" int b200ba_cost(b200ba_plan* p, const double* cam8, const double* k3,
   return B200BA_OK;
 }
 
+extern "C" int b200ba_reprojection_errors(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
+                                          int loss, double* err_rows, double* cam_sum, void* stream_) {
+  if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "reprojection_errors: null");
+  if (loss != 0 && loss != 1) FAIL(B200BA_EINVAL, "reprojection_errors: loss must be 0 (trivial) or 1 (Cauchy)");
+  cudaStream_t s = (cudaStream_t)stream_;
+  if (!p->C) return B200BA_OK;
+  if (loss)
+    PLAUNCH(p, PC_OTHER, (k_reproj_err<1>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
+            p->order_ps, pts, err_rows, cam_sum);
+  else
+    PLAUNCH(p, PC_OTHER, (k_reproj_err<0>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
+            p->order_ps, pts, err_rows, cam_sum);
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
 extern "C" void b200ba_lm_default_opts(b200ba_lm_opts* o) {
   if (!o) return;
   o->maxiter = 100;

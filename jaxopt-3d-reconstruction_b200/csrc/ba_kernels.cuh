@@ -170,6 +170,42 @@ k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__
   if (threadIdx.x == 0) cost_part[c] = v[0];
 }
 
+// ---------------------------------------------------------------- reprojection-error evaluator
+// Camera.compute_projection_errors_alt (src/dataset/camera.py:78-85) for every camera at once: per observation
+// e = loss(dx^2) + loss(dy^2) in pixels^2, loss = identity (LOSS 0, TRIVIAL_LOSS) or log(1 + x) (LOSS 1, CAUCHY_LOSS,
+// src/dataset/loss_functions.py:7-17).  Same traversal as the trial-cost kernel (one CTA per camera over its B runs,
+// camera table in shared memory, point gather inside the block window); e goes to the CALLER's row
+// (order_ps[posA[j]], an 8 B scatter) and the ordered per-camera sum to cam_sum[c].  20 B read + 8 B written per row.
+template <int LOSS>
+__global__ void __launch_bounds__(RJ_THREADS)
+k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
+             const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
+             const int32_t* __restrict__ order_ps, const double* __restrict__ pts, double* __restrict__ err_rows,
+             double* __restrict__ cam_sum) {
+  __shared__ CamRuns runs;
+  __shared__ double T[TAB_STRIDE];
+  __shared__ double sm[32];
+  const int c = blockIdx.x;
+  if (threadIdx.x == RJ_THREADS - 1) build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
+  const int L = runs.load(c, nPB, camtab);  // includes the __syncthreads that publishes T
+  double v[1] = {0.0};
+  int run = 0;
+  for (int l = threadIdx.x; l < L; l += RJ_THREADS) {
+    const size_t j = runs.locate(l, run);
+    const int p = __ldg(pt_B + j);
+    if (p < 0) continue;  // padding row of a run
+    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
+    const double2 o = __ldg(obs_B + j);
+    const Proj pr = project(T, X, Y, Z);
+    const double dx = pr.u - o.x, dy = pr.v - o.y;
+    const double e = LOSS ? log(1.0 + dx * dx) + log(1.0 + dy * dy) : dx * dx + dy * dy;
+    v[0] += e;
+    if (err_rows) err_rows[__ldg(order_ps + __ldg(posA + j))] = e;
+  }
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0 && cam_sum) cam_sum[c] = v[0];
+}
+
 // ---------------------------------------------------------------- K2a: 3x3 point blocks
 // One thread per point walks its (short) A run of 32 B row records.  V_p = sum b b^T (6 unique),
 // g_p = sum b r; also writes the point part of the rows as SoA arrays (what the PCG point kernel streams).

@@ -161,6 +161,25 @@ def rms_reprojection_px(x, C, cam_idx, pt_idx, obs, cx_cy_skew):
     return float(np.sqrt((dxdy ** 2).sum(1).mean()))
 
 
+def reprojection_errors(x, C, cam_idx, pt_idx, obs, cx_cy_skew, loss="trivial"):
+    """Per-observation reprojection error `loss((p2d - reprojection)**2).sum(axis=0)` in pixels^2 and its
+    per-camera sums — `Camera.compute_projection_errors_alt` (src/dataset/camera.py:78-85) as
+    `Dataset.compute_reprojection_errors_alt` (src/dataset/dataset.py:116-123) calls it once per camera, with
+    `LossFunction.TRIVIAL_LOSS` (x) or `CAUCHY_LOSS` (log(1 + x), src/dataset/loss_functions.py:7-17).
+    Rows stay in the caller's order; returns (err (N,), per_camera_sum (C,), per_camera_count (C,))."""
+    _, dxdy, _, _ = ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, 1.0, want_jac=False)
+    sq = dxdy ** 2
+    if loss in ("cauchy", 1):
+        sq = np.log(1 + sq)
+    elif loss not in ("trivial", 0):
+        raise ValueError(f"unknown loss {loss!r}")
+    err = sq.sum(axis=1)
+    sums = np.zeros(C)
+    for c in range(C):  # ordered per-camera sums (row order), like the reference's per-camera arrays
+        sums[c] = err[cam_idx == c].sum()
+    return err, sums, np.bincount(cam_idx, minlength=C)
+
+
 # ----------------------------------------------------------------------------- linear solvers
 def _cg_jaxopt(matvec, b, tol=1e-5, maxiter=None):
     """jax.scipy.sparse.linalg.cg as jaxopt.linear_solve.solve_cg calls it: x0=0, M=I,

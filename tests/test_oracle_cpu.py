@@ -159,3 +159,21 @@ def test_c_oracle_matches_numpy_oracle():
     n = min(4, len(loose["loss"]))
     np.testing.assert_allclose(loose["loss"][:n], ex.trace.loss[:n], rtol=0.2)
     assert loose["cg_iters"].max() > 50
+
+
+@pytest.mark.parametrize("loss", ["trivial", "cauchy"])
+def test_reprojection_errors_vs_reference_golden(loss):
+    """oracle.reprojection_errors against vectors computed by the REFERENCE's own
+    `Camera.compute_projection_errors_alt` (camera.py:78-85; tests/golden/make_reproj_golden.py).  This also pins the
+    oracle's projection chain (Rodrigues vector -> R, K [R|t], divide) to the reference's on 1 500 observations."""
+    import b200ba
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    gold = np.load(os.path.join(GOLD, "reproj_small_seed0.npz"))[loss]
+    err, sums, cnt = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, loss)
+    np.testing.assert_allclose(err, gold, rtol=1e-12)
+    assert cnt.sum() == sc.N and sums.sum() == pytest.approx(gold.sum(), rel=1e-12)
+    # TRIVIAL_LOSS is the BA residual times w^2 (bundle_adjustment.py:74)
+    if loss == "trivial":
+        r, _, _, _ = bo.ba_eval(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width ** 2, want_jac=False)
+        np.testing.assert_allclose(r * sc.avg_cam_width ** 2, gold, rtol=1e-12)
