@@ -177,3 +177,91 @@ def test_reprojection_errors_vs_reference_golden(loss):
     if loss == "trivial":
         r, _, _, _ = bo.ba_eval(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width ** 2, want_jac=False)
         np.testing.assert_allclose(r * sc.avg_cam_width ** 2, gold, rtol=1e-12)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Vectors produced by the reference's OWN source files (executed with NumPy standing in for jax.numpy:
+# tests/golden/make_refsrc_golden.py).  These pin the residual side of the oracle — and of the literal restatement
+# the Jacobian checks differentiate — to the reference itself.  The LM state machine inside jaxopt stays unpinned.
+@pytest.fixture(scope="module")
+def refsrc():
+    return np.load(os.path.join(GOLD, "refsrc_seed0.npz"))
+
+
+def test_ba_prepare_params_and_residuals_vs_reference_source(refsrc):
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    np.testing.assert_allclose(x0, refsrc["ba_x0"], rtol=1e-13, atol=1e-15)   # JaxBundleAdjustment.prepare_params
+    np.testing.assert_array_equal(k3, refsrc["ba_k3"])
+    # the product facade packs the same way (bundle_adjustment.py:93-102)
+    ba = b200ba.B200BundleAdjustment.__new__(b200ba.B200BundleAdjustment)
+    ba.cam_num = sc.C
+    x0p, k3p = b200ba.B200BundleAdjustment.prepare_params(ba, sc.poses0, sc.intrinsics0, sc.points0)
+    np.testing.assert_allclose(x0p, refsrc["ba_x0"], rtol=1e-13, atol=1e-15)
+    np.testing.assert_array_equal(k3p, refsrc["ba_k3"])
+    # BundleAdjustment.get_residuals on the dense-padded contract: valid slots = the oracle's sparse rows, pads = 0
+    r, _, _, _ = bo.ba_eval(refsrc["ba_x0"], sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width ** 2, want_jac=False)
+    order, flat = _dense_slots(sc)
+    gold = refsrc["ba_residual"]
+    assert gold.shape == (sc.C * int(refsrc["ba_nmax"]),)
+    np.testing.assert_allclose(r[order], gold[flat], rtol=1e-12, atol=1e-22)
+    assert np.all(gold[np.setdiff1d(np.arange(gold.size), flat)] == 0)
+    # and the literal torch restatement used for the autodiff Jacobian checks
+    p2d, idx, mask = sc.to_dense_padded()
+    rd = rl.ba_get_residuals(torch.tensor(refsrc["ba_x0"]), torch.tensor(p2d), torch.tensor(idx), torch.tensor(k3),
+                             torch.tensor(mask), sc.C, sc.avg_cam_width ** 2).numpy()
+    np.testing.assert_allclose(rd, gold, rtol=1e-12, atol=1e-22)
+    # call-site solver settings (bundle_adjustment.py:84-89): tol 1e-6, maxiter 100, default (CG) solver
+    assert float(refsrc["ba_lm_tol"]) == 1e-6 and int(refsrc["ba_lm_maxiter"]) == 100 and str(refsrc["ba_lm_solver"]) == "default"
+
+
+@pytest.mark.parametrize("loss", ["cauchy", "l2"])
+def test_pose_residuals_vs_reference_source(refsrc, loss):
+    q0, c3 = refsrc["pose_q0"], refsrc["pose_c3"]
+    code = po.CAUCHY if loss == "cauchy" else po.L2
+    r, _ = po.pose_eval(q0, refsrc["pose_points"], refsrc["pose_obs"], c3, refsrc["pose_mask"], 1000.0 ** 2, code)
+    gold = refsrc[f"pose_residual_{loss}"]
+    np.testing.assert_allclose(r, gold, rtol=1e-12, atol=1e-22)
+    assert np.all(gold[refsrc["pose_mask"] == 0] == 0) and (refsrc["pose_mask"] == 0).any()
+    fn = rl.cauchy_loss if loss == "cauchy" else rl.l2_loss
+    for b in range(len(q0)):
+        rd = rl.pose_get_residuals(torch.tensor(q0[b]), torch.tensor(refsrc["pose_points"][b]), torch.tensor(refsrc["pose_obs"][b]),
+                                   torch.tensor(c3[b]), torch.tensor(refsrc["pose_mask"][b]), 1000.0 ** 2, fn).numpy()
+        np.testing.assert_allclose(rd, gold[b], rtol=1e-12, atol=1e-22)
+    # JaxPoseOptimizer.prepare_params (pose_optimization.py:73-84) and call-site settings (:62-69)
+    pb = b200ba.synth.make_pose_batch(B=6, npts=48, seed=2)
+    np.testing.assert_allclose(np.concatenate([bo.pose_mat_to_vec(pb.poses0), pb.intrinsics0[:, :2]], axis=1), q0, rtol=1e-13, atol=1e-15)
+    opt = b200ba.B200PoseOptimizer.__new__(b200ba.B200PoseOptimizer)
+    qp, cp = b200ba.B200PoseOptimizer.prepare_params(opt, pb.poses0, pb.intrinsics0)
+    np.testing.assert_allclose(qp, q0, rtol=1e-13, atol=1e-15)
+    np.testing.assert_array_equal(cp, c3)
+    assert float(refsrc["pose_lm_tol"]) == 1e-7 and int(refsrc["pose_lm_maxiter"]) == 100 and str(refsrc["pose_lm_solver"]) == "cholesky"
+
+
+def test_rotation_helpers_vs_reference_source(refsrc):
+    np.testing.assert_allclose(bo.rot_mat_from_vec(refsrc["rot_w"]), refsrc["rot_R"], rtol=0, atol=1e-14)
+    np.testing.assert_allclose(bo.pose_mat_to_vec(refsrc["log_in"]), refsrc["log_out"], rtol=0, atol=1e-13)
+    np.testing.assert_allclose(b200ba.pose_mat_to_vec(refsrc["log_in"]), refsrc["log_out"], rtol=0, atol=1e-13)
+
+
+def test_analytic_jacobians_vs_autodiff_of_reference_source():
+    """tests/golden/refsrc_jac_seed1.npz: torch.autograd through the reference's own `get_residuals` source files
+    (tests/golden/make_refsrc_jac_golden.py).  The oracle's analytic rows must equal them."""
+    g = np.load(os.path.join(GOLD, "refsrc_jac_seed1.npz"))
+    sc = b200ba.synth.make_ba_scene("tiny", seed=1)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    np.testing.assert_array_equal(x0, g["ba_x0"])
+    r, _, a, b = bo.ba_eval(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, sc.avg_cam_width ** 2)
+    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, sc.cam_idx.astype(np.int64), sc.pt_idx.astype(np.int64)).toarray()
+    order, flat = _dense_slots(sc)
+    np.testing.assert_allclose(r[order], g["ba_residual"][flat], rtol=1e-12, atol=1e-22)
+    np.testing.assert_allclose(J[order], g["ba_jacobian"][flat], rtol=1e-9, atol=1e-12 * np.abs(J).max())
+    pad = np.setdiff1d(np.arange(g["ba_residual"].size), flat)
+    assert np.all(g["ba_residual"][pad] == 0) and np.all(g["ba_jacobian"][pad] == 0)  # masked slots: exact zero rows
+    pb = b200ba.synth.make_pose_batch(B=3, npts=16, seed=4, ragged=True)
+    q0 = np.concatenate([bo.pose_mat_to_vec(pb.poses0), pb.intrinsics0[:, :2]], axis=1)
+    np.testing.assert_array_equal(q0, g["pose_q0"])
+    for name, code in (("cauchy", po.CAUCHY), ("l2", po.L2)):
+        rp, Jp = po.pose_eval(q0, pb.points, pb.obs, pb.intrinsics0[:, 2:], pb.mask, pb.avg_cam_width ** 2, code)
+        np.testing.assert_allclose(rp, g[f"pose_residual_{name}"], rtol=1e-12, atol=1e-22)
+        np.testing.assert_allclose(Jp, g[f"pose_jacobian_{name}"], rtol=1e-9, atol=1e-12 * np.abs(Jp).max())
