@@ -82,3 +82,35 @@ def test_errors_drop_after_solve_and_null_outputs():
     torch.cuda.synchronize()
     np.testing.assert_array_equal(sums.cpu().numpy(), s1)
     assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 7, None, sums.data_ptr(), s) != 0
+
+
+def test_colmap_model_file_to_solution_file(tmp_path):
+    """File -> arrays -> solve -> evaluate -> export -> file (SURVEY.md §8 f1-f3 chained): the solve from a COLMAP model on
+    disk equals the solve from the in-memory scene it was written from, and the exported model reads back as the solution."""
+    from b200ba import model_io as mio
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    mio.write_colmap_model(mio.model_from_ba_arrays(sc.poses0, sc.intrinsics0, sc.points0, sc.cam_idx, sc.pt_idx, sc.obs), tmp_path / "in")
+    m = mio.read_colmap_model(tmp_path / "in")
+    a = m.to_ba_arrays()
+    # PINHOLE cameras carry no skew: compare with the scene at skew 0
+    intr = sc.intrinsics0.copy()
+    intr[:, 4] = 0.0
+    ba = b200ba.B200BundleAdjustment(sc.C, a["avg_cam_width"])
+    x0, k3 = ba.prepare_params(a["poses0"], a["intrinsics0"], a["points0"])
+    prob = ba.build_problem_sparse(a["cam_idx"], a["pt_idx"], a["obs"], len(a["points0"]))
+    x, st = ba.optimize(x0, prob, cx_cy_skew=k3)
+    xr0, k3r = ba.prepare_params(sc.poses0, intr, sc.points0)
+    ref = bo.lm_solve(xr0, sc.C, sc.P, sc.cam_idx, sc.pt_idx, sc.obs, k3r, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    err, per_cam = ba.compute_reprojection_errors_alt(x, k3, prob)
+    assert np.sqrt(err.mean()) == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3r), rel=1e-4)
+    C = sc.C
+    cam6, f = x[:6 * C].reshape(C, 6), x[6 * C:8 * C].reshape(C, 2)
+    poses = np.concatenate([bo.rot_mat_from_vec(cam6[:, :3]), cam6[:, 3:, None]], axis=2)
+    out = m.with_solution(poses, np.concatenate([f, k3], axis=1), x[8 * C:].reshape(-1, 3), a["point_ids"])
+    mio.write_colmap_model(out, tmp_path / "out")
+    b = mio.read_colmap_model(tmp_path / "out").to_ba_arrays()
+    np.testing.assert_allclose(b["poses0"], poses, atol=1e-12)
+    np.testing.assert_array_equal(b["points0"], x[8 * C:].reshape(-1, 3))
+    np.testing.assert_allclose(b["intrinsics0"][:, :2], f)
