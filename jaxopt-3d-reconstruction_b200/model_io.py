@@ -50,6 +50,9 @@ class CameraRec:
         """[fx, fy, cx, cy, skew] as `get_intrinsics` builds K (loader.py:33-43): SIMPLE_* models share f, every
         other model is read as (fx, fy, cx, cy[, skew]) and distortion terms are ignored by the BA path."""
         p = self.params
+        # (the reference itself only handles SIMPLE_RADIAL and 4/5-parameter models: SIMPLE_PINHOLE makes its
+        # get_intrinsics raise and RADIAL's (f, cx, cy, k1, k2) would be read as (fx, fy, cx, cy, s); here every
+        # single-focal model is expanded to (f, f, cx, cy))
         if self.model in ("SIMPLE_PINHOLE", "SIMPLE_RADIAL", "SIMPLE_RADIAL_FISHEYE", "RADIAL", "RADIAL_FISHEYE"):
             return np.array([p[0], p[0], p[1], p[2], 0.0])
         return np.array([p[0], p[1], p[2], p[3], 0.0])
@@ -127,6 +130,31 @@ class SparseModel:
                     point_ids=point_ids, image_ids=np.array([im.image_id for im in imgs], np.int64),
                     avg_cam_width=float(widths.mean()))
 
+    def reduced(self, camera_limit: Optional[int], points_limit: Optional[int]) -> "SparseModel":
+        """`Dataset.make_reduced_dataset(camera_limit, points_limit)` (src/dataset/dataset.py:172-201), the step
+        `_prepare_dataset` starts with: the first `camera_limit` images; per image only its first `points_limit`
+        2D points that have a 3D point count; 3D points seen fewer than twice among those are dropped; every other
+        2D point loses its 3D link.  None = no limit (points seen once are still dropped, as in the reference)."""
+        imgs = list(self.images.values())[:camera_limit]
+        firsts = []
+        for im in imgs:
+            firsts.append(np.flatnonzero(im.point3D_ids > 0)[:points_limit])
+        seen = np.concatenate([im.point3D_ids[f] for im, f in zip(imgs, firsts)]) if imgs else np.zeros(0, np.int64)
+        ids, cnt = np.unique(seen, return_counts=True)
+        ids = ids[cnt >= 2]
+        ids = ids[np.isin(ids, self.point_ids)]
+        new_imgs = {}
+        for im, f in zip(imgs, firsts):
+            keep = f[np.isin(im.point3D_ids[f], ids)]
+            p3 = np.full(len(im.point3D_ids), -1, np.int64)
+            p3[keep] = im.point3D_ids[keep]
+            new_imgs[im.image_id] = ImageRec(im.image_id, im.qvec, im.tvec, im.camera_id, im.name, im.xys, p3)
+        sel = np.flatnonzero(np.isin(self.point_ids, ids))
+        cams = {im.camera_id: self.cameras[im.camera_id] for im in imgs if im.camera_id in self.cameras}
+        m = SparseModel(cams, new_imgs, self.point_ids[sel], self.xyz[sel], self.rgb[sel], self.error[sel])
+        m.rebuild_tracks()
+        return m
+
     def with_solution(self, poses, intrinsics, points, point_ids) -> "SparseModel":
         """A copy carrying an optimised solution (the egress half of `_parse_output_params_bundle`,
         helpers.py:67-115 + `export_in_colmap_format`, loader.py:153-212): poses (C,3,4) W2C in image order,
@@ -166,6 +194,27 @@ class SparseModel:
         self.track_ptr = np.concatenate([[0], np.cumsum(np.bincount(row, minlength=len(self.point_ids)))]).astype(np.int64)
         self.track_image_ids = np.concatenate(img_l)[ok][order] if len(ids) else np.zeros(0, np.int32)
         self.track_point2D_idxs = np.concatenate(p2_l)[ok][order] if len(ids) else np.zeros(0, np.int32)
+
+
+def to_dense_padded(cam_idx, pt_idx, obs, C: int):
+    """Sparse rows -> the reference's dense contract (benchmark_bundle_adjustment.py:72-87): `(C, Nmax, 2)` 2D points,
+    `(C, Nmax)` point indices, `(C, Nmax)` mask; rows keep their order inside a camera, the padding repeats the
+    camera's FIRST observation with mask 0.  For comparisons with the reference only — the solver takes the rows."""
+    cam_idx, pt_idx, obs = np.asarray(cam_idx), np.asarray(pt_idx), np.asarray(obs, np.float64).reshape(-1, 2)
+    order = np.argsort(cam_idx, kind="stable")
+    cam_s = cam_idx[order]
+    counts = np.bincount(cam_s, minlength=C)
+    if counts.min() == 0:
+        raise ModelFormatError("a camera without observations has no first observation to pad with")
+    nmax = int(counts.max())
+    start = np.concatenate([[0], np.cumsum(counts)[:-1]])
+    slot = np.arange(len(order)) - start[cam_s]
+    first = order[start]
+    p2d = np.repeat(obs[first][:, None, :], nmax, axis=1)
+    idx = np.repeat(pt_idx[first].astype(np.int64)[:, None], nmax, axis=1)
+    mask = np.zeros((C, nmax))
+    p2d[cam_s, slot], idx[cam_s, slot], mask[cam_s, slot] = obs[order], pt_idx[order], 1.0
+    return p2d, idx, mask
 
 
 # ---------------------------------------------------------------------- rotations

@@ -220,3 +220,27 @@ def test_bal_roundtrip_and_camera_model(tmp_path):
     with pytest.raises(mio.ModelFormatError):
         path.write_text("2 2 1\n0 0 1.0 2.0\n")
         mio.read_bal(path)
+
+
+@pytest.mark.parametrize("tag,limits", [("full", (None, None)), ("reduced", (4, 12))])
+def test_adapter_arrays_equal_the_reference_adapter(tag, limits):
+    """tests/golden/adapter_colmap_small.npz holds what the reference's OWN `_prepare_dataset`
+    (benchmark_bundle_adjustment.py:45-106, incl. `Dataset.make_reduced_dataset`) returned for a reference Dataset built
+    from the same fixture files (tests/golden/make_adapter_golden.py)."""
+    g = np.load(os.path.join(os.path.dirname(GOLD), "adapter_colmap_small.npz"))
+    a = mio.read_colmap_model(GOLD).reduced(*limits).to_ba_arrays()
+    C = len(a["poses0"])
+    np.testing.assert_array_equal(a["point_ids"], g[f"{tag}_point_ids"])
+    np.testing.assert_array_equal(a["points0"], g[f"{tag}_p3d"])
+    np.testing.assert_allclose(a["poses0"], g[f"{tag}_poses"], atol=1e-14)
+    K = g[f"{tag}_K"]
+    np.testing.assert_array_equal(a["intrinsics0"], np.stack([K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2], K[:, 0, 1]], axis=1))
+    assert a["avg_cam_width"] == float(g[f"{tag}_avg_cam_width"])
+    p2d, idx, mask = mio.to_dense_padded(a["cam_idx"], a["pt_idx"], a["obs"], C)
+    np.testing.assert_array_equal(p2d, g[f"{tag}_p2d"])
+    np.testing.assert_array_equal(idx, g[f"{tag}_idx"])
+    np.testing.assert_array_equal(mask, g[f"{tag}_mask"])
+    # and the synthetic scenes' own dense adapter is the same rule
+    sc = b200ba.synth.make_ba_scene("tiny", seed=3)
+    for x, y in zip(sc.to_dense_padded(), mio.to_dense_padded(sc.cam_idx, sc.pt_idx, sc.obs, sc.C)):
+        np.testing.assert_array_equal(x, y)
