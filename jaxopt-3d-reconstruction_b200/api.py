@@ -46,6 +46,34 @@ def pose_mat_to_vec(pose):
     return np.concatenate([n, pose[..., :3, 3]], axis=-1)
 
 
+def rot_vec_to_mat(w):
+    """Rodrigues vector (...,3) -> R (...,3,3); host NumPy.  The reference's output side builds the same rotation with
+    `Rotation.from_rotvec` (helpers.py:29,93); unlike `rot_mat_from_vec` (utils.py:21-28) it is finite at w = 0."""
+    w = np.asarray(w, dtype=np.float64)
+    th = np.linalg.norm(w, axis=-1)[..., None, None]
+    safe = np.where(th > 0, th, 1.0)
+    k = w[..., None, :] / safe
+    K = np.zeros(w.shape[:-1] + (3, 3))
+    K[..., 0, 1], K[..., 0, 2], K[..., 1, 2] = -w[..., 2], w[..., 1], -w[..., 0]
+    K = (K - np.swapaxes(K, -1, -2)) / safe
+    eye = np.broadcast_to(np.eye(3), K.shape)
+    return np.cos(th) * eye + (1 - np.cos(th)) * (np.swapaxes(k, -1, -2) * k) + np.sin(th) * K
+
+
+def unpack_params(params, cx_cy_skew, cam_num):
+    """The inverse of `prepare_params`, i.e. the array part of `_parse_output_params_bundle`
+    (src/benchmark/jaxopt_benchmark/helpers.py:59-115): packed `[C*6 | C*2 | P*3]` + cx_cy_skew (C,3) ->
+    poses (C,3,4) W2C `[R|t]`, intrinsics (C,5) = [fx, fy, cx, cy, skew], points (P,3).  Raises on NaN camera
+    parameters like the reference's parser (helpers.py:82-85) — the solver itself never raises."""
+    x = np.asarray(params, dtype=np.float64)
+    Cn = int(cam_num)
+    cam6, f = x[:6 * Cn].reshape(Cn, 6), x[6 * Cn:8 * Cn].reshape(Cn, 2)
+    if np.isnan(cam6).any() or np.isnan(f).any():
+        raise ValueError("nan detected in optimised camera parameters")
+    poses = np.concatenate([rot_vec_to_mat(cam6[:, :3]), cam6[:, 3:, None]], axis=2)
+    return poses, np.concatenate([f, np.asarray(cx_cy_skew, dtype=np.float64).reshape(Cn, 3)], axis=1), x[8 * Cn:].reshape(-1, 3)
+
+
 def _require_cuda():
     if not torch.cuda.is_available():
         raise _lib.B200BAError("b200ba needs a CUDA device (sm_100a); there is no CPU fallback")

@@ -125,3 +125,23 @@ def test_point_sharding_world2_gloo():
     [p.join(120) for p in ps]
     out = sorted(q.get(timeout=10) for _ in range(2))
     assert out == [(0, True, True), (1, True, True)]
+
+
+def test_unpack_params_inverts_prepare_params_and_matches_scipy():
+    """`unpack_params` = array part of `_parse_output_params_bundle` (helpers.py:59-115, Rotation.from_rotvec)."""
+    import b200ba
+    from scipy.spatial.transform import Rotation
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    ba = b200ba.B200BundleAdjustment.__new__(b200ba.B200BundleAdjustment)
+    ba.cam_num = sc.C
+    x0, k3 = b200ba.B200BundleAdjustment.prepare_params(ba, sc.poses0, sc.intrinsics0, sc.points0)
+    poses, intr, pts = b200ba.unpack_params(x0, k3, sc.C)
+    np.testing.assert_allclose(poses, sc.poses0, atol=1e-13)
+    np.testing.assert_array_equal(intr, sc.intrinsics0)
+    np.testing.assert_array_equal(pts, sc.points0)
+    w = np.random.default_rng(0).normal(size=(50, 3)) * np.array([1e-9, 1e-3, 1.0, 3.0, 0.0])[np.arange(50) % 5][:, None]
+    np.testing.assert_allclose(b200ba.rot_vec_to_mat(w), Rotation.from_rotvec(w).as_matrix(), atol=1e-14)
+    bad = x0.copy()
+    bad[3] = np.nan
+    with pytest.raises(ValueError):
+        b200ba.unpack_params(bad, k3, sc.C)

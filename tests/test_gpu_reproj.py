@@ -106,9 +106,9 @@ def test_colmap_model_file_to_solution_file(tmp_path):
     err, per_cam = ba.compute_reprojection_errors_alt(x, k3, prob)
     assert np.sqrt(err.mean()) == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3r), rel=1e-4)
     C = sc.C
-    cam6, f = x[:6 * C].reshape(C, 6), x[6 * C:8 * C].reshape(C, 2)
-    poses = np.concatenate([bo.rot_mat_from_vec(cam6[:, :3]), cam6[:, 3:, None]], axis=2)
-    out = m.with_solution(poses, np.concatenate([f, k3], axis=1), x[8 * C:].reshape(-1, 3), a["point_ids"])
+    poses, intr_out, pts_out = b200ba.unpack_params(x, k3, C)
+    f = intr_out[:, :2]
+    out = m.with_solution(poses, intr_out, pts_out, a["point_ids"])
     mio.write_colmap_model(out, tmp_path / "out")
     b = mio.read_colmap_model(tmp_path / "out").to_ba_arrays()
     np.testing.assert_allclose(b["poses0"], poses, atol=1e-12)
