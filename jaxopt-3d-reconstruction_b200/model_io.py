@@ -130,6 +130,23 @@ class SparseModel:
                     point_ids=point_ids, image_ids=np.array([im.image_id for im in imgs], np.int64),
                     avg_cam_width=float(widths.mean()))
 
+    def to_pose_batch(self) -> dict:
+        """The batched single-pose inputs as `JaxoptSinglePoseBenchmarkBatched` builds them
+        (benchmark_pose_optimization.py:55-130): one lane per image with its 2D-3D correspondences in 2D-point order,
+        zero-padded to the longest lane, mask 1 on real rows.  Returns poses0 (B,3,4), intrinsics0 (B,5),
+        points (B,Nmax,3), observations (B,Nmax,2), mask (B,Nmax), avg_cam_width."""
+        a = self.to_ba_arrays()
+        B = len(a["poses0"])
+        counts = np.bincount(a["cam_idx"], minlength=B)
+        nmax = int(counts.max()) if B else 0
+        slot = np.arange(len(a["cam_idx"])) - np.repeat(np.cumsum(counts) - counts, counts)  # rows are camera-major
+        pts, obs, mask = np.zeros((B, nmax, 3)), np.zeros((B, nmax, 2)), np.zeros((B, nmax))
+        pts[a["cam_idx"], slot] = a["points0"][a["pt_idx"]]
+        obs[a["cam_idx"], slot] = a["obs"]
+        mask[a["cam_idx"], slot] = 1.0
+        return dict(poses0=a["poses0"], intrinsics0=a["intrinsics0"], points=pts, observations=obs, mask=mask,
+                    avg_cam_width=a["avg_cam_width"])
+
     def reduced(self, camera_limit: Optional[int], points_limit: Optional[int]) -> "SparseModel":
         """`Dataset.make_reduced_dataset(camera_limit, points_limit)` (src/dataset/dataset.py:172-201), the step
         `_prepare_dataset` starts with: the first `camera_limit` images; per image only its first `points_limit`

@@ -3,7 +3,8 @@ built from tests/golden/colmap_small/ (through the reference's readers `read_cam
 `read_points3d_bin` and its `_parse_points` / `get_intrinsics`; image files are not needed because widths come from
 cameras.bin), then `JaxoptBundleAdjustmentBenchmark._prepare_dataset` (benchmark_bundle_adjustment.py:45-106, which
 calls `Dataset.make_reduced_dataset`, dataset.py:172-201) runs for a full and a reduced (camera_limit, points_limit)
-configuration.  jax is replaced by tests/golden/jax_numpy_shim.py (only imports are touched on this code path).
+configuration; and `JaxoptSinglePoseBenchmarkBatched.setup/_prepare_points/_get_mask`
+(benchmark_pose_optimization.py:32-130) for the single-pose batch.  jax is replaced by tests/golden/jax_numpy_shim.py (only imports are touched on this code path).
 Run from the repo root:  python tests/golden/make_adapter_golden.py  -> tests/golden/adapter_colmap_small.npz"""
 import os
 import sys
@@ -27,6 +28,7 @@ for _m, _names in {"matplotlib": ("pyplot",), "matplotlib.pyplot": (), "triangul
         setattr(_mod, _n, None)
 sys.path.insert(1, "/root/reference")
 from src.benchmark.jaxopt_benchmark.benchmark_bundle_adjustment import JaxoptBundleAdjustmentBenchmark  # noqa: E402
+from src.benchmark.jaxopt_benchmark.benchmark_pose_optimization import JaxoptSinglePoseBenchmarkBatched  # noqa: E402
 from src.dataset.camera import Camera  # noqa: E402
 from src.dataset.camera_pose.camera_pose import CameraPose  # noqa: E402
 from src.dataset.camera_pose.enums_and_types import CoordinateSystem, TransformationDirection  # noqa: E402
@@ -65,4 +67,12 @@ for tag, (cl, pl) in {"full": (None, None), "reduced": (4, 12)}.items():
     out.update({f"{tag}_p2d": p2d, f"{tag}_p3d": p3d, f"{tag}_idx": idx, f"{tag}_mask": mask, f"{tag}_poses": poses, f"{tag}_K": K,
                 f"{tag}_point_ids": np.array([idx2id[i] for i in range(len(p3d))]), f"{tag}_avg_cam_width": w})
     print(tag, p2d.shape, p3d.shape, int(mask.sum()), w)
+# ---- single-pose adapter (benchmark_pose_optimization.py:32-130): per-image correspondences, zero-padded to the longest
+pb = JaxoptSinglePoseBenchmarkBatched(ds)
+pb.setup()
+B = len(pb)
+pts, obs = pb._prepare_points(0, batch_size=B)
+out.update(pose_poses=pb.cam_poses, pose_K=pb.intrinsics, pose_points=np.asarray(pts), pose_obs=np.asarray(obs),
+           pose_mask=np.asarray(pb._get_mask(0, batch_size=B)), pose_avg_cam_width=pb.avg_cam_width)
+print("pose", np.asarray(pts).shape, pb.avg_cam_width)
 np.savez_compressed(os.path.join(HERE, "adapter_colmap_small.npz"), **out)

@@ -244,3 +244,17 @@ def test_adapter_arrays_equal_the_reference_adapter(tag, limits):
     sc = b200ba.synth.make_ba_scene("tiny", seed=3)
     for x, y in zip(sc.to_dense_padded(), mio.to_dense_padded(sc.cam_idx, sc.pt_idx, sc.obs, sc.C)):
         np.testing.assert_array_equal(x, y)
+
+
+def test_pose_batch_equals_the_reference_pose_adapter():
+    """`JaxoptSinglePoseBenchmarkBatched.setup/_prepare_points/_get_mask` (benchmark_pose_optimization.py:32-130), executed
+    on a reference Dataset built from the same fixture files, against `SparseModel.to_pose_batch`."""
+    g = np.load(os.path.join(os.path.dirname(GOLD), "adapter_colmap_small.npz"))
+    b = mio.read_colmap_model(GOLD).to_pose_batch()
+    np.testing.assert_allclose(b["poses0"], g["pose_poses"], atol=1e-14)
+    K = g["pose_K"]
+    np.testing.assert_array_equal(b["intrinsics0"], np.stack([K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2], K[:, 0, 1]], axis=1))
+    np.testing.assert_array_equal(b["points"], g["pose_points"])
+    np.testing.assert_array_equal(b["observations"], g["pose_obs"])
+    np.testing.assert_array_equal(b["mask"], g["pose_mask"])
+    assert b["avg_cam_width"] == float(g["pose_avg_cam_width"]) and (b["mask"] == 0).any()
