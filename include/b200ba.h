@@ -107,11 +107,14 @@ int b200ba_cost(b200ba_plan* plan, const double* cam8, const double* cam_const3,
  * (Dataset.compute_reprojection_errors_alt, src/dataset/dataset.py:116-123, which calls
  * Camera.compute_projection_errors_alt, src/dataset/camera.py:78-85, once per camera in a Python loop).
  * Per observation e = loss(dx^2) + loss(dy^2) in pixels^2; loss 0 = TRIVIAL_LOSS (x), 1 = CAUCHY_LOSS (log(1 + x))
- * (src/dataset/loss_functions.py:7-17).  err_rows: N values in the caller's ORIGINAL row order (or NULL);
+ * (src/dataset/loss_functions.py:7-17).  loss 2 / 3: the cost the reference's COLMAP comparator minimises, e = rho(dx^2 + dy^2)
+ * of the 2-vector residual (colmap/src/base/cost_functions.h:44-86) with ceres::CauchyLoss(loss_scale) = b log(1 + s/b) or
+ * ceres::SoftLOneLoss(loss_scale) = 2b (sqrt(1 + s/b) - 1), b = loss_scale^2 (colmap/src/optim/bundle_adjustment.cc:53-68;
+ * Ceres reports half the sum); loss_scale is ignored for loss 0 / 1.  err_rows: N values in the caller's ORIGINAL row order (or NULL);
  * cam_sum: C ordered per-camera sums over this rank's rows (or NULL).  Asynchronous on `stream`. */
 int b200ba_reprojection_errors(b200ba_plan* plan, const double* cam8, const double* cam_const3,
-                               const double* pts, int loss, double* err_rows /*N*/, double* cam_sum /*C*/,
-                               void* stream);
+                               const double* pts, int loss, double loss_scale, double* err_rows /*N*/,
+                               double* cam_sum /*C*/, void* stream);
 
 /* ---- K4: batched single-pose LM (JaxPoseOptimizer.optimize, pose_optimization.py:86-89 =
  * jit(vmap(LevenbergMarquardt(tol=1e-7, maxiter=100, solver="cholesky").run)) over

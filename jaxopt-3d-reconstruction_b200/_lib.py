@@ -75,7 +75,7 @@ def load():
     lib.b200ba_schur_matvec.argtypes = [vp, vp, vp, vp]
     lib.b200ba_schur_solve.argtypes = [vp, dbl, i32, vp, vp, C.POINTER(i32), vp]
     lib.b200ba_cost.argtypes = [vp, vp, vp, vp, dbl, C.POINTER(dbl), vp]
-    lib.b200ba_reprojection_errors.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp]
+    lib.b200ba_reprojection_errors.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp, vp]
     lib.b200ba_pose_lm_batched.argtypes = [i32, i32, vp, vp, vp, vp, vp, dbl, i32, i32, dbl, dbl,
                                            vp, vp, vp, vp, vp, vp]
     lib.b200ba_profile_enable.argtypes = [vp, i32]

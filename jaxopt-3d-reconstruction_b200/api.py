@@ -29,6 +29,8 @@ class LossFunction:
     L2 = L2
     CAUCHY = CAUCHY
     TRIVIAL = L2  # dataset-side name of the same choice (src/dataset/loss_functions.py:15-17)
+    CERES_CAUCHY = 2   # evaluator only: rho(|r|^2) of COLMAP's 2-vector residual (bundle_adjustment.cc:53-68)
+    CERES_SOFT_L1 = 3
 
 
 def pose_mat_to_vec(pose):
@@ -297,16 +299,19 @@ class B200BundleAdjustment:
                                       1.0 / self.avg_cam_width_sqr, C.byref(opts), C.byref(res), _stream()), "lm_solve")
         return res, (loss_t, grad_t, mu_t, pcg_t, acc_t)
 
-    def compute_reprojection_errors_alt(self, opt_params, cx_cy_skew, prob: BAProblem, loss_function=LossFunction.TRIVIAL):
+    def compute_reprojection_errors_alt(self, opt_params, cx_cy_skew, prob: BAProblem, loss_function=LossFunction.TRIVIAL,
+                                        loss_scale=1.0):
         """`Dataset.compute_reprojection_errors_alt(loss_function)` (src/dataset/dataset.py:116-123) on packed solver
         parameters: returns (per-row errors in the caller's row order, per-camera sums), both NumPy, pixels^2.
-        One kernel launch for all cameras (`b200ba_reprojection_errors`); multi-rank: this rank's rows only."""
+        One kernel launch for all cameras (`b200ba_reprojection_errors`); multi-rank: this rank's rows only.
+        `LossFunction.CERES_CAUCHY / CERES_SOFT_L1` (+ loss_scale): the per-observation rho(|r|^2) of the COLMAP comparator's
+        cost (half the sum is what Ceres reports)."""
         Cn, dev = self.cam_num, self.device
         xd = _dev(opt_params, torch.float64, dev)
         cam8 = torch.cat([xd[:6 * Cn].view(Cn, 6), xd[6 * Cn:8 * Cn].view(Cn, 2)], dim=1).contiguous()
         pts = xd[8 * Cn:].view(-1, 3)[prob.pt_lo:prob.pt_hi].contiguous()
         k3 = _dev(cx_cy_skew, torch.float64, dev)
-        err, sums = BAKernels(prob, self.avg_cam_width_sqr ** 0.5).reprojection_errors(cam8, k3, pts, loss_function)
+        err, sums = BAKernels(prob, self.avg_cam_width_sqr ** 0.5).reprojection_errors(cam8, k3, pts, loss_function, loss_scale)
         return err.cpu().numpy(), sums.cpu().numpy()
 
     def _solve(self, opt_params, cx_cy_skew, prob: BAProblem):
@@ -452,14 +457,14 @@ class BAKernels:
             check(self.lib.b200ba_schur_solve(self.prob.plan, float(rtol), int(maxiter), _ptr(vc), _ptr(vp), C.byref(it), _stream()), "schur_solve")
         return vc, vp, it.value
 
-    def reprojection_errors(self, cam8, k3, pts, loss=LossFunction.TRIVIAL):
+    def reprojection_errors(self, cam8, k3, pts, loss=LossFunction.TRIVIAL, loss_scale=1.0):
         """Per-row errors (caller's row order, pixels^2) and ordered per-camera sums — the reference's
         `Dataset.compute_reprojection_errors_alt(loss_function)` (dataset.py:116-123) for all cameras in one launch."""
         err = torch.empty(self.prob.N, dtype=torch.float64, device=self.dev)
         sums = torch.zeros(self.prob.C, dtype=torch.float64, device=self.dev)
         with torch.cuda.device(self.dev):
             check(self.lib.b200ba_reprojection_errors(self.prob.plan, _ptr(cam8), _ptr(k3), _ptr(pts), int(loss),
-                                                      _ptr(err), _ptr(sums), _stream()), "reprojection_errors")
+                                                      float(loss_scale), _ptr(err), _ptr(sums), _stream()), "reprojection_errors")
         return err, sums
 
     def cost(self, cam8, k3, pts):

@@ -1034,17 +1034,23 @@ extern "C" int b200ba_cost(b200ba_plan* p, const double* cam8, const double* k3,
 }
 
 extern "C" int b200ba_reprojection_errors(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
-                                          int loss, double* err_rows, double* cam_sum, void* stream_) {
+                                          int loss, double loss_scale, double* err_rows, double* cam_sum, void* stream_) {
   if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "reprojection_errors: null");
-  if (loss != 0 && loss != 1) FAIL(B200BA_EINVAL, "reprojection_errors: loss must be 0 (trivial) or 1 (Cauchy)");
+  if (loss < 0 || loss > 3) FAIL(B200BA_EINVAL, "reprojection_errors: loss must be 0 (trivial), 1 (Cauchy), 2 (Ceres Cauchy) or 3 (Ceres soft L1)");
+  if (loss >= 2 && !(loss_scale > 0.0)) FAIL(B200BA_EINVAL, "reprojection_errors: loss_scale must be > 0");
   cudaStream_t s = (cudaStream_t)stream_;
   if (!p->C) return B200BA_OK;
-  if (loss)
-    PLAUNCH(p, PC_OTHER, (k_reproj_err<1>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-            p->order_ps, pts, err_rows, cam_sum);
-  else
-    PLAUNCH(p, PC_OTHER, (k_reproj_err<0>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-            p->order_ps, pts, err_rows, cam_sum);
+  const double b = loss_scale * loss_scale;
+#define REPROJ_LAUNCH(L)                                                                                                  \
+  PLAUNCH(p, PC_OTHER, (k_reproj_err<L>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, \
+          p->order_ps, pts, b, err_rows, cam_sum)
+  switch (loss) {
+    case 0: REPROJ_LAUNCH(0); break;
+    case 1: REPROJ_LAUNCH(1); break;
+    case 2: REPROJ_LAUNCH(2); break;
+    default: REPROJ_LAUNCH(3); break;
+  }
+#undef REPROJ_LAUNCH
   CK(cudaGetLastError());
   return B200BA_OK;
 }

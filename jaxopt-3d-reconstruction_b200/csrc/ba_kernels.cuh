@@ -173,14 +173,17 @@ k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__
 // ---------------------------------------------------------------- reprojection-error evaluator
 // Camera.compute_projection_errors_alt (src/dataset/camera.py:78-85) for every camera at once: per observation
 // e = loss(dx^2) + loss(dy^2) in pixels^2, loss = identity (LOSS 0, TRIVIAL_LOSS) or log(1 + x) (LOSS 1, CAUCHY_LOSS,
-// src/dataset/loss_functions.py:7-17).  Same traversal as the trial-cost kernel (one CTA per camera over its B runs,
+// src/dataset/loss_functions.py:7-17).  LOSS 2 / 3 = what the reference's COLMAP comparator minimises (cost
+// side only): rho(|r|^2) of the 2-vector residual r = projection - observation (colmap/src/base/cost_functions.h:44-86) with
+// ceres::CauchyLoss(a) = b log(1 + s/b) or ceres::SoftLOneLoss(a) = 2b (sqrt(1 + s/b) - 1), b = a^2
+// (colmap/src/optim/bundle_adjustment.cc:53-68); Ceres' cost is half the sum.  Same traversal as the trial-cost kernel (one CTA per camera over its B runs,
 // camera table in shared memory, point gather inside the block window); e goes to the CALLER's row
 // (order_ps[posA[j]], an 8 B scatter) and the ordered per-camera sum to cam_sum[c].  20 B read + 8 B written per row.
 template <int LOSS>
 __global__ void __launch_bounds__(RJ_THREADS)
 k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
              const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
-             const int32_t* __restrict__ order_ps, const double* __restrict__ pts, double* __restrict__ err_rows,
+             const int32_t* __restrict__ order_ps, const double* __restrict__ pts, double b_scale, double* __restrict__ err_rows,
              double* __restrict__ cam_sum) {
   __shared__ CamRuns runs;
   __shared__ double T[TAB_STRIDE];
@@ -198,7 +201,12 @@ k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restri
     const double2 o = __ldg(obs_B + j);
     const Proj pr = project(T, X, Y, Z);
     const double dx = pr.u - o.x, dy = pr.v - o.y;
-    const double e = LOSS ? log(1.0 + dx * dx) + log(1.0 + dy * dy) : dx * dx + dy * dy;
+    const double s2 = dx * dx + dy * dy;
+    double e;
+    if (LOSS == 0) e = s2;
+    else if (LOSS == 1) e = log(1.0 + dx * dx) + log(1.0 + dy * dy);
+    else if (LOSS == 2) e = b_scale * log(1.0 + s2 / b_scale);
+    else e = 2.0 * b_scale * (sqrt(1.0 + s2 / b_scale) - 1.0);
     v[0] += e;
     if (err_rows) err_rows[__ldg(order_ps + __ldg(posA + j))] = e;
   }

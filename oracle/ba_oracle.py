@@ -161,7 +161,7 @@ def rms_reprojection_px(x, C, cam_idx, pt_idx, obs, cx_cy_skew):
     return float(np.sqrt((dxdy ** 2).sum(1).mean()))
 
 
-def reprojection_errors(x, C, cam_idx, pt_idx, obs, cx_cy_skew, loss="trivial"):
+def reprojection_errors(x, C, cam_idx, pt_idx, obs, cx_cy_skew, loss="trivial", loss_scale=1.0):
     """Per-observation reprojection error `loss((p2d - reprojection)**2).sum(axis=0)` in pixels^2 and its
     per-camera sums — `Camera.compute_projection_errors_alt` (src/dataset/camera.py:78-85) as
     `Dataset.compute_reprojection_errors_alt` (src/dataset/dataset.py:116-123) calls it once per camera, with
@@ -169,11 +169,18 @@ def reprojection_errors(x, C, cam_idx, pt_idx, obs, cx_cy_skew, loss="trivial"):
     Rows stay in the caller's order; returns (err (N,), per_camera_sum (C,), per_camera_count (C,))."""
     _, dxdy, _, _ = ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, 1.0, want_jac=False)
     sq = dxdy ** 2
-    if loss in ("cauchy", 1):
-        sq = np.log(1 + sq)
-    elif loss not in ("trivial", 0):
-        raise ValueError(f"unknown loss {loss!r}")
-    err = sq.sum(axis=1)
+    if loss in ("ceres_cauchy", 2, "ceres_soft_l1", 3):
+        # the COLMAP comparator's cost: rho(s), s = |projection - observation|^2 (colmap/src/base/cost_functions.h:44-86),
+        # ceres::CauchyLoss(a): b log(1 + s/b); ceres::SoftLOneLoss(a): 2b (sqrt(1 + s/b) - 1); b = a^2 (Ceres Solver's
+        # published loss definitions, selected at colmap/src/optim/bundle_adjustment.cc:53-68).  Ceres' cost = sum / 2.
+        s, b = sq.sum(axis=1), float(loss_scale) ** 2
+        err = b * np.log(1 + s / b) if loss in ("ceres_cauchy", 2) else 2 * b * (np.sqrt(1 + s / b) - 1)
+    else:
+        if loss in ("cauchy", 1):
+            sq = np.log(1 + sq)
+        elif loss not in ("trivial", 0):
+            raise ValueError(f"unknown loss {loss!r}")
+        err = sq.sum(axis=1)
     sums = np.zeros(C)
     for c in range(C):  # ordered per-camera sums (row order), like the reference's per-camera arrays
         sums[c] = err[cam_idx == c].sum()

@@ -43,9 +43,10 @@ def test_shapes_and_row_order_independence(shape):
     cam8, k3d, pts = _dev_params(x0, k3, sc.C)
     prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
     K = b200ba.BAKernels(prob, sc.avg_cam_width)
-    for loss, code in (("trivial", 0), ("cauchy", 1)):
-        err, sums = K.reprojection_errors(cam8, k3d, pts, code)
-        eo, so, _ = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, loss)
+    for loss, code, scale in (("trivial", 0, 1.0), ("cauchy", 1, 1.0), ("ceres_cauchy", 2, 1.0), ("ceres_cauchy", 2, 3.5),
+                              ("ceres_soft_l1", 3, 2.0)):
+        err, sums = K.reprojection_errors(cam8, k3d, pts, code, scale)
+        eo, so, _ = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, loss, scale)
         np.testing.assert_allclose(err.cpu().numpy(), eo, rtol=1e-11)
         np.testing.assert_allclose(sums.cpu().numpy(), so, rtol=1e-11)
     # trivial loss is the BA residual times w^2 (bundle_adjustment.py:74 divides the same squared error by w^2)
@@ -78,10 +79,11 @@ def test_errors_drop_after_solve_and_null_outputs():
     lib = prob.lib
     sums = torch.zeros(sc.C, dtype=torch.float64, device="cuda")
     s = torch.cuda.current_stream().cuda_stream
-    assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 0, None, sums.data_ptr(), s) == 0
+    assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 0, 1.0, None, sums.data_ptr(), s) == 0
     torch.cuda.synchronize()
     np.testing.assert_array_equal(sums.cpu().numpy(), s1)
-    assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 7, None, sums.data_ptr(), s) != 0
+    assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 7, 1.0, None, sums.data_ptr(), s) != 0
+    assert lib.b200ba_reprojection_errors(prob.plan, cam8.data_ptr(), k3d.data_ptr(), pts.data_ptr(), 2, 0.0, None, sums.data_ptr(), s) != 0
 
 
 def test_colmap_model_file_to_solution_file(tmp_path):

@@ -265,3 +265,24 @@ def test_analytic_jacobians_vs_autodiff_of_reference_source():
         rp, Jp = po.pose_eval(q0, pb.points, pb.obs, pb.intrinsics0[:, 2:], pb.mask, pb.avg_cam_width ** 2, code)
         np.testing.assert_allclose(rp, g[f"pose_residual_{name}"], rtol=1e-12, atol=1e-22)
         np.testing.assert_allclose(Jp, g[f"pose_jacobian_{name}"], rtol=1e-9, atol=1e-12 * np.abs(Jp).max())
+
+
+def test_ceres_style_losses_of_the_colmap_cost():
+    """Evaluator loss codes 2 / 3 (cost side): rho(|r|^2) with Ceres' published CauchyLoss / SoftLOneLoss
+    (colmap/src/optim/bundle_adjustment.cc:53-68).  Checked through their defining properties."""
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    args = (x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    s, _, _ = bo.reprojection_errors(*args, "trivial")
+    c1, sums, _ = bo.reprojection_errors(*args, "ceres_cauchy", 1.0)
+    np.testing.assert_allclose(c1, np.log1p(s), rtol=1e-13)                       # rho(s) = log(1 + s) at a = 1
+    np.testing.assert_allclose(sums.sum(), c1.sum(), rtol=1e-13)
+    for name in ("ceres_cauchy", "ceres_soft_l1"):
+        big, _, _ = bo.reprojection_errors(*args, name, 1e6)
+        np.testing.assert_allclose(big, s, rtol=1e-6)                             # a -> inf: rho(s) -> s (TrivialLoss)
+        a = 2.5
+        e, _, _ = bo.reprojection_errors(*args, name, a)
+        e1, _, _ = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, name, 1.0)
+        assert np.all(e <= s * (1 + 1e-15)) and np.all(np.diff(e[np.argsort(s)]) >= -1e-9)  # rho(s) <= s, monotone in s
+    l1, _, _ = bo.reprojection_errors(*args, "ceres_soft_l1", 2.0)
+    np.testing.assert_allclose(l1, 8.0 * (np.sqrt(1 + s / 4.0) - 1), rtol=1e-13)   # 2 b (sqrt(1 + s/b) - 1), b = 4
