@@ -90,17 +90,27 @@ def _look_at_cameras(rng, C, radius=10.0):
     return np.concatenate([R, t[..., None]], axis=2)
 
 
-def _noisy_poses(rng, poses, rot_noise, pos_noise):
-    """`apply_move` then `apply_transform_3d` (`camera_pose.py:93-107`, `dataset.py:50-58`)."""
-    C = poses.shape[0]
+def apply_pose_noise(poses, move, rotvec):
+    """W2C poses (C,3,4) after `apply_move(move)` then `apply_transform_3d(R(rotvec))` as `Dataset.with_noise` INTENDS
+    them (`dataset.py:50-58`): the camera centre is displaced by `move`, then `[R|t] <- Rn [R|t]`.
+    Measured against the reference's own `CameraPose` (tests/golden/make_noise_golden.py): `apply_transform_3d`
+    (`camera_pose.py:93-95`) is exactly the second step; `apply_move` (`camera_pose.py:101-107`, "TODO: Check validity")
+    is a NO-OP on W2C poses — it restores the translation it just changed — so on COLMAP-loaded datasets the
+    reference's noise never moves a camera centre.  The synthetic workloads keep the intended 5e-2 displacement (a
+    harder start); `pos_noise=0` reproduces the reference's actual behaviour."""
     R = poses[:, :, :3]
     t = poses[:, :, 3]
-    d = _pos_dir(rng, C, 3) * pos_noise
-    t = t - (R @ d[..., None])[..., 0]  # camera centre moved by d
-    Rn = rodrigues_np(_pos_dir(rng, C, 3) * rot_noise)
+    t = t - (R @ move[..., None])[..., 0]  # camera centre moved by `move`
+    Rn = rodrigues_np(rotvec)
     R = Rn @ R
     t = (Rn @ t[..., None])[..., 0]
     return np.concatenate([R, t[..., None]], axis=2)
+
+
+def _noisy_poses(rng, poses, rot_noise, pos_noise):
+    C = poses.shape[0]
+    d = _pos_dir(rng, C, 3) * pos_noise
+    return apply_pose_noise(poses, d, _pos_dir(rng, C, 3) * rot_noise)
 
 
 def project_np(poses, intr, X):

@@ -145,3 +145,25 @@ def test_unpack_params_inverts_prepare_params_and_matches_scipy():
     bad[3] = np.nan
     with pytest.raises(ValueError):
         b200ba.unpack_params(bad, k3, sc.C)
+
+
+def test_synthetic_noise_model_vs_reference_operations():
+    """tests/golden/noise_ops.npz = the reference's own CameraPose / CameraIntrinsics / Dataset._random_direction operations
+    (tests/golden/make_noise_golden.py) that `Dataset.with_noise` (dataset.py:43-63) is made of."""
+    import b200ba
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "noise_ops.npz"))
+    # the reference's apply_move is a no-op on W2C poses (camera_pose.py:101-107) ...
+    np.testing.assert_allclose(g["after_move"], g["poses"], atol=1e-13)
+    # ... so its pose noise is the rotation step alone = apply_pose_noise with no displacement
+    np.testing.assert_allclose(b200ba.synth.apply_pose_noise(g["poses"], np.zeros((6, 3)), g["rotvec"]), g["after_both"], atol=1e-13)
+    # with a displacement the synthetic scenes move the camera CENTRE by exactly `move` (the operation's stated intent)
+    # (the rotation step Rn [R|t] leaves the centre -R^T t where it is)
+    q = b200ba.synth.apply_pose_noise(g["poses"], g["move"], g["rotvec"])
+    centre = lambda T: -(np.swapaxes(T[:, :, :3], 1, 2) @ T[:, :, 3:])[..., 0]  # noqa: E731
+    np.testing.assert_allclose(centre(q) - centre(g["poses"]), g["move"], atol=1e-13)
+    # intrinsics noise: fx, fy, cx, cy, skew each get their own entry of a U[0,10)^(3x3) matrix (camera.py:30-47)
+    nm = g["noise_matrix"]
+    np.testing.assert_allclose(g["intr1"], [1200 + nm[0, 0], 1200 + nm[1, 1], 500 + nm[0, 2], 500 + nm[1, 2], nm[0, 1]])
+    # random directions are unit vectors in the POSITIVE orthant (rand, not randn: dataset.py:32-41) — like synth._pos_dir
+    for d in (g["dirs3"], g["dirs2"], b200ba.synth._pos_dir(np.random.default_rng(0), 200, 3)):
+        assert np.all(d >= 0) and np.allclose(np.linalg.norm(d, axis=1), 1.0)
