@@ -201,12 +201,7 @@ k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restri
     const double2 o = __ldg(obs_B + j);
     const Proj pr = project(T, X, Y, Z);
     const double dx = pr.u - o.x, dy = pr.v - o.y;
-    const double s2 = dx * dx + dy * dy;
-    double e;
-    if (LOSS == 0) e = s2;
-    else if (LOSS == 1) e = log(1.0 + dx * dx) + log(1.0 + dy * dy);
-    else if (LOSS == 2) e = b_scale * log(1.0 + s2 / b_scale);
-    else e = 2.0 * b_scale * (sqrt(1.0 + s2 / b_scale) - 1.0);
+    const double e = reproj_loss<LOSS>(dx, dy, b_scale);
     v[0] += e;
     if (err_rows) err_rows[__ldg(order_ps + __ldg(posA + j))] = e;
   }

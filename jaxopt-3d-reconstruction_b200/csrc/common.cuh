@@ -1,6 +1,12 @@
 // Shared device helpers for the b200ba kernels (sm_100a).
 #pragma once
+// B200BA_HOST_MATH: tests/host_math/ compiles the per-row arithmetic below (camera table, projection, Jacobian row,
+// evaluator losses, 8x8 Cholesky) with g++ to check the CUDA SOURCE against the oracle on a machine without a GPU.
+// It is test scaffolding only: everything that touches threads, warps, barriers or PTX is compiled out of that build,
+// and nothing in the library or the Python package ever defines the macro.
+#ifndef B200BA_HOST_MATH
 #include <cuda_runtime.h>
+#endif
 #include <stdio.h>
 #include <stdint.h>
 
@@ -17,6 +23,7 @@ struct SolverState {
   int pcg_first, pcg_stop /*0 converged, 1 maxiter, 2 NaN, 3 stagnated*/, since_best, pad_;
 };
 
+#ifndef B200BA_HOST_MATH
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -63,6 +70,8 @@ __device__ __forceinline__ double block_max1(double v, double* sm) {
   }
   return x;
 }
+
+#endif  // !B200BA_HOST_MATH
 
 // Projection chain shared by the BA and pose kernels.
 struct Proj {
@@ -185,6 +194,19 @@ __device__ __forceinline__ void chol8_solve(double* A, double* b) {
   }
 }
 
+// Per-observation value of the reprojection-error evaluator (k_reproj_err): LOSS 0 TRIVIAL_LOSS, 1 CAUCHY_LOSS
+// (src/dataset/loss_functions.py:7-17, applied per coordinate), 2 / 3 ceres::CauchyLoss / SoftLOneLoss of |r|^2 with b = a^2
+// (colmap/src/optim/bundle_adjustment.cc:53-68).
+template <int LOSS>
+__device__ __forceinline__ double reproj_loss(double dx, double dy, double b) {
+  const double s2 = dx * dx + dy * dy;
+  if (LOSS == 0) return s2;
+  if (LOSS == 1) return log(1.0 + dx * dx) + log(1.0 + dy * dy);
+  if (LOSS == 2) return b * log(1.0 + s2 / b);
+  return 2.0 * b * (sqrt(1.0 + s2 / b) - 1.0);
+}
+
+#ifndef B200BA_HOST_MATH
 // ---------------------------------------------------------------- mbarrier + bulk async copy (TMA, 1-D)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -217,3 +239,4 @@ template <int NT>
 __device__ __forceinline__ void named_bar_sync(int id) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(NT) : "memory");
 }
+#endif  // !B200BA_HOST_MATH
