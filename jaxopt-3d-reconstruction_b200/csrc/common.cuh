@@ -1,7 +1,7 @@
 // Shared device helpers for the b200ba kernels (sm_100a).
 #pragma once
 // B200BA_HOST_MATH: tests/host_math/ compiles the per-row arithmetic below (camera table, projection, Jacobian row,
-// evaluator losses, 8x8 Cholesky) with g++ to check the CUDA SOURCE against the oracle on a machine without a GPU.
+// evaluator losses, 8x8 Cholesky) with g++ so the CPU test suite can check the CUDA SOURCE against known answers on a machine without a GPU.
 // It is test scaffolding only: everything that touches threads, warps, barriers or PTX is compiled out of that build,
 // and nothing in the library or the Python package ever defines the macro.
 #ifndef B200BA_HOST_MATH
