@@ -11,6 +11,7 @@ if [ -z "$SKIP_TESTS" ]; then
 fi
 timeout 300 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
 tail -c 600 $out/bench.json
+timeout 200 python tools/reproj_probe.py > $out/reproj.json 2> $out/reproj.err; echo "reproj probe exit $?"; cat $out/reproj.json
 if [ -n "$VARIANTS" ]; then bash tools/mv_variants.sh > $out/variants.txt 2>&1; cat $out/variants.txt; fi
 if [ -z "$SKIP_NCU" ]; then
   CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-pose"
@@ -20,5 +21,7 @@ if [ -z "$SKIP_NCU" ]; then
       -k regex:"k_cs_ring|k_ps|k_cs<" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
       -k regex:"k_resjac|k_cam_blocks|k_point" -s 5 -c 7 -f -o $out/prof_lin $CMD > $out/ncu_full_lin.log 2>&1
+  timeout 300 ncu --set full --clock-control none --import-source on -k regex:"k_reproj_err" -c 2 -f -o $out/prof_reproj \
+      python tools/reproj_probe.py venice1778 1 > $out/ncu_full_reproj.log 2>&1
   echo "ncu exit $?"; ls -la $out
 fi
