@@ -1,11 +1,17 @@
 """ORACLE (test infrastructure, NOT product code) — float64 CPU restatement of the reference's
-bundle-adjustment hot path.  PARITY UNPINNED: the arithmetic of the path lives in the
-un-vendored dependency `jaxopt==0.7` (`/root/reference/requirements.txt:30`, on `jax==0.4.8`,
-`:81-82`), which is absent from this image, and the reference has no test that pins the path
-(SURVEY.md §4).  What IS pinned: the projection against COLMAP's four known-answer vectors
-(`colmap/src/base/cost_functions_test.cc:41-69`), the analytic Jacobian against autodiff of a
-literal restatement of the reference's `get_residuals` (`oracle/ref_literal.py`), and the pose
-log/exp maps against scipy and the reference's `test_pose.txt` fixture.
+bundle-adjustment hot path.
+
+PARITY: residual side PINNED to the reference's own source, LM state machine UNPINNED.
+  * pinned — `rot_mat_from_vec`, `pose_mat_to_vec`, `prepare_params`, `get_residuals` (dense-padded contract) and
+    their Jacobians, against golden vectors produced by EXECUTING the reference's source files with NumPy / float64
+    torch standing in for `jax.numpy` (tests/golden/make_refsrc_golden.py, make_refsrc_jac_golden.py ->
+    refsrc_seed0.npz, refsrc_jac_seed1.npz); `reprojection_errors` against the reference's own
+    `Camera.compute_projection_errors_alt` (make_reproj_golden.py -> reproj_small_seed0.npz); the projection against
+    COLMAP's four known-answer vectors (`colmap/src/base/cost_functions_test.cc:41-69`); the pose log/exp maps against
+    scipy and the reference's `test_pose.txt` fixture.
+  * unpinned — `lm_solve` / `_cg_jaxopt`: the LM state machine and CG live in the un-vendored dependency
+    `jaxopt==0.7` (`/root/reference/requirements.txt:30`, on `jax==0.4.8`, `:81-82`), absent from this image and from
+    /opt/wheelhouse; no reference test pins them.  Restated from SURVEY.md App. A.4.
 
 Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s cpu_baseline / `--impl reference`
 legs may import this module.

@@ -1,7 +1,8 @@
 /* ORACLE (test infrastructure, NOT product code) — plain C (OpenMP) restatement of the reference's
  * bundle-adjustment path in ITS OWN formulation: residual + Jacobian rows, then jaxopt 0.7's
  * LevenbergMarquardt with the default inner solver (unpreconditioned CG on the full (8C+3P) normal
- * equations, rel. tol 1e-5, maxiter 10n, x0 = 0).  PARITY UNPINNED (see ba_oracle.py header); this
+ * equations, rel. tol 1e-5, maxiter 10n, x0 = 0).  PARITY: residual side pinned through ba_oracle.py, LM state
+ * machine UNPINNED (see ba_oracle.py header); this
  * file is checked against ba_oracle.py in tests/test_oracle_cpu.py and exists so that the CPU
  * baseline uses every host core.
  *

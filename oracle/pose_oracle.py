@@ -1,6 +1,8 @@
 """ORACLE (test infrastructure, NOT product code) — float64 CPU restatement of the reference's
-batched single-pose refinement.  PARITY UNPINNED for the same reason as `ba_oracle.py`
-(jaxopt 0.7 absent; no reference test pins the path).
+batched single-pose refinement.  PARITY: `pose_eval` (residuals and Jacobian rows, both losses, masked rows) is PINNED to
+golden vectors produced by executing the reference's own `PoseOptimization.get_residuals` source (tests/golden/
+refsrc_seed0.npz, refsrc_jac_seed1.npz); the LM loop `pose_lm_batched` is UNPINNED for the same reason as
+`ba_oracle.lm_solve` (jaxopt 0.7 absent; no reference test pins the path).
 
 Follows (relative to /root/reference/src/reconstruction/bundle_adjustment/):
   PoseOptimization.get_residuals   pose_optimization.py:33-52  -> pose_eval

@@ -1,7 +1,8 @@
 """ORACLE (test infrastructure, NOT product code) — literal float64 torch restatement of the
 reference's two residual functions in their ORIGINAL dense-padded array contract, used only to
 validate `ba_oracle.py` / `pose_oracle.py` (sparse rows, analytic Jacobians) by autodiff.
-jax is not installed here, so torch.float64 on CPU plays jax.numpy's role.
+jax is not installed here, so torch.float64 on CPU plays jax.numpy's role.  Its residuals are themselves pinned to the
+reference's source executed under a jax.numpy stand-in (tests/golden/refsrc_seed0.npz).
 
   ba_get_residuals    <- BundleAdjustment.get_residuals, bundle_adjustment.py:52-74
                          (reproject_point :17-21, double vmap :24-29)
