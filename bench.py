@@ -113,8 +113,9 @@ def bytes_models(C, P, N, jsz):
         # camera-run order: read obs 16 + point index 4 + A position 4; write Jc 8*jsz + r 8 (B order) and one 32 B
         # record {b, r} scattered to A order; points once (gathered inside the point block), cameras once
         "resjac": N * (16 + 4 + 4 + 8 * jsz + 8 + 32) + 24 * P + 88 * C,
-        # point kernel: Jp 3*jsz + posB 4 + pt 4 + sigma 8 -> omega 8 ; per point Vinv 48 + ptr 4
-        "mv_pt": N * (3 * jsz + 4 + 4 + 8 + 8) + 52 * P,
+        # point kernel: Jp 3*jsz + posB 4 + sigma 8 -> omega 8 ; per point Vinv 48 + ptr 4.  (No per-row point index: the
+        # row -> point map is rebuilt in shared memory, PS_OWN in ba_pcg.cuh; earlier bench lines counted 4 B/row for it.)
+        "mv_pt": N * (3 * jsz + 4 + 8 + 8) + 52 * P,
         # camera kernel: Jc 8*jsz + omega 8 -> sigma 8 ; per camera PCG record 576 r+w, U 512, Minv 512, run table
         "mv_cam": N * (8 * jsz + 8 + 8) + (2 * 576 + 1024 + 160) * C,
         "cost": N * (16 + 4) + 24 * P + 88 * C,
