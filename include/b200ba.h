@@ -46,6 +46,14 @@ int b200ba_plan_set_observations(b200ba_plan* plan, const double* obs_xy, void* 
 int b200ba_nccl_unique_id(char* unique_id_host /*128 B*/);
 int b200ba_plan_set_comm(b200ba_plan* plan, int rank, int nranks, const char* unique_id_host);
 
+/* Residual model of a plan.  0 (default): the reference's ONE scalar residual per observation, (dx^2 + dy^2)/w^2
+ * (bundle_adjustment.py:17-21,74).  1: the 2-vector model of the reference's COLMAP comparator, r = (u - x, v - y)/w with the
+ * principal point fixed (colmap/src/base/cost_functions.h:44-86; refine_principal_point = 0,
+ * src/benchmark/colmap_benchmark/bundle_adjuster.py:25-38) run as the same pipeline over 2N rows: list every observation twice in
+ * plan_create and pass (x, NaN) for its x row and (NaN, y) for its y row to plan_set_observations.  Objective
+ * 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 (TrivialLoss).  EXPERIMENTAL: not yet run on a GPU. */
+int b200ba_plan_set_residual_model(b200ba_plan* plan, int model);
+
 /* ---- K1: residual + analytic Jacobian rows (BundleAdjustment.get_residuals,
  * bundle_adjustment.py:52-74 with reproject_point :17-21, plus the Jacobian jaxopt obtains by
  * jvp/vjp).  Outputs in the caller's ORIGINAL row order.  cam8: C x 8 = [w(3), t(3), fx, fy];

@@ -125,7 +125,7 @@ class LMState:
 class BAProblem:
     """Problem structure resident on the GPU: plan (sorted rows, CSR, workspaces) + observations."""
 
-    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True):
+    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True, residual_model=0):
         lib = _require_cuda()
         self.lib = lib
         self.C, self.P, self.N = int(C_), int(P), int(cam_idx.numel())
@@ -137,6 +137,8 @@ class BAProblem:
             check(lib.b200ba_plan_create(self.C, self.P, self.N, _ptr(cam_idx), _ptr(pt_idx),
                                          int(bool(jac_f32)), _stream(), C.byref(plan)), "plan_create")
             self.plan = plan
+            if residual_model:
+                check(lib.b200ba_plan_set_residual_model(plan, int(residual_model)), "set_residual_model")
             check(lib.b200ba_plan_set_observations(plan, _ptr(obs), _stream()), "set_observations")
             torch.cuda.current_stream().synchronize()
 
@@ -168,7 +170,10 @@ class B200BundleAdjustment:
 
     def __init__(self, cam_num, avg_cam_width, device=None, tol=1e-6, maxiter=100,
                  damping_parameter=1e-6, pcg_rtol=1e-10, pcg_maxiter=1000, jac_f32=True,
-                 verbose=False, process_group=None, distributed=None):
+                 verbose=False, process_group=None, distributed=None, residual_model="scalar"):
+        if residual_model not in ("scalar", "vector2"):
+            raise ValueError("residual_model must be 'scalar' (the reference) or 'vector2' (COLMAP-style, experimental)")
+        self.residual_model = residual_model
         self.cam_num = int(cam_num)
         self.avg_cam_width_sqr = float(avg_cam_width) ** 2
         self.device = torch.device(device if device is not None else "cuda")
@@ -243,7 +248,14 @@ class B200BundleAdjustment:
             lo, hi = int(bounds[self.rank]), int(bounds[self.rank + 1])
             keep = (pt_idx >= lo) & (pt_idx < hi)
             cam_idx, pt_idx, obs = cam_idx[keep].contiguous(), (pt_idx[keep] - lo).contiguous(), obs[keep].contiguous()
-        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32)
+        model = 0
+        if getattr(self, "residual_model", "scalar") == "vector2":
+            # 2-vector model: the same pipeline over 2N rows, (x, NaN) / (NaN, y) mark the component
+            model = 1
+            o2 = torch.full((2 * obs.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
+            o2[0::2, 0], o2[1::2, 1] = obs[:, 0], obs[:, 1]
+            cam_idx, pt_idx, obs = cam_idx.repeat_interleave(2).contiguous(), pt_idx.repeat_interleave(2).contiguous(), o2
+        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32, residual_model=model)
         prob.pt_lo, prob.pt_hi, prob.P_global = lo, hi, P
         if self.world > 1:
             self._init_comm(prob)

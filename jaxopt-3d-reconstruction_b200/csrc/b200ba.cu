@@ -57,6 +57,7 @@ struct b200ba_plan {
   int C = 0, P = 0;
   int64_t N = 0;
   int jac_f32 = 0;
+  int residual_model = 0;  // 0: the reference's scalar squared error per observation; 1: 2-vector model over 2N rows (k_resjac_v2)
   size_t jsz = 8;
   // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
@@ -740,6 +741,10 @@ struct Ops {
                        cudaStream_t s) {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
+    if (p->residual_model)
+      PLAUNCH(p, PC_RESJAC, (k_resjac_v2<JT, true>), C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
+              sqrt(inv_w2), (JT*)p->Jc_B, p->r_B, (RowRec<JT>*)p->rec_A, p->part);
+    else
     PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
             inv_w2, (JT*)p->Jc_B, p->r_B, (RowRec<JT>*)p->rec_A, p->part);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 1, 1, p->lin_scal, 0);
@@ -910,6 +915,10 @@ struct Ops {
 
   static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
                   double* out_dev, cudaStream_t s) {
+    if (p->residual_model)
+      PLAUNCH(p, PC_COST, (k_resjac_v2<JT, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
+              sqrt(inv_w2), nullptr, nullptr, nullptr, p->part);
+    else
     PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
             inv_w2, nullptr, nullptr, nullptr, p->part);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, p->C, 1, 1, out_dev, 0);
@@ -1033,11 +1042,19 @@ extern "C" int b200ba_cost(b200ba_plan* p, const double* cam8, const double* k3,
   return B200BA_OK;
 }
 
+extern "C" int b200ba_plan_set_residual_model(b200ba_plan* p, int model) {
+  if (!p) FAIL(B200BA_EINVAL, "null plan");
+  if (model != 0 && model != 1) FAIL(B200BA_EINVAL, "residual model must be 0 (scalar squared error) or 1 (2-vector rows)");
+  p->residual_model = model;
+  return B200BA_OK;
+}
+
 extern "C" int b200ba_reprojection_errors(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
                                           int loss, double loss_scale, double* err_rows, double* cam_sum, void* stream_) {
   if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "reprojection_errors: null");
   if (loss < 0 || loss > 3) FAIL(B200BA_EINVAL, "reprojection_errors: loss must be 0 (trivial), 1 (Cauchy), 2 (Ceres Cauchy) or 3 (Ceres soft L1)");
   if (loss >= 2 && !(loss_scale > 0.0)) FAIL(B200BA_EINVAL, "reprojection_errors: loss_scale must be > 0");
+  if (p->residual_model) FAIL(B200BA_EINVAL, "reprojection_errors: build the plan from the observations themselves (residual model 0)");
   cudaStream_t s = (cudaStream_t)stream_;
   if (!p->C) return B200BA_OK;
   const double b = loss_scale * loss_scale;

@@ -170,6 +170,49 @@ k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__
   if (threadIdx.x == 0) cost_part[c] = v[0];
 }
 
+// ---------------------------------------------------------------- K0+K1 for the 2-vector residual model
+// COLMAP's BundleAdjustmentCostFunction (colmap/src/base/cost_functions.h:44-86) has TWO residuals per observation,
+// (u - x, v - y), principal point fixed (refine_principal_point = 0, src/benchmark/colmap_benchmark/bundle_adjuster.py:25-38).
+// Here that is the SAME pipeline over 2N rows: the caller lists every observation twice and marks the component by a NaN
+// in the other coordinate — row (x, NaN): r = (u - x)/w, dr/d(u,v) = (1/w, 0); row (NaN, y): r = (v - y)/w, (0, 1/w) —
+// so 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 (TrivialLoss).  Everything after K1 is generic over rows.
+// A separate kernel (not a template parameter of k_resjac) so that the default model's machine code is untouched.
+template <typename JT, bool WITH_JAC>
+__global__ void __launch_bounds__(RJ_THREADS)
+k_resjac_v2(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
+            const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
+            const double* __restrict__ pts, double inv_w, JT* __restrict__ Jc_B, double* __restrict__ r_B,
+            RowRec<JT>* __restrict__ rec_A, double* __restrict__ cost_part) {
+  __shared__ CamRuns runs;
+  __shared__ double T[TAB_STRIDE];
+  __shared__ double sm[32];
+  const int c = blockIdx.x;
+  if (threadIdx.x == RJ_THREADS - 1) build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
+  const int L = runs.load(c, nPB, camtab);  // includes the __syncthreads that publishes T
+  double v[1] = {0.0};
+  int run = 0;
+  for (int l = threadIdx.x; l < L; l += RJ_THREADS) {
+    const size_t j = runs.locate(l, run);
+    const int p = __ldg(pt_B + j);
+    if (p < 0) continue;  // padding row of a run
+    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
+    const double2 o = __ldg(obs_B + j);
+    const Proj pr = project(T, X, Y, Z);
+    double ex, ey;
+    const double r = v2_residual(pr, o.x, o.y, inv_w, ex, ey);
+    v[0] += r * r;
+    if (WITH_JAC) {
+      double a[8], b[3];
+      jac_row(T, pr, X, Y, Z, ex, ey, a, b);
+      store8<JT>(Jc_B + 8 * j, a);
+      r_B[j] = r;
+      st_rec(rec_A + __ldg(posA + j), b, r);
+    }
+  }
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) cost_part[c] = v[0];
+}
+
 // ---------------------------------------------------------------- reprojection-error evaluator
 // Camera.compute_projection_errors_alt (src/dataset/camera.py:78-85) for every camera at once: per observation
 // e = loss(dx^2) + loss(dy^2) in pixels^2, loss = identity (LOSS 0, TRIVIAL_LOSS) or log(1 + x) (LOSS 1, CAUCHY_LOSS,

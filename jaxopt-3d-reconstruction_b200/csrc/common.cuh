@@ -194,6 +194,15 @@ __device__ __forceinline__ void chol8_solve(double* A, double* b) {
   }
 }
 
+// Row of the 2-vector residual model (k_resjac_v2): the observation (x, NaN) marks the x component, (NaN, y) the y component.
+// Returns r = (u - x)/w or (v - y)/w and dr/d(u,v) in (ex, ey).
+__device__ __forceinline__ double v2_residual(const Proj& pr, double ox, double oy, double inv_w, double& ex, double& ey) {
+  const bool xrow = oy != oy;
+  ex = xrow ? inv_w : 0.0;
+  ey = xrow ? 0.0 : inv_w;
+  return (xrow ? pr.u - ox : pr.v - oy) * inv_w;
+}
+
 // Per-observation value of the reprojection-error evaluator (k_reproj_err): LOSS 0 TRIVIAL_LOSS, 1 CAUCHY_LOSS
 // (src/dataset/loss_functions.py:7-17, applied per coordinate), 2 / 3 ceres::CauchyLoss / SoftLOneLoss of |r|^2 with b = a^2
 // (colmap/src/optim/bundle_adjustment.cc:53-68).

@@ -103,7 +103,16 @@ def rot_jac_factor(w, R):
 
 
 # ----------------------------------------------------------------------------- residual + Jacobian
-def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True):
+def expand_vector2(cam_idx, pt_idx, obs):
+    """Rows of the 2-vector residual model: every observation twice, (x, NaN) = its x row,
+    (NaN, y) = its y row — the row contract of `b200ba_plan_set_residual_model(plan, 1)`."""
+    obs = np.asarray(obs, dtype=np.float64).reshape(-1, 2)
+    o2 = np.full((2 * len(obs), 2), np.nan)
+    o2[0::2, 0], o2[1::2, 1] = obs[:, 0], obs[:, 1]
+    return np.repeat(np.asarray(cam_idx), 2), np.repeat(np.asarray(pt_idx), 2), o2
+
+
+def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True, model="scalar"):
     """Residual r_i = ((u-x)^2+(v-y)^2)/w^2 per valid observation (bundle_adjustment.py:17-21,74)
     and the 8 camera + 3 point non-zeros of each Jacobian row (analytic).
 
@@ -122,12 +131,26 @@ def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True):
     iz = 1.0 / q[:, 2]
     u = (fx * q[:, 0] + s * q[:, 1]) * iz + cx
     v = fy * q[:, 1] * iz + cy
-    dx = u - obs[:, 0]
-    dy = v - obs[:, 1]
-    r = (dx * dx + dy * dy) / w2
-    dxdy = np.stack([dx, dy], axis=1)
-    if not want_jac:
-        return r, dxdy, None, None
+    if model == "vector2":
+        # COLMAP's BundleAdjustmentCostFunction (colmap/src/base/cost_functions.h:44-86): residual = projection - observation,
+        # one row per component (rows from expand_vector2), scaled by 1/w so that both models share avg_cam_width
+        xrow = np.isnan(obs[:, 1])
+        iw = 1.0 / np.sqrt(w2)
+        dx = np.where(xrow, u - np.where(xrow, obs[:, 0], 0.0), 0.0)
+        dy = np.where(xrow, 0.0, v - np.where(xrow, 0.0, obs[:, 1]))
+        r = (dx + dy) * iw
+        dxdy = np.stack([dx, dy], axis=1)
+        if not want_jac:
+            return r, dxdy, None, None
+        e_override = np.stack([np.where(xrow, iw, 0.0), np.where(xrow, 0.0, iw)], axis=1)
+    else:
+        dx = u - obs[:, 0]
+        dy = v - obs[:, 1]
+        r = (dx * dx + dy * dy) / w2
+        dxdy = np.stack([dx, dy], axis=1)
+        if not want_jac:
+            return r, dxdy, None, None
+        e_override = None
     N = len(r)
     # d(u,v)/dq
     dpi = np.zeros((N, 2, 3))
@@ -136,7 +159,7 @@ def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True):
     dpi[:, 0, 2] = -(fx * q[:, 0] + s * q[:, 1]) * iz * iz
     dpi[:, 1, 1] = fy * iz
     dpi[:, 1, 2] = -fy * q[:, 1] * iz * iz
-    e = (2.0 / w2) * dxdy                     # dr/d(u,v)
+    e = (2.0 / w2) * dxdy if e_override is None else e_override  # dr/d(u,v)
     eq = np.einsum("ni,nij->nj", e, dpi)      # dr/dq   (N,3)
     M = rot_jac_factor(w, R)
     dq_dw = -Rc @ _skew(X) @ M[cam_idx]       # (N,3,3)
@@ -287,7 +310,7 @@ class LMResult:
 
 
 def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6, maxiter=100,
-             damping_parameter=1e-6, solver="exact", round_jac_f32=False, cg_tol=1e-5) -> LMResult:
+             damping_parameter=1e-6, solver="exact", round_jac_f32=False, cg_tol=1e-5, model="scalar") -> LMResult:
     """jaxopt 0.7 LevenbergMarquardt.run as the reference configures it
     (bundle_adjustment.py:83-91: tol=1e-6, maxiter=100, default solver, 'grad-l2-norm' stop).
 
@@ -295,6 +318,7 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
             'jaxopt_cg' — the reference's actual inner solver: unpreconditioned CG on the full
                           normal equations, rel. tol 1e-5, maxiter 10n (`cg_tol` to tighten it)
     round_jac_f32: emulate fp32 storage of Jacobian rows (design study; gradient stays exact).
+    model: 'scalar' (the reference) or 'vector2' (rows from expand_vector2: the COLMAP comparator's residual).
     Accept/reject uses a select instead of jaxopt's arithmetic blend."""
     cam_idx = np.asarray(cam_idx, dtype=np.int64)
     pt_idx = np.asarray(pt_idx, dtype=np.int64)
@@ -303,7 +327,7 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
     tr = LMTrace()
 
     def evaluate(xx):
-        r, _, a, b = ba_eval(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2)
+        r, _, a, b = ba_eval(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, model=model)
         J = ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx)
         g = J.T @ r
         if round_jac_f32:
@@ -336,7 +360,7 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
             raise ValueError(solver)
         delta = -v
         x_next = x + delta
-        r_next, _, _, _ = ba_eval(x_next, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=False)
+        r_next, _, _, _ = ba_eval(x_next, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=False, model=model)
         tr.n_eval_res += 1
         loss_next = 0.5 * float(r_next @ r_next)
         rho = (loss - loss_next) / (0.5 * float(delta @ (mu * delta - g)))

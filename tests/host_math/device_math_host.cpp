@@ -43,6 +43,13 @@ void hm_pose_row(const double* T, const double* X, const double* obs, double mas
   }
   jac_row(T, pr, X[0], X[1], X[2], ex, ey, a, b);
 }
+// row of the 2-vector model exactly as k_resjac_v2 forms it
+void hm_ba_row_v2(const double* T, const double* X, const double* obs, double inv_w, double* r, double* a, double* b) {
+  const Proj pr = project(T, X[0], X[1], X[2]);
+  double ex, ey;
+  *r = v2_residual(pr, obs[0], obs[1], inv_w, ex, ey);
+  jac_row(T, pr, X[0], X[1], X[2], ex, ey, a, b);
+}
 double hm_reproj_loss(int loss, double dx, double dy, double b) {
   switch (loss) {
     case 0: return reproj_loss<0>(dx, dy, b);

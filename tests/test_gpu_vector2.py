@@ -1,0 +1,49 @@
+"""GPU parity of the 2-vector residual model (`b200ba_plan_set_residual_model(plan, 1)`, kernel
+`k_resjac_v2`) against the oracle's `model="vector2"`.
+
+EXPERIMENTAL AND GATED: this path was written after the round's GPU budget was spent and has never run on a GPU, so the
+tests only run with B200BA_EXPERIMENTAL=1 (first GPU call of the next round); ungated they skip, they do not pass."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200ba
+from oracle import ba_oracle as bo
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("B200BA_EXPERIMENTAL") != "1", reason="2-vector model not yet verified on a GPU (set B200BA_EXPERIMENTAL=1)")]
+
+
+@pytest.mark.parametrize("shape", ["tiny", "small"])
+def test_vector2_rows(shape):
+    sc = b200ba.synth.make_ba_scene(shape, seed=0)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=False, residual_model="vector2")
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    assert prob.N == 2 * sc.N
+    xd = torch.from_numpy(x0).cuda()
+    cam8 = torch.cat([xd[:6 * sc.C].view(sc.C, 6), xd[6 * sc.C:8 * sc.C].view(sc.C, 2)], 1).contiguous()
+    r, Jc, Jp, cost = b200ba.BAKernels(prob, sc.avg_cam_width).residual_jacobian(cam8, torch.from_numpy(k3).cuda(), xd[8 * sc.C:].view(-1, 3).contiguous())
+    c2, p2, o2 = bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs)
+    ro, _, a, b = bo.ba_eval(x0, sc.C, c2, p2, o2, k3, sc.avg_cam_width ** 2, model="vector2")
+    np.testing.assert_allclose(r.cpu().numpy(), ro, rtol=1e-9, atol=1e-15)
+    np.testing.assert_allclose(Jc.cpu().numpy(), a, rtol=1e-9, atol=1e-12 * np.abs(a).max())
+    np.testing.assert_allclose(Jp.cpu().numpy(), b, rtol=1e-9, atol=1e-12 * np.abs(b).max())
+    assert cost == pytest.approx(0.5 * float(ro @ ro), rel=1e-12)
+
+
+@pytest.mark.parametrize("jac_f32", [True, False])
+def test_vector2_lm_trajectory(jac_f32):
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=jac_f32, residual_model="vector2")
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    x, st = ba.optimize(x0, prob, cx_cy_skew=k3)
+    c2, p2, o2 = bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs)
+    ref = bo.lm_solve(x0, sc.C, sc.P, c2, p2, o2, k3, sc.avg_cam_width, model="vector2")
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    rms = bo.rms_reprojection_px(x, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+    assert rms == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3), rel=1e-4)

@@ -286,3 +286,37 @@ def test_ceres_style_losses_of_the_colmap_cost():
         assert np.all(e <= s * (1 + 1e-15)) and np.all(np.diff(e[np.argsort(s)]) >= -1e-9)  # rho(s) <= s, monotone in s
     l1, _, _ = bo.reprojection_errors(*args, "ceres_soft_l1", 2.0)
     np.testing.assert_allclose(l1, 8.0 * (np.sqrt(1 + s / 4.0) - 1), rtol=1e-13)   # 2 b (sqrt(1 + s/b) - 1), b = 4
+
+
+def test_vector2_residual_model_vs_autodiff_of_the_projection():
+    """the 2-vector residual (projection - observation)/w of COLMAP's BundleAdjustmentCostFunction
+    (colmap/src/base/cost_functions.h:44-86) as 2N rows (`expand_vector2`).  Residuals and Jacobian against torch.autograd
+    through the literal restatement of the reference's K [R|t] projection chain; its cost is the classical BA objective."""
+    sc = b200ba.synth.make_ba_scene("tiny", seed=2)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    w = sc.avg_cam_width
+    c2, p2, o2 = bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs)
+    r, _, a, b = bo.ba_eval(x0, sc.C, c2, p2, o2, k3, w * w, model="vector2")
+    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, c2.astype(np.int64), p2.astype(np.int64)).toarray()
+    ci, pi, ob, kk = torch.tensor(sc.cam_idx.astype(np.int64)), torch.tensor(sc.pt_idx.astype(np.int64)), torch.tensor(sc.obs), torch.tensor(k3)
+
+    def f(p):
+        C = sc.C
+        cam, ff, X = p[:6 * C].reshape(-1, 6), p[6 * C:8 * C].reshape(-1, 2), p[8 * C:].reshape(-1, 3)
+        KE = torch.stack([rl.parse_intrinsics(ff[c], kk[c]) @ rl.parse_cam_pose(cam[c]) for c in range(C)])
+        q = torch.einsum("nij,nj->ni", KE[ci][:, :, :3], X[pi]) + KE[ci][:, :, 3]
+        return ((q[:, :2] / q[:, 2:3] - ob) / w).reshape(-1)          # (x0, y0, x1, y1, ...): the row order of expand_vector2
+
+    np.testing.assert_allclose(r, f(torch.tensor(x0)).numpy(), rtol=1e-11, atol=1e-15)
+    Jd = torch.autograd.functional.jacobian(f, torch.tensor(x0)).numpy()
+    np.testing.assert_allclose(J, Jd, rtol=1e-9, atol=1e-12 * np.abs(Jd).max())
+    # 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 = half the TRIVIAL_LOSS evaluator total / w^2
+    e, _, _ = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, "trivial")
+    assert 0.5 * float(r @ r) == pytest.approx(0.5 * e.sum() / (w * w), rel=1e-13)
+    # and an LM run on it reaches a far smaller reprojection error than the reference's squared-scalar residual does
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    c2, p2, o2 = bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs)
+    v2 = bo.lm_solve(x0, sc.C, sc.P, c2, p2, o2, k3, sc.avg_cam_width, model="vector2")
+    assert np.all(np.diff(v2.trace.loss)[np.array(v2.trace.accepted)] < 0)
+    assert bo.rms_reprojection_px(v2.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3) < 0.5
