@@ -11,6 +11,7 @@ if [ -z "$SKIP_TESTS" ]; then
 fi
 timeout 300 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"
 tail -c 600 $out/bench.json
+B200BA_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_vector2.py -m gpu -q > $out/pytest_vector2.log 2>&1; echo "vector2 pytest exit $?"; tail -3 $out/pytest_vector2.log
 timeout 200 python tools/reproj_probe.py > $out/reproj.json 2> $out/reproj.err; echo "reproj probe exit $?"; cat $out/reproj.json
 if [ -n "$VARIANTS" ]; then bash tools/mv_variants.sh > $out/variants.txt 2>&1; cat $out/variants.txt; fi
 if [ -z "$SKIP_NCU" ]; then
