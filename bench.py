@@ -367,6 +367,7 @@ def bench_pose(b200ba, dev, args):
     return {"workload": "4096 poses x 512 correspondences, Cauchy, pose noise 5e-3", "solves_per_s": 4096 / (ms * 1e-3),
             "pose_iterations_per_s": float(its.sum()) / (ms * 1e-3), "ms_per_batch": ms,
             "iters_mean": float(its.mean()), "iters_max": int(its.max()),
+            "iters_histogram": [int(v) for v in np.bincount(its.astype(np.int64).clip(min=0))],  # [k] = poses that took k LM iterations
             "e2e_solves_per_s": 4096 / t_e2e, "e2e_h2d_bytes": int(q0.nbytes + c3.nbytes + pb.points.nbytes + pb.obs.nbytes + pb.mask.nbytes)}
 
 
