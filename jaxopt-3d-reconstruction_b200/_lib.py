@@ -81,10 +81,9 @@ def load():
                                            vp, vp, vp, vp, vp, vp]
     lib.b200ba_profile_enable.argtypes = [vp, i32]
     lib.b200ba_profile_get.argtypes = [vp, C.POINTER(dbl), C.POINTER(i64)]
-    for name in SYMBOLS:
-        fn = getattr(lib, name)
-        if fn.restype is C.c_int and name not in ("b200ba_version",):
-            pass
+    for name in SYMBOLS:  # a stale library (older build without a newer entry point) must fail here, not at first use
+        if not hasattr(lib, name):
+            raise B200BAError(f"{LIB_PATH} lacks {name}: rebuild it (make -C jaxopt-3d-reconstruction_b200/csrc)")
     _lib = lib
     return lib
 

@@ -31,7 +31,6 @@ CAMERA_MODELS = {
     9: ("RADIAL_FISHEYE", 5), 10: ("THIN_PRISM_FISHEYE", 12),
 }
 _MODEL_ID = {name: (mid, n) for mid, (name, n) in CAMERA_MODELS.items()}
-_NO_POINT = np.uint64(0xFFFFFFFFFFFFFFFF)  # images.py:49
 
 
 class ModelFormatError(ValueError):
