@@ -327,6 +327,19 @@ def run_b200(args):
                                   "status": i[5]} for i in info],
                       "jacobian_obs_per_s": jac_obs_s, "kernels": kern, "host_cores": os.cpu_count()}}
 
+    if world == 1:
+        # RMS reprojection error (pixels) before / after the last end-to-end solve, from the host copy of its result with the
+        # package's NumPy projection helper (outside every timed region; never allowed to break the line)
+        try:
+            def _rms_px(xv):
+                poses, intr, pts3 = b200ba.unpack_params(np.asarray(xv), k3, sc.C)
+                uv = b200ba.synth.project_np(poses[sc.cam_idx], intr[sc.cam_idx], pts3[sc.pt_idx])
+                return float(np.sqrt(((uv - sc.obs) ** 2).sum(axis=1).mean()))
+            line["extra"]["rms_reprojection_px"] = {"initial": _rms_px(x0), "final": _rms_px(params),
+                                                    "of": "last end-to-end solve (full LM solve from the noisy start)"}
+        except Exception as exc:  # noqa: BLE001
+            line["extra"]["rms_reprojection_px"] = {"error": repr(exc)}
+
     if not args.no_pose and world == 1:
         line["extra"]["pose"] = bench_pose(b200ba, dev, args)
     if not args.no_cpu_baseline and world == 1:
