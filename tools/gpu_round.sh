@@ -22,6 +22,9 @@ if [ -z "$SKIP_NCU" ]; then
       -k regex:"k_cs_ring|k_ps|k_cs<" -s 30 -c 4 -f -o $out/prof_mv $CMD > $out/ncu_full_mv.log 2>&1
   timeout 600 ncu --set full --clock-control none --import-source on \
       -k regex:"k_resjac|k_cam_blocks|k_point" -s 5 -c 7 -f -o $out/prof_lin $CMD > $out/ncu_full_lin.log 2>&1
+  timeout 200 python tools/pose_probe.py > $out/pose.json 2> $out/pose.err &&
+  timeout 300 ncu --set full --clock-control none --import-source on -k regex:"k_pose_lm" -s 3 -c 1 -f -o $out/prof_pose \
+      python tools/pose_probe.py > $out/ncu_full_pose.log 2>&1
   timeout 300 ncu --set full --clock-control none --import-source on -k regex:"k_reproj_err" -c 2 -f -o $out/prof_reproj \
       python tools/reproj_probe.py venice1778 1 > $out/ncu_full_reproj.log 2>&1
   echo "ncu exit $?"; ls -la $out
