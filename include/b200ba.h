@@ -135,10 +135,15 @@ int b200ba_pose_lm_batched(int B, int Npts, double* params8_inout, const double*
                            double* loss_out /*B*/, double* grad_l2 /*B*/,
                            double* damping_out /*B or NULL*/, int32_t* status /*B*/, void* stream);
 
+/* How the plan will run (diagnostics for bench.py / tests): out[8] = {point side tiled (ba_ps_tile.cuh), tile rows, tiles,
+ * fused residual/Jacobian + camera blocks, point blocks of the B order, dense reduced-camera solve selected, point chunks,
+ * split camera passes (multi-rank sequence)}. */
+int b200ba_plan_info(b200ba_plan* plan, int* out /*[8]*/);
+
 /* ---- measurement: per-kernel-class CUDA-event timing on the launching stream.  Classes:
  * 0 residual+Jacobian (K1), 1 point blocks, 2 camera blocks, 3 point inverses, 4 Schur camera
  * corrections, 5 block-Jacobi inverses, 6 matvec point pass, 7 matvec camera pass, 8 PCG vector
- * kernels, 9 back-substitution, 10 trial cost, 11 other. */
+ * kernels, 9 back-substitution, 10 trial cost, 11 other, 12 reprojection-error evaluator. */
 int b200ba_profile_enable(b200ba_plan* plan, int on);
 int b200ba_profile_get(b200ba_plan* plan, double* ms_out /*[16]*/, int64_t* count_out /*[16]*/);
 

@@ -83,7 +83,8 @@ def _require_cuda():
 
 
 def _dev(a, dtype, device):
-    """host/any array -> contiguous device tensor (pinned staging for large host arrays)."""
+    """host/any array -> contiguous device tensor.  A pinned torch CPU tensor is copied asynchronously at full PCIe
+    speed; a NumPy array (pageable) goes through the driver's staged copy."""
     if isinstance(a, torch.Tensor):
         return a.to(device=device, dtype=dtype, non_blocking=True).contiguous()
     t = torch.from_numpy(np.ascontiguousarray(a))
@@ -154,15 +155,36 @@ class BAProblem:
             pass
 
 
-def shard_points(pt_idx: np.ndarray, P: int, world: int):
+def shard_points(pt_idx, P: int, world: int):
     """Contiguous point ranges balanced by observation count.
-    Returns bounds (world+1,) such that rank r owns points [bounds[r], bounds[r+1])."""
-    counts = np.bincount(np.asarray(pt_idx, dtype=np.int64), minlength=P)
-    cum = np.concatenate([[0], np.cumsum(counts)])
-    total = cum[-1]
-    bounds = np.searchsorted(cum, np.arange(world + 1) * (total / world), side="left")
+    Returns bounds (world+1,) int64 such that rank r owns points [bounds[r], bounds[r+1]).  `pt_idx` may be a NumPy
+    array (host) or a torch tensor (then the histogram / scan / search run on its device and only world+1 integers
+    come back)."""
+    if isinstance(pt_idx, torch.Tensor):
+        counts = torch.bincount(pt_idx.to(torch.int64), minlength=P)
+        cum = torch.cat([counts.new_zeros(1), torch.cumsum(counts, 0)])
+        total = int(cum[-1])
+        targets = torch.arange(world + 1, device=cum.device, dtype=torch.float64) * (total / world)
+        bounds = torch.searchsorted(cum.to(torch.float64), targets, right=False).cpu().numpy().astype(np.int64)
+    else:
+        counts = np.bincount(np.asarray(pt_idx, dtype=np.int64), minlength=P)
+        cum = np.concatenate([[0], np.cumsum(counts)])
+        total = cum[-1]
+        bounds = np.searchsorted(cum, np.arange(world + 1) * (total / world), side="left")
     bounds[0], bounds[-1] = 0, P
     return np.maximum.accumulate(np.minimum(bounds, P)).astype(np.int64)
+
+
+def shard_rows(cam_idx, pt_idx, obs, P: int, world: int, rank: int):
+    """One rank's share of a point-sharded problem, on the HOST (data placement, done once per problem): the rows whose
+    point lies in this rank's range, point indices rebased to the range.  Returns
+    (cam_idx, pt_idx_local, obs, (lo, hi), bounds) — feed them to `build_problem_sparse(..., pt_range=(lo, hi))`."""
+    pt = np.asarray(pt_idx)
+    bounds = shard_points(pt, P, world)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    keep = (pt >= lo) & (pt < hi)
+    return (np.ascontiguousarray(np.asarray(cam_idx)[keep]), np.ascontiguousarray(pt[keep] - lo).astype(np.int32),
+            np.ascontiguousarray(np.asarray(obs)[keep]), (lo, hi), bounds)
 
 
 class B200BundleAdjustment:
@@ -182,10 +204,14 @@ class B200BundleAdjustment:
         self.jac_f32, self.verbose = jac_f32, verbose
         self.fixed_pcg_iters = 0
         self.group = process_group
+        # Point-sharded multi-GPU mode is OPT-IN (distributed=True or an explicit process_group): a process group that
+        # happens to be initialised for unrelated work must not turn every solve into a collective.
         import torch.distributed as dist
-        self.world = dist.get_world_size(process_group) if (distributed if distributed is not None else dist.is_initialized()) else 1
+        on = bool(distributed) or process_group is not None
+        if on and not dist.is_initialized():
+            raise _lib.B200BAError("distributed=True needs an initialised torch.distributed process group")
+        self.world = dist.get_world_size(process_group) if on else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
-        self._cache = None  # (arrays, BAProblem)
 
     # ------------------------------------------------------------------ reference API
     def prepare_params(self, poses0, intrinsics0, points0):
@@ -207,16 +233,15 @@ class B200BundleAdjustment:
         """bundle_adjustment.py:104-120.  `points_2d_all` may also be a BAProblem built by
         build_problem()/build_problem_sparse() (then indices/masks are ignored)."""
         if isinstance(points_2d_all, BAProblem):
-            prob = points_2d_all
-        else:
-            key = (points_2d_all, p3d_indices_all, masks_all)
-            if self._cache is not None and all(a is b for a, b in zip(self._cache[0], key)):
-                prob = self._cache[1]
-            else:
-                n_pts = (np.asarray(opt_params).shape[0] - 8 * self.cam_num) // 3
-                prob = self.build_problem(points_2d_all, p3d_indices_all, masks_all, n_pts)
-                self._cache = (key, prob)
-        return self._solve(opt_params, cx_cy_skew, prob)
+            return self._solve(opt_params, cx_cy_skew, points_2d_all)
+        # like the reference, the arrays are re-read on every call (no cache keyed on object identity: a caller that
+        # rewrites its buffers in place must get the new problem); build a BAProblem once for repeated solves
+        n_pts = (np.asarray(opt_params).shape[0] - 8 * self.cam_num) // 3
+        prob = self.build_problem(points_2d_all, p3d_indices_all, masks_all, n_pts)
+        try:
+            return self._solve(opt_params, cx_cy_skew, prob)
+        finally:
+            prob.close()
 
     # ------------------------------------------------------------------ problem builders
     def build_problem(self, points_2d_all, p3d_indices_all, masks_all, points_num):
@@ -233,9 +258,11 @@ class B200BundleAdjustment:
         obs = p2d[sel].contiguous()
         return self.build_problem_sparse(cam_idx, pt_idx, obs, points_num)
 
-    def build_problem_sparse(self, cam_idx, pt_idx, obs, points_num):
-        """One row per observation (any order). With torch.distributed initialised the rows are
-        sharded by point range across ranks (each rank passes the FULL problem)."""
+    def build_problem_sparse(self, cam_idx, pt_idx, obs, points_num, pt_range=None):
+        """One row per observation (any order).  Multi-rank (distributed=True): either every rank passes the FULL
+        problem and the rows are sharded by point range on the device (only world+1 integers travel to the host), or
+        every rank passes its OWN rows from `shard_rows` together with `pt_range=(lo, hi)` (point indices already local)
+        and uploads nothing else."""
         _require_cuda()
         dev = self.device
         cam_idx = _dev(cam_idx, torch.int32, dev)
@@ -243,8 +270,10 @@ class B200BundleAdjustment:
         obs = _dev(obs, torch.float64, dev)
         P = int(points_num)
         lo, hi = 0, P
-        if self.world > 1:
-            bounds = shard_points(pt_idx.cpu().numpy(), P, self.world)
+        if pt_range is not None:
+            lo, hi = int(pt_range[0]), int(pt_range[1])
+        elif self.world > 1:
+            bounds = shard_points(pt_idx, P, self.world)
             lo, hi = int(bounds[self.rank]), int(bounds[self.rank + 1])
             keep = (pt_idx >= lo) & (pt_idx < hi)
             cam_idx, pt_idx, obs = cam_idx[keep].contiguous(), (pt_idx[keep] - lo).contiguous(), obs[keep].contiguous()
@@ -338,17 +367,18 @@ class B200BundleAdjustment:
         res, traj = self.solve_device(prob, cam8, k3, pts)
         loss_t, grad_t, mu_t, pcg_t, acc_t = traj
         if self.world > 1:
+            # every rank returns the FULL parameter vector (the reference's contract): one all-reduce of a zero-filled
+            # (P,3) buffer that holds this rank's point range (ranges are disjoint; works for unequal shard sizes and on
+            # any backend)
             import torch.distributed as dist
-            sizes = [None] * self.world
-            dist.all_gather_object(sizes, int(pts.shape[0]), group=self.group)
+            pts_full = torch.zeros(prob.P_global, 3, dtype=torch.float64, device=dev)
+            pts_full[prob.pt_lo:prob.pt_hi] = pts
             if dist.get_backend(self.group) == "nccl":
-                parts = [torch.empty(s, 3, dtype=torch.float64, device=dev) for s in sizes]
-                dist.all_gather(parts, pts, group=self.group)
+                dist.all_reduce(pts_full, group=self.group)
             else:
-                parts = [torch.empty(s, 3, dtype=torch.float64) for s in sizes]
-                dist.all_gather(parts, pts.cpu(), group=self.group)
-                parts = [q.to(dev) for q in parts]
-            pts_full = torch.cat(parts, dim=0)
+                h = pts_full.cpu()
+                dist.all_reduce(h, group=self.group)
+                pts_full = h.to(dev)
         else:
             pts_full = pts
         out = torch.cat([cam8[:, :6].reshape(-1), cam8[:, 6:].reshape(-1), pts_full.reshape(-1)]).cpu().numpy()
@@ -400,17 +430,43 @@ class B200PoseOptimizer:
         return params, it, loss, err, mu, st
 
     def optimize(self, opt_params, points, observations, cx_cy_skew, mask):
-        """pose_optimization.py:86-89. Host arrays in, (params (B,8), state) out; inputs untouched."""
+        """pose_optimization.py:86-89. Host arrays in, (params (B,8), state) out; inputs untouched.
+        The batch is cut into chunks: chunk k+1 travels host->device on a copy stream while chunk k is being solved
+        (pinned torch CPU tensors copy at full PCIe speed; NumPy arrays take the driver's pageable path); ONE
+        device->host copy returns parameters and per-pose state."""
         _require_cuda()
         dev = self.device
-        p = _dev(opt_params, torch.float64, dev).clone()
-        pts = _dev(points, torch.float64, dev)
-        obs = _dev(observations, torch.float64, dev)
-        k3 = _dev(cx_cy_skew, torch.float64, dev)
-        m = _dev(mask, torch.float64, dev)
-        p, it, loss, err, mu, st = self.optimize_device(p, pts, obs, k3, m)
-        out = torch.cat([p, loss[:, None], err[:, None], mu[:, None], it.to(torch.float64)[:, None],
-                         st.to(torch.float64)[:, None]], dim=1).cpu().numpy()  # one D2H copy
+        host = [a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+                for a in (opt_params, points, observations, cx_cy_skew, mask)]
+        host = [t if t.dtype == torch.float64 else t.to(torch.float64) for t in host]
+        B = int(host[0].shape[0])
+        nchunk = max(1, min(8, B // 256))
+        with torch.cuda.device(dev):
+            main = torch.cuda.current_stream()
+            if getattr(self, "_copy_stream", None) is None:
+                self._copy_stream = torch.cuda.Stream(device=dev)
+            cs = self._copy_stream
+            d = [torch.empty(t.shape, dtype=torch.float64, device=dev) for t in host]
+            out = torch.empty(B, 13, dtype=torch.float64, device=dev)
+            cs.wait_stream(main)
+            bounds = [B * k // nchunk for k in range(nchunk + 1)]
+            events = []
+            with torch.cuda.stream(cs):
+                for k in range(nchunk):
+                    lo, hi = bounds[k], bounds[k + 1]
+                    for dst, src in zip(d, host):
+                        dst[lo:hi].copy_(src[lo:hi], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(cs)
+                    events.append(ev)
+            for k in range(nchunk):
+                lo, hi = bounds[k], bounds[k + 1]
+                main.wait_event(events[k])
+                p, it, loss, err, mu, st = self.optimize_device(d[0][lo:hi], d[1][lo:hi], d[2][lo:hi], d[3][lo:hi], d[4][lo:hi])
+                o = out[lo:hi]
+                o[:, :8] = p
+                o[:, 8], o[:, 9], o[:, 10], o[:, 11], o[:, 12] = loss, err, mu, it.to(torch.float64), st.to(torch.float64)
+            out = out.cpu().numpy()  # one D2H copy
         state = LMState(iter_num=out[:, 11].astype(np.int64), loss=out[:, 8].copy(), error=out[:, 9].copy(),
                         damping_factor=out[:, 10].copy(), status=out[:, 12].astype(np.int64))
         return out[:, :8].copy(), state

@@ -18,6 +18,7 @@
 #include "ba_pcg.cuh"
 #include "ba_cs_ring.cuh"
 #include "ba_cs_warp.cuh"
+#include "ba_ps_tile.cuh"
 #include "pose_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -57,7 +58,7 @@ struct b200ba_plan {
   int C = 0, P = 0;
   int64_t N = 0;
   int jac_f32 = 0;
-  int residual_model = 0;  // 0: the reference's scalar squared error per observation; 1: 2-vector model over 2N rows (k_resjac_v2)
+  int residual_model = 0;  // 0: the reference's scalar squared error per observation; 1: 2-vector model over 2N rows (k_resjac<JT, 1, .>)
   size_t jsz = 8;
   // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
@@ -76,17 +77,26 @@ struct b200ba_plan {
   int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
   int nchunks = 0, nPB = 1, block_rows = 0, max_cam_rows = 0, stash_rows = 0;
   size_t stash_bytes = 0;
+  // tiled point-side kernel (ba_ps_tile.cuh): tiles of whole chunks, their rows in B order, A row -> slot in tile
+  int32_t *tile_row = nullptr, *tile_pt = nullptr, *gpos = nullptr;
+  uint16_t* lpos = nullptr;
+  int ntiles = 0, tile_rows = 0, use_tile = 0;
+  int fused_lin = 0;    // U_c / g_c accumulated inside the residual/Jacobian kernel
+  int dense_schur = 0;  // small scenes: reduced camera system formed densely and factored (ba_dense.cuh)
   int32_t* pt_B = nullptr;   // point of every B row (padding rows: -1)
   double2* obs_B = nullptr;  // observations in B order
   void* rec_A = nullptr;     // 32 B row records {b, r} in A order (K1 -> point blocks)
   // linearisation
   void *Jp_ps = nullptr, *Jc_B = nullptr;
-  double *r_B = nullptr, *w_B = nullptr, *beta_B = nullptr, *sig = nullptr, *omg = nullptr;
+  double *sig = nullptr, *omg = nullptr;
+  double2* wb_B = nullptr;   // {w_i, beta_i} per B row: Schur rhs / block-diagonal scalars (k_point_prepare -> k_cam_blocks)
+  int32_t* order_B = nullptr;  // caller's row of every B position (padding: -1)
   double *U = nullptr, *gc = nullptr, *lin_scal = nullptr, *V = nullptr, *gp = nullptr, *Vinv = nullptr;
   double *Sd = nullptr, *rhs_part = nullptr, *Minv = nullptr, *rhs = nullptr;
   double* cv = nullptr;  // PCG vectors, camera-major records (ba_pcg.cuh)
   double *y = nullptr, *vp = nullptr;
-  double *cam_trial = nullptr, *pts_trial = nullptr;
+  double *cam_trial = nullptr;
+  double *pts4 = nullptr, *pts4_trial = nullptr;  // points as 32 B records {X, Y, Z, 0}: ONE 256-bit gather per row
   double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
   SolverState* st = nullptr;
   SolverState* st_host = nullptr;  // pinned
@@ -112,7 +122,7 @@ struct b200ba_plan {
   }
 };
 enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, PC_CAM_FINISH, PC_MV_PT, PC_MV_CAM,
-       PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_COUNT };
+       PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_EVAL, PC_COUNT };
 // k_cs_warp with the plan's unroll (see ba_cs_warp.cuh)
 #define CW_LAUNCH(p, cls, grid, st, ...)                                                                   \
   do {                                                                                                     \
@@ -285,7 +295,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   A(U, (size_t)C * 72 + 8) A(V, (size_t)P * 6) A(gp, (size_t)P * 3) A(Vinv, (size_t)P * 6)
   A(Sd, (size_t)C * 64 + (size_t)C * 8) A(Minv, (size_t)C * 64) A(rhs, (size_t)C * 8)
   A(cv, (size_t)C * CV_STRIDE) A(y, (size_t)C * 8 + 8)
-  A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts_trial, (size_t)P * 3)
+  A(vp, (size_t)P * 3) A(cam_trial, (size_t)C * 8) A(pts4, (size_t)P * 4 + 4) A(pts4_trial, (size_t)P * 4 + 4)
   p->rhs_part = p->Sd + (size_t)C * 64;  // contiguous with Sd: one all-reduce covers both
   p->gc = p->U + (size_t)C * 64;         // [U | g_c | sum r^2, |g_p|^2] contiguous likewise
   p->lin_scal = p->gc + (size_t)C * 8;
@@ -461,8 +471,8 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     void* q = nullptr;
     int bad_alloc = 0;
     if (pool_malloc((void**)&q, nb_rows * 8 * p->jsz) != cudaSuccess) bad_alloc = 1; else { p->allocs.push_back(q); p->Jc_B = q; cudaMemsetAsync(q, 0, nb_rows * 8 * p->jsz, s); }
-    double** arr[5] = {&p->r_B, &p->w_B, &p->beta_B, &p->sig, &p->omg};
-    for (int i = 0; i < 5 && !bad_alloc; ++i) {
+    double** arr[2] = {&p->sig, &p->omg};
+    for (int i = 0; i < 2 && !bad_alloc; ++i) {
       if (pool_malloc((void**)&q, nb_rows * sizeof(double)) != cudaSuccess) { bad_alloc = 1; break; }
       p->allocs.push_back(q);
       *arr[i] = (double*)q;
@@ -474,6 +484,12 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       if (N) k_scatter_i32<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->pt_ps, p->pt_B);
     } else bad_alloc = 1;
     if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(double2)) == cudaSuccess) { p->allocs.push_back(q); p->obs_B = (double2*)q; cudaMemsetAsync(q, 0, nb_rows * sizeof(double2), s); } else bad_alloc = 1;
+    if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(double2)) == cudaSuccess) { p->allocs.push_back(q); p->wb_B = (double2*)q; cudaMemsetAsync(q, 0, nb_rows * sizeof(double2), s); } else bad_alloc = 1;
+    if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
+      p->allocs.push_back(q); p->order_B = (int32_t*)q;
+      k_fill_i32<<<cdiv((int64_t)nb_rows, 256), 256, 0, s>>>((int64_t)nb_rows, -1, p->order_B);
+      if (N) k_scatter_i32<<<cdiv(N, 256), 256, 0, s>>>(N, p->posB, p->order_ps, p->order_B);
+    } else bad_alloc = 1;
     if (!bad_alloc && pool_malloc((void**)&q, ((size_t)N + 1) * 32) == cudaSuccess) { p->allocs.push_back(q); p->rec_A = q; } else bad_alloc = 1;
     if (!bad_alloc && pool_malloc((void**)&q, nb_rows * sizeof(int32_t)) == cudaSuccess) {
       p->allocs.push_back(q); p->posA = (int32_t*)q;
@@ -495,6 +511,14 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    p->fused_lin = 1;
+    if (cudaFuncSetAttribute(k_resjac<float, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
+        cudaFuncSetAttribute(k_resjac<float, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
+        cudaFuncSetAttribute(k_resjac<double, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
+        cudaFuncSetAttribute(k_resjac<double, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess) {
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, "plan_create: shared-memory configuration of the residual/Jacobian kernel");
+    }
     cudaError_t e1 = cudaFuncSetAttribute(k_cs<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
     cudaError_t e2 = cudaFuncSetAttribute(k_cs<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(100 * 1024));
     if (e1 != cudaSuccess || e2 != cudaSuccess || p->stash_bytes > 100 * 1024) {
@@ -552,8 +576,61 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaMemcpyAsync(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaMemcpyAsync(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaStreamSynchronize(s);
+    lap("point chunks");
+    // Tiles of the tiled point-side kernel: consecutive chunks up to tile_rows rows.  Used when a tile still holds
+    // >= 2 rows of the average camera (then the tile's rows are piecewise contiguous in B order) and no single point
+    // exceeds a tile; otherwise the chunk kernel with its L2-window gather stays (Final-13682: 13 682 cameras).
+    int tr = 8192;
+    if (const char* e = getenv("B200BA_TILE_ROWS")) { const int v = atoi(e); if (v >= 1024 && v <= 24576) tr = v; }
+    int want = N > 0 && tr >= 2 * C;
+    if (const char* e = getenv("B200BA_PS_TILE")) want = N > 0 && atoi(e) != 0;
+    if (want) {
+      std::vector<int32_t> trow, tpt;
+      trow.push_back(0); tpt.push_back(0);
+      int cur = 0;
+      bool ok = true;
+      for (int k = 0; k < p->nchunks; ++k) {
+        const int d = crow[k + 1] - crow[k];
+        if (d > tr) { ok = false; break; }
+        if (cur > 0 && cur + d > tr) { trow.push_back(crow[k]); tpt.push_back(cpt[k]); cur = 0; }
+        cur += d;
+      }
+      trow.push_back((int32_t)N); tpt.push_back(P);
+      if (ok) {
+        p->ntiles = (int)trow.size() - 1;
+        p->tile_rows = tr;
+        int64_t *keys = nullptr, *keys2 = nullptr;
+        int32_t *vals = nullptr, *vals2 = nullptr;
+        void* tmp = nullptr;
+        size_t tmp_bytes = 0;
+        const int nbits = 32 + bits_for(p->ntiles);
+        cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, (int)N, 0, nbits, s);
+        const bool a_ok = !dalloc(p, &p->tile_row, trow.size()) && !dalloc(p, &p->tile_pt, tpt.size()) && !dalloc(p, &p->gpos, (size_t)N) &&
+                          !dalloc(p, &p->lpos, (size_t)N) && pool_malloc((void**)&keys, N * sizeof(int64_t)) == cudaSuccess &&
+                          pool_malloc((void**)&keys2, N * sizeof(int64_t)) == cudaSuccess && pool_malloc((void**)&vals, N * sizeof(int32_t)) == cudaSuccess &&
+                          pool_malloc((void**)&vals2, N * sizeof(int32_t)) == cudaSuccess && pool_malloc(&tmp, tmp_bytes) == cudaSuccess;
+        cudaError_t e = a_ok ? cudaSuccess : cudaErrorMemoryAllocation;
+        if (a_ok) {
+          cudaMemcpyAsync(p->tile_row, trow.data(), trow.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+          cudaMemcpyAsync(p->tile_pt, tpt.data(), tpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+          LAUNCH(k_tile_keys, cdiv(N, 256), 256, 0, s, N, p->ntiles, p->tile_row, p->posB, keys, vals);
+          cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, (int)N, 0, nbits, s);
+          LAUNCH(k_tile_fill, cdiv(N, 256), 256, 0, s, N, p->tile_row, keys2, vals2, p->gpos, p->lpos);
+          e = cudaStreamSynchronize(s);
+        }
+        pool_free(keys); pool_free(keys2); pool_free(vals); pool_free(vals2); pool_free(tmp);
+        const int smem = tr * (int)sizeof(double);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, std::string("plan_create: tile tables: ") + cudaGetErrorString(e)); }
+        p->use_tile = 1;
+        if (2 * (size_t)p->ntiles + 16 > 2 * mx + 16) { /* partN holds 2 doubles per tile: ntiles <= nchunks <= mx */ }
+      }
+    }
+    lap("point tiles");
   }
-  lap("point chunks");
   *out = p;
   return B200BA_OK;
 }
@@ -735,25 +812,40 @@ static int read_state(b200ba_plan* p, cudaStream_t s) {
   return 0;
 }
 
+// caller's P x 3 points <-> internal 32 B records {X, Y, Z, 0}
+__global__ void k_pts_to4(int64_t n4, const double* __restrict__ pts, double* __restrict__ pts4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n4) pts4[i] = (i & 3) == 3 ? 0.0 : pts[3 * (i >> 2) + (i & 3)];
+}
+__global__ void k_pts_from4(int64_t n3, const double* __restrict__ pts4, double* __restrict__ pts) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n3) pts[i] = pts4[4 * (i / 3) + (i % 3)];
+}
+static void pts_to4(b200ba_plan* p, const double* pts, double* pts4, cudaStream_t s) {
+  if (p->P) PLAUNCH(p, PC_OTHER, k_pts_to4, cdiv(4 * (int64_t)p->P, 256), 256, 0, s, 4 * (int64_t)p->P, pts, pts4);
+}
+static void pts_from4(b200ba_plan* p, const double* pts4, double* pts, cudaStream_t s) {
+  if (p->P) PLAUNCH(p, PC_OTHER, k_pts_from4, cdiv(3 * (int64_t)p->P, 256), 256, 0, s, 3 * (int64_t)p->P, pts4, pts);
+}
+
 template <typename JT>
 struct Ops {
-  static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
+  static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
                        cudaStream_t s) {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
+    // K0+K1+K2b in one launch: rows, A-order records, and the camera blocks U_c / g_c (ba_kernels.cuh)
     if (p->residual_model)
-      PLAUNCH(p, PC_RESJAC, (k_resjac_v2<JT, true>), C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
-              sqrt(inv_w2), (JT*)p->Jc_B, p->r_B, (RowRec<JT>*)p->rec_A, p->part);
+      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 1, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
+              pts4, sqrt(inv_w2), (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc);
     else
-    PLAUNCH(p, PC_RESJAC, (k_resjac<JT, true>), C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
-            inv_w2, (JT*)p->Jc_B, p->r_B, (RowRec<JT>*)p->rec_A, p->part);
+      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 0, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
+              pts4, inv_w2, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 1, 1, p->lin_scal, 0);
-    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec<JT>*)p->rec_A,
+    if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec*)p->rec_A,
                   (JT*)p->Jp_ps, p->V, p->gp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
-    PLAUNCH(p, PC_CAM_BLOCKS, (k_cam_blocks<JT>), C, p->cb_threads, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, p->r_B, nullptr, nullptr,
-           p->U, p->gc);
     int rc;
     if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
     if ((rc = allreduce(p, p->scal + 2, 1, ncclMax, s))) return rc;
@@ -805,9 +897,15 @@ struct Ops {
   }
   // point-side kernel: omega from sigma (and the PCG scalars of iteration `it` when do_scalars)
   static void ps(b200ba_plan* p, int it, int do_scalars, double rtol, int maxiter, cudaStream_t s) {
+    if (p->use_tile) {
+      PLAUNCH(p, PC_MV_PT, (k_ps_tile<JT, false>), p->ntiles, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
+              p->ntiles, p->C, it, do_scalars, rtol, maxiter, p->st, p->part2, p->tile_row, p->tile_pt, p->pt_ptr, p->gpos, p->lpos,
+              (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr);
+      return;
+    }
     PLAUNCH(p, PC_MV_PT, (k_ps<JT, false>), p->nchunks > 0 ? p->nchunks : 1, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, it,
             do_scalars, rtol, maxiter, p->st, p->part2, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB,
-            (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr);
+            (const JT*)p->Jp_ps, p->Vinv, (size_t)p->P, p->sig, p->omg, nullptr, nullptr, nullptr);
   }
   // matvec tail + vector update + next matvec head; multi-rank: partial sums are all-reduced in between
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
@@ -827,9 +925,9 @@ struct Ops {
   static int prepare(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, P = p->P;
     if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, p->posB,
-                  (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->w_B, p->beta_B);
-    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, p->cb_threads, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, nullptr, p->w_B,
-           p->beta_B, p->Sd, p->rhs_part);
+                  (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->wb_B);
+    PLAUNCH(p, PC_CAM_SCHUR, (k_cam_blocks<JT>), C, p->cb_threads, 0, s, p->nPB, p->camtab, (const JT*)p->Jc_B, nullptr, p->wb_B,
+           p->Sd, p->rhs_part);
     int rc;
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
     PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(8 * (int64_t)C, CF_T), CF_T, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
@@ -906,21 +1004,28 @@ struct Ops {
 
   static int backsub(b200ba_plan* p, cudaStream_t s) {
     cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, CV_X, s);
+    if (p->N && p->use_tile) {
+      PLAUNCH(p, PC_BACKSUB, (k_ps_tile<JT, true>), p->ntiles, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
+              p->ntiles, p->C, 0, 0, 0.0, 0, p->st, nullptr, p->tile_row, p->tile_pt, p->pt_ptr, p->gpos, p->lpos,
+              (const JT*)p->Jp_ps, p->Vinv, p->sig, nullptr, p->gp, p->vp, p->partN);
+      PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->ntiles, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+      return 0;
+    }
     if (p->N) PLAUNCH(p, PC_BACKSUB, (k_ps<JT, true>), p->nchunks, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, 0, 0, 0.0, 0, p->st,
-                      nullptr, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB, (const JT*)p->Jp_ps, p->Vinv, p->sig,
+                      nullptr, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB, (const JT*)p->Jp_ps, p->Vinv, (size_t)p->P, p->sig,
                       nullptr, p->gp, p->vp, p->partN);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;
   }
 
-  static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts, double inv_w2,
+  static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
                   double* out_dev, cudaStream_t s) {
     if (p->residual_model)
-      PLAUNCH(p, PC_COST, (k_resjac_v2<JT, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
-              sqrt(inv_w2), nullptr, nullptr, nullptr, p->part);
+      PLAUNCH(p, PC_COST, (k_resjac<JT, 1, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
+              sqrt(inv_w2), nullptr, nullptr, p->part, nullptr, nullptr);
     else
-    PLAUNCH(p, PC_COST, (k_resjac<JT, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts,
-            inv_w2, nullptr, nullptr, nullptr, p->part);
+      PLAUNCH(p, PC_COST, (k_resjac<JT, 0, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
+              inv_w2, nullptr, nullptr, p->part, nullptr, nullptr);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, p->C, 1, 1, out_dev, 0);
     return 0;
   }
@@ -945,7 +1050,8 @@ extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double
   if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "linearize: null");
   cudaStream_t s = (cudaStream_t)stream_;
   int rc;
-  if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+  pts_to4(p, pts, p->pts4, s);
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
   PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, 1e-6);
   if (U) CK(cudaMemcpyAsync(U, p->U, (size_t)p->C * 64 * 8, cudaMemcpyDeviceToDevice, s));
   if (gc) CK(cudaMemcpyAsync(gc, p->gc, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
@@ -969,7 +1075,7 @@ extern "C" int b200ba_residual_jacobian(b200ba_plan* p, const double* cam8, cons
   cudaStream_t s = (cudaStream_t)stream_;
   const int64_t N = p->N;
   if (N) {
-    if (r) LAUNCH(k_unpermute_rec_r, cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->rec_A, p->jac_f32 ? 2 : 3, r);
+    if (r) LAUNCH(k_unpermute_rec_r, cdiv(N, 256), 256, 0, s, N, p->order_ps, (const double*)p->rec_A, 3, r);
     if (p->jac_f32) {
       if (Jc) LAUNCH((k_unpermute_jc<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, p->posB, (const float*)p->Jc_B, Jc);
       if (Jp) LAUNCH((k_unpermute_rows<float>), cdiv(N, 256), 256, 0, s, N, p->order_ps, (const float*)p->Jp_ps, (size_t)N, 3, Jp);
@@ -1034,7 +1140,8 @@ extern "C" int b200ba_cost(b200ba_plan* p, const double* cam8, const double* k3,
   if (!p || !cost_host) FAIL(B200BA_EINVAL, "null");
   cudaStream_t s = (cudaStream_t)stream_;
   int rc;
-  if ((rc = DISPATCH(p, cost, p, cam8, k3, pts, inv_w2, p->scal + 8, s))) return rc;
+  pts_to4(p, pts, p->pts4_trial, s);  // scratch copy as 32 B records
+  if ((rc = DISPATCH(p, cost, p, cam8, k3, p->pts4_trial, inv_w2, p->scal + 8, s))) return rc;
   if ((rc = allreduce(p, p->scal + 8, 1, ncclSum, s))) return rc;
   CK(cudaMemcpyAsync(p->scal_host, p->scal + 8, 8, cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
@@ -1058,9 +1165,10 @@ extern "C" int b200ba_reprojection_errors(b200ba_plan* p, const double* cam8, co
   cudaStream_t s = (cudaStream_t)stream_;
   if (!p->C) return B200BA_OK;
   const double b = loss_scale * loss_scale;
+  pts_to4(p, pts, p->pts4_trial, s);  // scratch copy as 32 B records
 #define REPROJ_LAUNCH(L)                                                                                                  \
-  PLAUNCH(p, PC_OTHER, (k_reproj_err<L>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, \
-          p->order_ps, pts, b, err_rows, cam_sum)
+  PLAUNCH(p, PC_EVAL, (k_reproj_err<L>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B,          \
+          p->order_B, p->pts4_trial, b, err_rows, cam_sum)
   switch (loss) {
     case 0: REPROJ_LAUNCH(0); break;
     case 1: REPROJ_LAUNCH(1); break;
@@ -1090,8 +1198,9 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   const int C = p->C, P = p->P;
   int rc;
   res->n_jac_evals = res->n_res_evals = res->n_pcg_iters_total = 0;
-  // init_state
-  if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+  // init_state (points live as 32 B records inside the solve; the caller's P x 3 array is written back at the end)
+  pts_to4(p, pts, p->pts4, s);
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
   PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, opts->damping_parameter);
   if ((rc = read_state(p, s))) return rc;
   res->n_jac_evals++;
@@ -1110,18 +1219,18 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
-    if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(3 * (int64_t)P, 256), 256, 0, s, 3 * (int64_t)P, pts, p->vp, p->pts_trial);
-    if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts_trial, inv_w2, p->scal + 8, s))) return rc;
+    if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
+    if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts4_trial, inv_w2, p->scal + 8, s))) return rc;
     res->n_res_evals++;
     if ((rc = allreduce(p, p->scal + 8, 3, ncclSum, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_pack_decide, 1, 1, 0, s, p->scal);
     PLAUNCH(p, PC_OTHER, k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
     PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
-    if (P) PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(3 * (int64_t)P, 256), 256, 0, s, p->st, 3 * (int64_t)P, p->pts_trial, pts);
+    if (P) PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(4 * (int64_t)P, 256), 256, 0, s, p->st, 4 * (int64_t)P, p->pts4_trial, p->pts4);
     if ((rc = read_state(p, s))) return rc;
     const int accepted = p->st_host->accepted;
     if (accepted) {
-      if ((rc = DISPATCH(p, linearize, p, cam8, k3, pts, inv_w2, s))) return rc;
+      if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
       PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
       if ((rc = read_state(p, s))) return rc;
       res->n_jac_evals++;
@@ -1140,6 +1249,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if (status & B200BA_ST_XCHG_TIMEOUT) FAIL(B200BA_ENCCL, "lm_solve: timed out waiting for a peer's partial sums (peer-memory exchange)");
     if (!(it < opts->maxiter && err > opts->tol)) break;  // run(): NaN error also stops (NaN > tol is false)
   }
+  pts_from4(p, p->pts4, pts, s);
   if (err > opts->tol) status |= B200BA_ST_MAXITER;
   if (!(p->st_host->loss == p->st_host->loss) || !(err == err)) status |= B200BA_ST_NAN;
   res->iter_num = it;
@@ -1179,6 +1289,14 @@ extern "C" int b200ba_pose_lm_batched(int B, int Npts, double* params8, const do
            maxiter, tol, damping, iter_num, loss_out, grad_l2, damping_out, status);
   }
   CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_plan_info(b200ba_plan* p, int* out) {
+  if (!p || !out) FAIL(B200BA_EINVAL, "null");
+  for (int k = 0; k < 8; ++k) out[k] = 0;
+  out[0] = p->use_tile; out[1] = p->tile_rows; out[2] = p->ntiles; out[3] = p->fused_lin; out[4] = p->nPB; out[5] = p->dense_schur;
+  out[6] = p->nchunks; out[7] = p->split;
   return B200BA_OK;
 }
 

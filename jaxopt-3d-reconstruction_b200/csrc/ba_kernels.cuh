@@ -100,117 +100,154 @@ struct CamRuns {
   }
 };
 
-// 32 B row records {b[3], r} of the A order: one 256-bit store / load each (one request per sector)
-template <typename JT> struct RowRec;
-template <> struct __align__(32) RowRec<float> { float b[3]; float pad0; double r; double pad1; };
-template <> struct __align__(32) RowRec<double> { double b[3]; double r; };
-static_assert(sizeof(RowRec<float>) == 32 && sizeof(RowRec<double>) == 32, "row record = one 32 B sector");
-__device__ __forceinline__ void st_rec(RowRec<float>* p, const double* b, double r) {
-  const unsigned lo = (unsigned)__double2loint(r), hi = (unsigned)__double2hiint(r);
-  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(__float_as_uint((float)b[0])),
-               "r"(__float_as_uint((float)b[1])), "r"(__float_as_uint((float)b[2])), "r"(0u), "r"(lo), "r"(hi), "r"(0u), "r"(0u) : "memory");
-}
-__device__ __forceinline__ void st_rec(RowRec<double>* p, const double* b, double r) {
+// 32 B row records {b[3], r} of the A order: one 256-bit store / load each (one request per sector).  fp64 in BOTH builds
+// (the record is one sector either way): V_p and g_p = sum b r are accumulated from unrounded rows, so the gradient is
+// exact also with fp32-STORED Jacobian rows (the 2-vector model does not converge to tol on a gradient with fp32 noise).
+struct __align__(32) RowRec { double b[3]; double r; };
+static_assert(sizeof(RowRec) == 32, "row record = one 32 B sector");
+__device__ __forceinline__ void st_rec(RowRec* p, const double* b, double r) {
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(b[0]), "d"(b[1]), "d"(b[2]), "d"(r) : "memory");
 }
-__device__ __forceinline__ void ld_rec(const RowRec<float>* p, double* b, double& r) {
-  float v[8];
-  ld256(reinterpret_cast<const float*>(p), v);
-  b[0] = v[0]; b[1] = v[1]; b[2] = v[2];
-  r = __hiloint2double((int)__float_as_uint(v[5]), (int)__float_as_uint(v[4]));
-}
-__device__ __forceinline__ void ld_rec(const RowRec<double>* p, double* b, double& r) {
+__device__ __forceinline__ void ld_rec(const RowRec* p, double* b, double& r) {
   double v[4];
   ld256(reinterpret_cast<const double*>(p), v);
   b[0] = v[0]; b[1] = v[1]; b[2] = v[2]; r = v[3];
 }
 
-// ---------------------------------------------------------------- K0+K1: residual + Jacobian rows
+// ---------------------------------------------------------------- K0+K1+K2b: residual + Jacobian rows + camera blocks
 // One CTA per camera walks the camera's rows in B order (runs of consecutive points inside a point
 // block).  The 26-double camera table is built once per CTA in shared memory (every lane reads the same
-// entries: broadcasts), the only gather is the 24 B point, and it stays inside the block's point range
-// (L2-resident).  Per row it writes, coalesced in B order, the camera part of the Jacobian row
-// (8 x JT) and r, and SCATTERS one 32 B record {b (3 x JT), r} to the row's A position (a whole sector,
-// inside the L2 window of the point block) from which k_point_blocks builds V_p, g_p and the SoA point part.
-// cost_part[c] = sum r^2 over the camera.  WITH_JAC = false: trial cost only (reads 20 B/row, writes nothing).
+// entries: broadcasts), the only gather is the 32 B point record (ONE 256-bit request per row), and it stays inside the
+// block's point range (L2-resident).  Per row it writes, coalesced in B order, the camera part of the Jacobian row
+// (8 x JT), and SCATTERS one 32 B record {b (3 x fp64), r} to the row's A position (a whole sector, inside the L2
+// window of the point block) from which k_point_blocks builds V_p, g_p and the SoA point part.
+// FUSED camera blocks (round 2): the rows never leave the SM between K1 and K2b.  g_c = sum a r is accumulated from the
+// UNROUNDED fp64 row (exact gradient also with fp32-stored rows); the row as STORED (rounded to JT) is stashed in a
+// shared-memory tile and U_c = sum a a^T is accumulated from that in a second phase per tile — the camera block is
+// therefore exactly the one of the stored operator, (U - W V^-1 W^T) stays the Schur complement of J~^T J~ + mu I.
+// Replaces the separate k_cam_blocks launch over the linearisation (40 B/row re-read + 8 B/row r_B write gone).
+// MODEL 0: the reference's scalar residual r = (dx^2 + dy^2)/w^2 (bundle_adjustment.py:17-21,74), scale = 1/w^2.
+// MODEL 1: the 2-vector residual of the reference's COLMAP comparator over 2N rows (colmap/src/base/cost_functions.h:44-86,
+//          principal point fixed): observation (x, NaN) marks the x row, (NaN, y) the y row, scale = 1/w.
+// cost_part[c] = sum r^2 over the camera.  WITH_JAC = false: trial cost only (reads 24 B/row, writes nothing).
 #define RJ_THREADS 256
-template <typename JT, bool WITH_JAC>
-__global__ void __launch_bounds__(RJ_THREADS)
-k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
-         const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
-         const double* __restrict__ pts, double inv_w2, JT* __restrict__ Jc_B, double* __restrict__ r_B,
-         RowRec<JT>* __restrict__ rec_A, double* __restrict__ cost_part) {
-  __shared__ CamRuns runs;
-  __shared__ double T[TAB_STRIDE];
-  __shared__ double sm[32];
-  const int c = blockIdx.x;
-  if (threadIdx.x == RJ_THREADS - 1) build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
-  const int L = runs.load(c, nPB, camtab);  // includes the __syncthreads that publishes T
-  double v[1] = {0.0};
-  int run = 0;
-  for (int l = threadIdx.x; l < L; l += RJ_THREADS) {
-    const size_t j = runs.locate(l, run);
-    const int p = __ldg(pt_B + j);
-    if (p < 0) continue;  // padding row of a run
-    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
-    const double2 o = __ldg(obs_B + j);
-    const Proj pr = project(T, X, Y, Z);
-    const double dx = pr.u - o.x, dy = pr.v - o.y;
-    const double r = (dx * dx + dy * dy) * inv_w2;
-    v[0] += r * r;
-    if (WITH_JAC) {
-      double a[8], b[3];
-      jac_row(T, pr, X, Y, Z, 2.0 * dx * inv_w2, 2.0 * dy * inv_w2, a, b);
-      store8<JT>(Jc_B + 8 * j, a);
-      r_B[j] = r;
-      st_rec(rec_A + __ldg(posA + j), b, r);
-    }
-  }
-  block_sum<1>(v, sm);
-  if (threadIdx.x == 0) cost_part[c] = v[0];
+#define RJ_TILE_BYTES (64 * 1024)  // shared-memory row stash of the fused kernel: 2048 fp32 rows / 1024 fp64 rows
+template <typename JT> __device__ __forceinline__ void strow_cvt(JT* p, const double* a);
+template <> __device__ __forceinline__ void strow_cvt<float>(float* p, const double* a) {
+  float4* q = reinterpret_cast<float4*>(p);
+  q[0] = make_float4((float)a[0], (float)a[1], (float)a[2], (float)a[3]);
+  q[1] = make_float4((float)a[4], (float)a[5], (float)a[6], (float)a[7]);
+}
+template <> __device__ __forceinline__ void strow_cvt<double>(double* p, const double* a) { strow(p, a); }
+
+template <int MODEL>
+__device__ __forceinline__ double row_residual(const Proj& pr, double ox, double oy, double scale, double& ex, double& ey) {
+  if (MODEL == 1) return v2_residual(pr, ox, oy, scale, ex, ey);
+  const double dx = pr.u - ox, dy = pr.v - oy;
+  ex = 2.0 * dx * scale;
+  ey = 2.0 * dy * scale;
+  return (dx * dx + dy * dy) * scale;
 }
 
-// ---------------------------------------------------------------- K0+K1 for the 2-vector residual model
-// COLMAP's BundleAdjustmentCostFunction (colmap/src/base/cost_functions.h:44-86) has TWO residuals per observation,
-// (u - x, v - y), principal point fixed (refine_principal_point = 0, src/benchmark/colmap_benchmark/bundle_adjuster.py:25-38).
-// Here that is the SAME pipeline over 2N rows: the caller lists every observation twice and marks the component by a NaN
-// in the other coordinate — row (x, NaN): r = (u - x)/w, dr/d(u,v) = (1/w, 0); row (NaN, y): r = (v - y)/w, (0, 1/w) —
-// so 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 (TrivialLoss).  Everything after K1 is generic over rows.
-// A separate kernel (not a template parameter of k_resjac) so that the default model's machine code is untouched.
-template <typename JT, bool WITH_JAC>
-__global__ void __launch_bounds__(RJ_THREADS)
-k_resjac_v2(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
-            const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
-            const double* __restrict__ pts, double inv_w, JT* __restrict__ Jc_B, double* __restrict__ r_B,
-            RowRec<JT>* __restrict__ rec_A, double* __restrict__ cost_part) {
+template <int N>
+__device__ __forceinline__ void tr_fold(double* v, int lane, int off);
+
+template <typename JT, int MODEL, bool WITH_JAC>
+__global__ void __launch_bounds__(RJ_THREADS, WITH_JAC ? 2 : 4)
+k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
+         const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
+         const double* __restrict__ pts4, double scale, JT* __restrict__ Jc_B, RowRec* __restrict__ rec_A,
+         double* __restrict__ cost_part, double* __restrict__ U, double* __restrict__ gc) {
+  extern __shared__ __align__(128) unsigned char rj_stash_raw[];
+  JT* stash = reinterpret_cast<JT*>(rj_stash_raw);
+  constexpr int TILE = RJ_TILE_BYTES / (8 * (int)sizeof(JT));
   __shared__ CamRuns runs;
   __shared__ double T[TAB_STRIDE];
-  __shared__ double sm[32];
+  __shared__ double sm[44 * 8];
   const int c = blockIdx.x;
   if (threadIdx.x == RJ_THREADS - 1) build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
   const int L = runs.load(c, nPB, camtab);  // includes the __syncthreads that publishes T
   double v[1] = {0.0};
+  double acc[44];  // [0,36) upper triangle of U_c, [36,44) g_c
+#pragma unroll
+  for (int k = 0; k < 44; ++k) acc[k] = 0.0;
   int run = 0;
-  for (int l = threadIdx.x; l < L; l += RJ_THREADS) {
-    const size_t j = runs.locate(l, run);
-    const int p = __ldg(pt_B + j);
-    if (p < 0) continue;  // padding row of a run
-    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
-    const double2 o = __ldg(obs_B + j);
-    const Proj pr = project(T, X, Y, Z);
-    double ex, ey;
-    const double r = v2_residual(pr, o.x, o.y, inv_w, ex, ey);
-    v[0] += r * r;
+  for (int base = 0; base < L; base += (WITH_JAC ? TILE : L)) {
+    const int hi = WITH_JAC ? min(L, base + TILE) : L;
+    for (int l = base + threadIdx.x; l < hi; l += RJ_THREADS) {
+      const size_t j = runs.locate(l, run);
+      const int p = __ldg(pt_B + j);
+      if (p < 0) {  // padding row of a run
+        if (WITH_JAC) {
+          const double z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+          strow_cvt<JT>(stash + 8 * (size_t)(l - base), z);
+        }
+        continue;
+      }
+      double X4[4];
+      ld256(pts4 + 4 * (size_t)p, X4);  // one 32 B record {X, Y, Z, -}: ONE divergent request per row instead of three
+      const double X = X4[0], Y = X4[1], Z = X4[2];
+      const double2 o = __ldg(obs_B + j);
+      const Proj pr = project(T, X, Y, Z);
+      double ex, ey;
+      const double r = row_residual<MODEL>(pr, o.x, o.y, scale, ex, ey);
+      v[0] += r * r;
+      if (WITH_JAC) {
+        double a[8], b[3];
+        jac_row(T, pr, X, Y, Z, ex, ey, a, b);
+        store8<JT>(Jc_B + 8 * j, a);
+        st_rec(rec_A + __ldg(posA + j), b, r);
+        strow_cvt<JT>(stash + 8 * (size_t)(l - base), a);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[36 + k] += a[k] * r;
+      }
+    }
     if (WITH_JAC) {
-      double a[8], b[3];
-      jac_row(T, pr, X, Y, Z, ex, ey, a, b);
-      store8<JT>(Jc_B + 8 * j, a);
-      r_B[j] = r;
-      st_rec(rec_A + __ldg(posA + j), b, r);
+      __syncthreads();
+      for (int l = base + threadIdx.x; l < hi; l += RJ_THREADS) {
+        JT ar[8];
+        ldrow_shared(stash + 8 * (size_t)(l - base), ar);
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = (double)ar[k];
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+          for (int l2 = k; l2 < 8; ++l2) acc[t++] += a[k] * a[l2];
+      }
+      __syncthreads();
     }
   }
   block_sum<1>(v, sm);
   if (threadIdx.x == 0) cost_part[c] = v[0];
+  if (!WITH_JAC) return;
+  __syncthreads();
+  // transpose-reduce inside the warp (47 shuffles instead of 44 x 5), then an ordered cross-warp sum (as k_cam_blocks)
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = RJ_THREADS >> 5;
+  double hi16[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) hi16[k] = k < 12 ? acc[32 + k] : 0.0;
+  tr_fold<32>(acc, lane, 16); tr_fold<16>(acc, lane, 8); tr_fold<8>(acc, lane, 4); tr_fold<4>(acc, lane, 2); tr_fold<2>(acc, lane, 1);
+  tr_fold<16>(hi16, lane, 16); tr_fold<8>(hi16, lane, 8); tr_fold<4>(hi16, lane, 4); tr_fold<2>(hi16, lane, 2);
+  hi16[0] += __shfl_xor_sync(0xffffffffu, hi16[0], 1);
+  sm[wid * 44 + lane] = acc[0];
+  if (!(lane & 1) && lane < 24) sm[wid * 44 + 32 + (lane >> 1)] = hi16[0];
+  __syncthreads();
+  if (threadIdx.x < 44) {
+    double s = 0.0;
+    for (int w = 0; w < nw; ++w) s += sm[w * 44 + threadIdx.x];  // fixed order
+    const int t = threadIdx.x;
+    if (t >= 36) {
+      gc[8 * (size_t)c + (t - 36)] = s;
+    } else {
+      int k = 0, rem = t;
+      while (rem >= 8 - k) { rem -= 8 - k; ++k; }
+      const int l = k + rem;
+      U[64 * (size_t)c + 8 * k + l] = s;
+      U[64 * (size_t)c + 8 * l + k] = s;
+    }
+  }
 }
 
 // ---------------------------------------------------------------- reprojection-error evaluator
@@ -221,12 +258,12 @@ k_resjac_v2(int nPB, const int32_t* __restrict__ camtab, const double* __restric
 // ceres::CauchyLoss(a) = b log(1 + s/b) or ceres::SoftLOneLoss(a) = 2b (sqrt(1 + s/b) - 1), b = a^2
 // (colmap/src/optim/bundle_adjustment.cc:53-68); Ceres' cost is half the sum.  Same traversal as the trial-cost kernel (one CTA per camera over its B runs,
 // camera table in shared memory, point gather inside the block window); e goes to the CALLER's row
-// (order_ps[posA[j]], an 8 B scatter) and the ordered per-camera sum to cam_sum[c].  20 B read + 8 B written per row.
+// (order_B[j], an 8 B scatter) and the ordered per-camera sum to cam_sum[c].  24 B read + 8 B written per row.
 template <int LOSS>
 __global__ void __launch_bounds__(RJ_THREADS)
 k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
-             const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
-             const int32_t* __restrict__ order_ps, const double* __restrict__ pts, double b_scale, double* __restrict__ err_rows,
+             const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B,
+             const int32_t* __restrict__ order_B, const double* __restrict__ pts4, double b_scale, double* __restrict__ err_rows,
              double* __restrict__ cam_sum) {
   __shared__ CamRuns runs;
   __shared__ double T[TAB_STRIDE];
@@ -240,13 +277,15 @@ k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restri
     const size_t j = runs.locate(l, run);
     const int p = __ldg(pt_B + j);
     if (p < 0) continue;  // padding row of a run
-    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
+    double X4[4];
+    ld256(pts4 + 4 * (size_t)p, X4);  // one 32 B record {X, Y, Z, -}: ONE divergent request per row instead of three
+    const double X = X4[0], Y = X4[1], Z = X4[2];
     const double2 o = __ldg(obs_B + j);
     const Proj pr = project(T, X, Y, Z);
     const double dx = pr.u - o.x, dy = pr.v - o.y;
     const double e = reproj_loss<LOSS>(dx, dy, b_scale);
     v[0] += e;
-    if (err_rows) err_rows[__ldg(order_ps + __ldg(posA + j))] = e;
+    if (err_rows) err_rows[__ldg(order_B + j)] = e;  // order_B: caller's row of every B position (built once per plan)
   }
   block_sum<1>(v, sm);
   if (threadIdx.x == 0 && cam_sum) cam_sum[c] = v[0];
@@ -258,7 +297,7 @@ k_reproj_err(int nPB, const int32_t* __restrict__ camtab, const double* __restri
 // part[2*block+0] = sum |g_p|^2, part[2*block+1] = max diag V.
 template <typename JT>
 __global__ void __launch_bounds__(256)
-k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const RowRec<JT>* __restrict__ rec_A,
+k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const RowRec* __restrict__ rec_A,
                JT* __restrict__ Jp_ps, double* __restrict__ V, double* __restrict__ gp, double* __restrict__ part) {
   __shared__ double sm[32];
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -279,8 +318,10 @@ k_point_blocks(int P, size_t N, const int32_t* __restrict__ pt_ptr, const RowRec
         if (i0 + u >= e) break;
 #pragma unroll
         for (int k = 0; k < 3; ++k) jput<JT>(Jp_ps, N, k, (size_t)(i0 + u), b[u][k]);
-        v[0] += b[u][0] * b[u][0]; v[1] += b[u][0] * b[u][1]; v[2] += b[u][0] * b[u][2];
-        v[3] += b[u][1] * b[u][1]; v[4] += b[u][1] * b[u][2]; v[5] += b[u][2] * b[u][2];
+        // V_p from the row as STORED (rounded to JT): the operator is exactly J~^T J~; g_p from the unrounded row
+        const double q0 = (double)(JT)b[u][0], q1 = (double)(JT)b[u][1], q2 = (double)(JT)b[u][2];
+        v[0] += q0 * q0; v[1] += q0 * q1; v[2] += q0 * q2;
+        v[3] += q1 * q1; v[4] += q1 * q2; v[5] += q2 * q2;
         g[0] += b[u][0] * r[u]; g[1] += b[u][1] * r[u]; g[2] += b[u][2] * r[u];
       }
     }
@@ -311,7 +352,7 @@ __device__ __forceinline__ void tr_fold(double* v, int lane, int off) {
   }
 }
 
-// One CTA per camera (64..256 threads, by the average camera size) streams its B-order runs.  If beta_B != nullptr the rows are weighted:
+// One CTA per camera (64..256 threads, by the average camera size) streams its B-order runs.  If wb_B != nullptr the rows are weighted by its {w_i, beta_i} records:
 // out = -sum beta_i a a^T and -sum a w_i (the Schur corrections of the block-Jacobi blocks / reduced rhs);
 // otherwise U_c = sum a a^T and g_c = sum a r.
 // (An fp64 tensor-core version — one mma.sync.m8n8k4.f64 per 4 rows, the SYRK mapped 1:1 onto the DMMA tile — was
@@ -320,7 +361,7 @@ __device__ __forceinline__ void tr_fold(double* v, int lane, int off) {
 template <typename JT>
 __global__ void __launch_bounds__(256)
 k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__ Jc_B,
-             const double* __restrict__ s_B, const double* __restrict__ w_B, const double* __restrict__ beta_B,
+             const double* __restrict__ s_B, const double2* __restrict__ wb_B,
              double* __restrict__ U, double* __restrict__ gc) {
   __shared__ double sm[44 * 8];
   __shared__ CamRuns runs;
@@ -335,9 +376,10 @@ k_cam_blocks(int nPB, const int32_t* __restrict__ camtab, const JT* __restrict__
     double a[8];
     load8<JT>(Jc_B + 8 * j, a);
     double s, wgt;
-    if (beta_B) {
-      s = -__ldg(w_B + j);
-      wgt = -__ldg(beta_B + j);
+    if (wb_B) {
+      const double2 wb = __ldg(wb_B + j);
+      s = -wb.x;
+      wgt = -wb.y;
     } else {
       s = __ldg(s_B + j);
       wgt = 1.0;
@@ -412,8 +454,7 @@ template <typename JT>
 __global__ void __launch_bounds__(256)
 k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_t* __restrict__ pt_ptr,
                 const int32_t* __restrict__ posB, const JT* __restrict__ Jp_ps, const double* __restrict__ V,
-                const double* __restrict__ gp, double* __restrict__ Vinv, double* __restrict__ w_B,
-                double* __restrict__ beta_B) {
+                const double* __restrict__ gp, double* __restrict__ Vinv, double2* __restrict__ wb_B) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const double mu = *mu_ptr;
@@ -422,7 +463,7 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
   for (int k = 0; k < 6; ++k) v[k] = V[6 * (size_t)p + k];
   inv3_sym(v, mu, vi);
 #pragma unroll
-  for (int k = 0; k < 6; ++k) Vinv[6 * (size_t)p + k] = vi[k];
+  for (int k = 0; k < 6; ++k) Vinv[(size_t)k * P + p] = vi[k];  // SoA: the point-side kernels read it one lane per point
   const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
   const double z0 = vi[0] * g0 + vi[1] * g1 + vi[2] * g2;
   const double z1 = vi[1] * g0 + vi[3] * g1 + vi[4] * g2;
@@ -443,11 +484,11 @@ k_point_prepare(int P, size_t N, const double* __restrict__ mu_ptr, const int32_
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (j[u] < 0) continue;
-      w_B[j[u]] = b[u][0] * z0 + b[u][1] * z1 + b[u][2] * z2;
+      const double wv = b[u][0] * z0 + b[u][1] * z1 + b[u][2] * z2;
       const double t0 = vi[0] * b[u][0] + vi[1] * b[u][1] + vi[2] * b[u][2];
       const double t1 = vi[1] * b[u][0] + vi[3] * b[u][1] + vi[4] * b[u][2];
       const double t2 = vi[2] * b[u][0] + vi[4] * b[u][1] + vi[5] * b[u][2];
-      beta_B[j[u]] = b[u][0] * t0 + b[u][1] * t1 + b[u][2] * t2;
+      wb_B[j[u]] = make_double2(wv, b[u][0] * t0 + b[u][1] * t1 + b[u][2] * t2);  // ONE 16 B scatter per row
     }
   }
 }

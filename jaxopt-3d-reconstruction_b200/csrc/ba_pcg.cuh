@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(PS_T)
 k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxiter, SolverState* __restrict__ st,
      const double* __restrict__ cpart, const int32_t* __restrict__ chunk_row, const int32_t* __restrict__ chunk_pt,
      const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ pt_A, const int32_t* __restrict__ posB,
-     const JT* __restrict__ Jp_A, const double* __restrict__ Vinv, const double* __restrict__ sig,
+     const JT* __restrict__ Jp_A, const double* __restrict__ Vinv /*SoA: [k * Pst + p]*/, size_t Pst, const double* __restrict__ sig,
      double* __restrict__ omg, const double* __restrict__ gp, double* __restrict__ vp, double* __restrict__ part) {
   constexpr int CAP = PS_T * PS_RPT;
   __shared__ double sb[3][CAP];
@@ -397,7 +397,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
       beg = __ldg(pt_ptr + p) - r0;
       end = __ldg(pt_ptr + p + 1) - r0;
 #pragma unroll
-      for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
+      for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + (size_t)k * Pst + p);
       if (BACKSUB) { g0 = gp[3 * (size_t)p]; g1 = gp[3 * (size_t)p + 1]; g2 = gp[3 * (size_t)p + 2]; }
     }
 #pragma unroll
@@ -460,7 +460,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     double t0 = sz[0][0], t1 = sz[1][0], t2 = sz[2][0];
     double vi[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + 6 * (size_t)p + k);
+    for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + (size_t)k * Pst + p);
     if (BACKSUB) {
       if (tid == 0) {
         const double g0 = gp[3 * (size_t)p], g1 = gp[3 * (size_t)p + 1], g2 = gp[3 * (size_t)p + 2];
@@ -544,10 +544,11 @@ __global__ void k_trial_cams(int C, const double* __restrict__ cam8, const doubl
   part[2 * c] = vg;
   part[2 * c + 1] = vv;
 }
-__global__ void k_trial_pts(int64_t n3, const double* __restrict__ pts, const double* __restrict__ vp,
-                            double* __restrict__ pts_trial) {
+// points are 32 B records {X, Y, Z, 0}; vp is P x 3
+__global__ void k_trial_pts(int64_t n4, const double* __restrict__ pts4, const double* __restrict__ vp,
+                            double* __restrict__ pts4_trial) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n3) pts_trial[i] = pts[i] - vp[i];
+  if (i < n4) pts4_trial[i] = (i & 3) == 3 ? 0.0 : pts4[i] - vp[3 * (i >> 2) + (i & 3)];
 }
 
 // generic ordered reduction: out[k] = sum_i in[i*stride + k], k < nout (single CTA)

@@ -386,3 +386,74 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
         if not (it < maxiter and err > tol):
             break
     return LMResult(x, it, loss, err, mu, nu, tr)
+
+
+def lm_solve_dense_c(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6, maxiter=100,
+                     damping_parameter=1e-6, verbose=False) -> LMResult:
+    """`lm_solve(solver="exact")` for shapes scipy.sparse cannot reach (Venice-1778: 5 M rows): the same LM state machine,
+    rows from the C restatement (`ba_c_eval`), the reduced camera system formed densely in C (`ba_c_schur_dense`,
+    S is 14 224^2 fp64 = 1.6 GB at Venice) and factored by LAPACK Cholesky, points back-substituted in NumPy.
+    Same mathematics as `_solve_schur_exact`; `tests/test_oracle_cpu.py` holds the two equal on the small shapes."""
+    from . import c_binding as cb
+    cam_idx = np.ascontiguousarray(cam_idx, dtype=np.int32)
+    pt_idx = np.ascontiguousarray(pt_idx, dtype=np.int32)
+    obs = np.ascontiguousarray(obs, dtype=np.float64)
+    k3 = np.ascontiguousarray(cx_cy_skew, dtype=np.float64)
+    w2 = float(avg_cam_width) ** 2
+    x = np.array(x0, dtype=np.float64)
+    tr = LMTrace()
+
+    def seg(idx, w, n):
+        return np.stack([np.bincount(idx, weights=w[:, k], minlength=n) for k in range(w.shape[1])], axis=1)
+
+    def evaluate(xx):
+        r, a, b, cost = cb.ba_eval(xx, C, P, cam_idx, pt_idx, obs, k3, w2, want_jac=True)
+        gc = seg(cam_idx, a * r[:, None], C)
+        gp = seg(pt_idx, b * r[:, None], P)
+        tr.n_eval_jac += 1
+        return r, a, b, gc, gp
+
+    def pack(vc8, vp):
+        return np.concatenate([vc8[:, :6].reshape(-1), vc8[:, 6:].reshape(-1), vp.reshape(-1)])
+
+    r, a, b, gc, gp = evaluate(x)
+    maxdiag = max(seg(cam_idx, a * a, C).max(), seg(pt_idx, b * b, P).max())
+    mu, nu = damping_parameter * float(maxdiag), 2.0
+    loss = 0.5 * float(r @ r)
+    err = float(np.sqrt((gc ** 2).sum() + (gp ** 2).sum()))
+    it = 0
+    tr.loss.append(loss); tr.grad_l2.append(err); tr.mu.append(mu)
+    while True:
+        S, rhs, Vinv, gp_c = cb.schur_dense(C, P, cam_idx, pt_idx, a, b, r, mu)
+        cho = scipy.linalg.cho_factor(S, lower=True, overwrite_a=True, check_finite=False)
+        vc = scipy.linalg.cho_solve(cho, rhs, check_finite=False).reshape(C, 8)
+        del S, cho
+        sig = np.einsum("nk,nk->n", a, vc[cam_idx])
+        t = seg(pt_idx, b * sig[:, None], P)
+        vp = np.einsum("pij,pj->pi", Vinv, gp_c - t)
+        g = pack(gc, gp)
+        v = pack(vc, vp)
+        x_next = x - v
+        r_next, _, _, _ = cb.ba_eval(x_next, C, P, cam_idx, pt_idx, obs, k3, w2, want_jac=False)
+        tr.n_eval_res += 1
+        loss_next = 0.5 * float(r_next @ r_next)
+        rho = (loss - loss_next) / (0.5 * float(mu * (v @ v) + v @ g))  # delta = -v
+        ok = bool(rho > 0.0)
+        if ok:
+            x = x_next
+            r, a, b, gc, gp = evaluate(x)
+            mu = mu * max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)
+            nu = 2.0
+        else:
+            mu = mu * nu
+            nu = 2.0 * nu
+        it += 1
+        loss = 0.5 * float(r @ r)
+        err = float(np.sqrt((gc ** 2).sum() + (gp ** 2).sum()))
+        tr.loss.append(loss); tr.grad_l2.append(err); tr.mu.append(mu); tr.rho.append(rho); tr.accepted.append(ok)
+        tr.inner_iters.append(0)
+        if verbose:
+            print(f"[oracle dense] it {it} loss {loss:.12e} |g| {err:.3e} mu {mu:.3e} rho {rho:.3e} acc {ok}", flush=True)
+        if not (it < maxiter and err > tol):
+            break
+    return LMResult(x, it, loss, err, mu, nu, tr)

@@ -42,6 +42,14 @@ int ba_c_num_threads(void) {
 #endif
 }
 
+void ba_c_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 static void build_lists(Prob* q) {
   q->pt_ptr = (int64_t*)calloc((size_t)q->P + 1, sizeof(int64_t));
   q->cam_ptr = (int64_t*)calloc((size_t)q->C + 1, sizeof(int64_t));
@@ -273,4 +281,85 @@ int ba_c_lm(int C, int P, int64_t N, double* x, const int32_t* cam, const int32_
   free(q.a); free(q.b); free(q.r); free(q.pt_ptr); free(q.cam_ptr); free(q.pt_rows); free(q.cam_rows);
   free(g); free(v); free(xn); free(ws); free(srow); free(rsave);
   return it;
+}
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Exact inner solve at Venice scale: the reduced camera system of SURVEY.md App. A.6 formed DENSELY,
+ *   S = blockdiag(U_c + mu I) - W (V + mu I)^-1 W^T   (8C x 8C, row-major, full symmetric; S must arrive zeroed)
+ *   rhs = g_c - W (V + mu I)^-1 g_p,
+ * from the Jacobian rows a (N x 8), b (N x 3) and residuals r of ba_c_eval (caller's row order).  Also returns
+ * Vinv (P x 9, full 3x3) and g_p (P x 3) for the back-substitution.  The caller factors S with LAPACK (Cholesky) —
+ * arithmetic-equivalent to a direct solve of (J^T J + mu I) v = g, the same mathematics as ba_oracle._solve_schur_exact
+ * (which goes through scipy.sparse and cannot reach 5 M rows).  Camera-major 8-blocks: index 8c+k, k = [w, t, fx, fy].
+ * Threads own the block rows c_i % T == tid, so no two threads ever write the same entry (no atomics, fixed order). */
+int ba_c_schur_dense(int C, int P, int64_t N, const int32_t* cam, const int32_t* pt, const double* a, const double* b,
+                     const double* r, double mu, double* S, double* rhs, double* Vinv, double* gp) {
+  Prob q = {C, P, N, cam, pt, 0, 0, 0.0, 0, 0, 0, 0, (double*)a, (double*)b, (double*)r};
+  build_lists(&q);
+  const size_t n = 8 * (size_t)C;
+  int bad = 0;
+#pragma omp parallel for schedule(static, 1024) reduction(| : bad)
+  for (int p = 0; p < P; ++p) {
+    double V[9] = {mu, 0, 0, 0, mu, 0, 0, 0, mu}, g[3] = {0, 0, 0};
+    for (int64_t j = q.pt_ptr[p]; j < q.pt_ptr[p + 1]; ++j) {
+      const int64_t i = q.pt_rows[j];
+      for (int k = 0; k < 3; ++k) {
+        g[k] += b[3 * i + k] * r[i];
+        for (int l = 0; l < 3; ++l) V[3 * k + l] += b[3 * i + k] * b[3 * i + l];
+      }
+    }
+    const double c00 = V[4] * V[8] - V[5] * V[7], c01 = V[5] * V[6] - V[3] * V[8], c02 = V[3] * V[7] - V[4] * V[6];
+    const double det = V[0] * c00 + V[1] * c01 + V[2] * c02;
+    if (!(det > 0.0)) bad = 1;
+    const double id = 1.0 / det;
+    double* I = Vinv + 9 * (size_t)p;
+    I[0] = c00 * id; I[1] = (V[2] * V[7] - V[1] * V[8]) * id; I[2] = (V[1] * V[5] - V[2] * V[4]) * id;
+    I[3] = c01 * id; I[4] = (V[0] * V[8] - V[2] * V[6]) * id; I[5] = (V[2] * V[3] - V[0] * V[5]) * id;
+    I[6] = c02 * id; I[7] = (V[1] * V[6] - V[0] * V[7]) * id; I[8] = (V[0] * V[4] - V[1] * V[3]) * id;
+    for (int k = 0; k < 3; ++k) gp[3 * (size_t)p + k] = g[k];
+  }
+  memset(rhs, 0, n * sizeof(double));
+#pragma omp parallel
+  {
+#ifdef _OPENMP
+    const int T = omp_get_num_threads(), tid = omp_get_thread_num();
+#else
+    const int T = 1, tid = 0;
+#endif
+    for (int c = tid; c < C; c += T)
+      for (int k = 0; k < 8; ++k) S[(8 * (size_t)c + k) * n + 8 * (size_t)c + k] += mu;
+    for (int p = 0; p < P; ++p) {
+      const double* I = Vinv + 9 * (size_t)p;
+      const double* g = gp + 3 * (size_t)p;
+      for (int64_t ji = q.pt_ptr[p]; ji < q.pt_ptr[p + 1]; ++ji) {
+        const int64_t i = q.pt_rows[ji];
+        const int ci = cam[i];
+        if (ci % T != tid) continue;
+        const double *ai = a + 8 * i, *bi = b + 3 * i;
+        double* Srow = S + 8 * (size_t)ci * n;
+        /* U_c and g_c */
+        for (int k = 0; k < 8; ++k) {
+          rhs[8 * (size_t)ci + k] += ai[k] * r[i];
+          for (int l = 0; l < 8; ++l) Srow[(size_t)k * n + 8 * (size_t)ci + l] += ai[k] * ai[l];
+        }
+        const double t0 = I[0] * bi[0] + I[3] * bi[1] + I[6] * bi[2]; /* Vinv symmetric: t = Vinv b_i */
+        const double t1 = I[1] * bi[0] + I[4] * bi[1] + I[7] * bi[2];
+        const double t2 = I[2] * bi[0] + I[5] * bi[1] + I[8] * bi[2];
+        const double wg = t0 * g[0] + t1 * g[1] + t2 * g[2];
+        for (int k = 0; k < 8; ++k) rhs[8 * (size_t)ci + k] -= ai[k] * wg;
+        for (int64_t jj = q.pt_ptr[p]; jj < q.pt_ptr[p + 1]; ++jj) {
+          const int64_t j = q.pt_rows[jj];
+          const double* aj = a + 8 * j;
+          const double beta = t0 * b[3 * j] + t1 * b[3 * j + 1] + t2 * b[3 * j + 2];
+          double* Sb = Srow + 8 * (size_t)cam[j];
+          for (int k = 0; k < 8; ++k) {
+            const double ab = ai[k] * beta;
+            for (int l = 0; l < 8; ++l) Sb[(size_t)k * n + l] -= ab * aj[l];
+          }
+        }
+      }
+    }
+  }
+  free(q.pt_ptr); free(q.cam_ptr); free(q.pt_rows); free(q.cam_rows);
+  return bad;
 }

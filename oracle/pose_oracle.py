@@ -75,6 +75,7 @@ class PoseLMResult:
     loss: np.ndarray        # (B,)
     grad_l2: np.ndarray     # (B,)
     damping_factor: np.ndarray
+    grad_history: np.ndarray = None  # (B, iterations+1): ||g|| of every lane after each of ITS updates (NaN once the lane has stopped)
 
 
 def _chol_solve(A, b):
@@ -105,6 +106,7 @@ def pose_lm_batched(params0, points, obs, cx_cy_skew, mask, avg_cam_width, loss=
     it = np.zeros(B, dtype=np.int64)
     active = np.ones(B, dtype=bool)        # first update unconditional
     eye = np.eye(8)
+    hist = [err.copy()]
     while active.any():
         ia = np.flatnonzero(active)
         v = _chol_solve(JtJ[ia] + mu[ia, None, None] * eye, g[ia])
@@ -127,5 +129,8 @@ def pose_lm_batched(params0, points, obs, cx_cy_skew, mask, avg_cam_width, loss=
         nu[rej] = 2.0 * nu[rej]
         it[ia] += 1
         err[ia] = np.linalg.norm(g[ia], axis=1)
+        h = np.full(B, np.nan)
+        h[ia] = err[ia]
+        hist.append(h)
         active[ia] = (it[ia] < maxiter) & (err[ia] > tol)
-    return PoseLMResult(x, it, cur, err, mu)
+    return PoseLMResult(x, it, cur, err, mu, np.stack(hist, axis=1))

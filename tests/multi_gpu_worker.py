@@ -39,7 +39,7 @@ def solve_one(shape, dev, rank, world):
         deg = np.bincount(sc.pt_idx, minlength=sc.P)
         drop = (sc.cam_idx == 0) & (sc.pt_idx >= sc.P // 2) & (deg[sc.pt_idx] > 2)
         sc.cam_idx, sc.pt_idx, sc.obs = sc.cam_idx[~drop], sc.pt_idx[~drop], sc.obs[~drop]
-    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device=dev)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device=dev, distributed=True)
     assert ba.world == world
     x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
     params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)

@@ -99,19 +99,27 @@ def _gloo_worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     sc = b200ba.synth.make_ba_scene("small", seed=0)
-    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device="cpu")
+    # multi-rank mode is opt-in: an initialised process group alone must NOT switch it on
+    assert b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device="cpu").world == 1
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, device="cpu", distributed=True)
     assert ba.world == world and ba.rank == rank
     b = b200ba.shard_points(sc.pt_idx, sc.P, world)
+    np.testing.assert_array_equal(b, b200ba.shard_points(torch.from_numpy(sc.pt_idx), sc.P, world))  # tensor path = host path
     keep = (sc.pt_idx >= b[rank]) & (sc.pt_idx < b[rank + 1])
+    ci, pi, ob, (lo, hi), b2 = b200ba.shard_rows(sc.cam_idx, sc.pt_idx, sc.obs, sc.P, world, rank)
+    assert (lo, hi) == (b[rank], b[rank + 1]) and np.array_equal(b2, b)
+    assert np.array_equal(ci, sc.cam_idx[keep]) and np.array_equal(pi + lo, sc.pt_idx[keep]) and np.array_equal(ob, sc.obs[keep])
     # the sum of per-rank partial camera reductions equals the global one (what NCCL sums on GPU)
     part = torch.zeros(sc.C, dtype=torch.float64)
     part.index_add_(0, torch.from_numpy(sc.cam_idx[keep].astype(np.int64)), torch.from_numpy(sc.obs[keep, 0]))
     dist.all_reduce(part)
     full = torch.zeros(sc.C, dtype=torch.float64)
     full.index_add_(0, torch.from_numpy(sc.cam_idx.astype(np.int64)), torch.from_numpy(sc.obs[:, 0]))
-    sizes = [None] * world
-    dist.all_gather_object(sizes, int(b[rank + 1] - b[rank]))
-    q.put((rank, bool(torch.allclose(part, full, rtol=1e-12)), sum(sizes) == sc.P))
+    # the full point array is assembled by one all-reduce of zero-filled buffers holding disjoint ranges (api._solve)
+    pts = torch.zeros(sc.P, 3, dtype=torch.float64)
+    pts[lo:hi] = torch.from_numpy(sc.points0[lo:hi])
+    dist.all_reduce(pts)
+    q.put((rank, bool(torch.allclose(part, full, rtol=1e-12)), bool(torch.equal(pts, torch.from_numpy(sc.points0)))))
     dist.destroy_process_group()
 
 

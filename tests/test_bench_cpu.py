@@ -50,10 +50,26 @@ def test_bytes_models_are_the_design_formulas():
     sys.path.insert(0, ROOT)
     import bench
     C, P, N = 1778, 993923, 5001946
-    m = bench.bytes_models(C, P, N, 4)
-    assert m["resjac"] == 96 * N + 24 * P + 88 * C          # N·(16+4+4+8·jsz+8+32) + 24·P + 88·C
-    assert m["mv_pt"] == 32 * N + 52 * P                    # N·(3·jsz + 4 + 8 + 8) + 52·P  (+4 pt index)
+    m = bench.bytes_models(C, P, N, 4, tiled=False, fused=False)
+    assert m["resjac"] == 96 * N + 32 * P + 88 * C          # N·(16+4+4+8·jsz+8+32) + 32·P + 88·C
+    assert m["mv_pt"] == 32 * N + 52 * P                    # chunk kernel: N·(3·jsz + 4 + 8 + 8) + 52·P
     assert m["mv_cam"] == 48 * N + (2 * 576 + 1024 + 160) * C
-    assert m["cost"] == 20 * N + 24 * P + 88 * C
-    m8 = bench.bytes_models(C, P, N, 8)
+    assert m["cost"] == 20 * N + 32 * P + 88 * C
+    assert m["eval"] == 32 * N + 32 * P + 96 * C
+    mt = bench.bytes_models(C, P, N, 4, tiled=True, fused=True)
+    assert mt["mv_pt"] == 34 * N + 52 * P                   # tiled kernel: N·(3·jsz + 2 + 4 + 8 + 8) + 52·P
+    assert mt["resjac"] == 88 * N + 32 * P + (88 + 576) * C  # fused: no r_B array, U_c / g_c written by the same launch
+    m8 = bench.bytes_models(C, P, N, 8, tiled=False, fused=False)
     assert m8["mv_cam"] - m["mv_cam"] == 32 * N and m8["mv_pt"] - m["mv_pt"] == 12 * N
+
+
+def test_both_arms_share_one_config_dict():
+    """The driver compares `config` of the two arms byte for byte."""
+    sys.path.insert(0, ROOT)
+    import argparse
+
+    import bench
+
+    class S:
+        C, P, N = 3, 8, 20
+    assert bench.workload_config(argparse.Namespace(workload="tiny"), S) == {"workload": "tiny", "C": 3, "P": 8, "N": 20}

@@ -6,6 +6,22 @@ import b200ba
 from oracle import pose_oracle as po
 
 pytestmark = pytest.mark.gpu
+TOL = 1e-7  # pose_optimization.py:64
+
+
+def _check(st, params, ref, min_same):
+    """Per lane: same iteration count, loss and parameters.  The stop test is a hard threshold on ||g||, which shrinks
+    ~8x per iteration: a lane may legitimately differ by ONE iteration only when the oracle's ||g|| at the earlier stop
+    lies within 1e-3 relative of tol — asserted lane by lane, nothing is silently dropped."""
+    same = st.iter_num == ref.iter_num
+    for lane in np.flatnonzero(~same):
+        k = int(min(st.iter_num[lane], ref.iter_num[lane]))
+        g_at_k = ref.grad_history[lane, k]
+        assert abs(int(st.iter_num[lane]) - int(ref.iter_num[lane])) == 1, (lane, st.iter_num[lane], ref.iter_num[lane])
+        assert abs(g_at_k - TOL) <= 1e-3 * TOL, (lane, st.iter_num[lane], ref.iter_num[lane], g_at_k)
+    assert same.mean() >= min_same, (st.iter_num, ref.iter_num)
+    np.testing.assert_allclose(st.loss[same], ref.loss[same], rtol=1e-6, atol=1e-30)
+    np.testing.assert_allclose(params[same], ref.params[same], rtol=1e-6, atol=1e-9)
 
 
 @pytest.mark.parametrize("loss,noise,ragged", [(1, 5e-3, False), (1, 5e-2, False), (0, 5e-2, False), (1, 5e-3, True)])
@@ -16,8 +32,15 @@ def test_pose_batch_vs_oracle(loss, noise, ragged):
     x0, k3 = opt.prepare_params(pb.poses0, pb.intrinsics0)
     params, st = opt.optimize(x0, pb.points, pb.obs, k3, pb.mask)
     ref = po.pose_lm_batched(x0, pb.points, pb.obs, k3, pb.mask, pb.avg_cam_width, loss=loss)
-    same = st.iter_num == ref.iter_num
-    # a pose whose ||g|| lands within 1e-3 rel of tol may legitimately differ by one iteration
-    assert same.mean() >= 0.95, (st.iter_num, ref.iter_num)
-    np.testing.assert_allclose(st.loss[same], ref.loss[same], rtol=1e-6, atol=1e-30)
-    np.testing.assert_allclose(params[same], ref.params[same], rtol=1e-6, atol=1e-9)
+    _check(st, params, ref, 0.95)
+
+
+def test_pose_full_config_4096x512_vs_oracle():
+    """BASELINE.json configs[1] at full size (4 096 poses x 512 correspondences, Cauchy, pose noise 5e-3): every lane against
+    the NumPy oracle (~1 min of host time); also exercises the chunked host->device pipeline of `optimize`."""
+    pb = b200ba.synth.make_pose_batch(B=4096, npts=512, seed=0, rot_noise=5e-3, pos_noise=5e-3)
+    opt = b200ba.B200PoseOptimizer(pb.avg_cam_width)
+    x0, k3 = opt.prepare_params(pb.poses0, pb.intrinsics0)
+    params, st = opt.optimize(x0, pb.points, pb.obs, k3, pb.mask)
+    ref = po.pose_lm_batched(x0, pb.points, pb.obs, k3, pb.mask, pb.avg_cam_width)
+    _check(st, params, ref, 0.99)
