@@ -228,7 +228,7 @@ def run_reference(args):
 
 # ---------------------------------------------------------------------------- our arm
 PC_NAMES = ["resjac", "pt_blocks", "cam_blocks", "pt_prepare", "cam_schur", "cam_finish", "mv_pt", "mv_cam",
-            "pcg_vec", "backsub", "cost", "other", "eval"]
+            "pcg_vec", "backsub", "cost", "other", "eval", "dn_assemble", "dn_cholesky", "dn_solve"]
 
 
 def golden_parity(workload, seed, solves, rms_final):
@@ -456,16 +456,25 @@ def run_b200(args):
     if not args.no_extras:
         sec = {}
         if world == 1:
-            for wl in ("trafalgar257", "ladybug49", "small"):
-                try:
-                    r = ba_workload(D, b200ba, args, wl, 20, 3, want_e2e=False)
-                    its = sum(s["iters"] for s in r["solves"])
-                    sec[wl] = {"lm_iterations_per_s": r["value"], "us_per_lm_iteration": 1e3 * r["ms"] / 20,
-                               "launches_per_lm_iteration": r["launches"] / max(its, 1), "plan": r.get("plan_info"),
-                               "pcg_iters_per_lm_iteration": sum(s["pcg_iters"] for s in r["solves"]) / max(its, 1),
-                               "first_solve": {k: v for k, v in r["solves"][0].items() if k != "loss_trajectory"}}
-                except Exception as exc:  # noqa: BLE001
-                    sec[wl] = {"error": repr(exc)}
+            # small scenes: launch-latency bound, not HBM bound — us per LM iteration with the dense reduced-camera path
+            # (DMMA Cholesky, the default for 8C <= 2560) next to the PCG path forced onto the same problem
+            for wl in ("trafalgar257", "ladybug49", "ref15x400"):
+                ent = {}
+                for mode, env in (("dense", "1"), ("pcg", "0")):
+                    try:
+                        os.environ["B200BA_DENSE"] = env
+                        r = ba_workload(D, b200ba, args, wl, 20, 3, want_e2e=False)
+                        its = sum(s["iters"] for s in r["solves"])
+                        ent[mode] = {"lm_iterations_per_s": r["value"], "us_per_lm_iteration": 1e3 * r["ms"] / 20,
+                                     "launches_per_lm_iteration": r["launches"] / max(its, 1), "plan": r.get("plan_info"),
+                                     "pcg_iters_per_lm_iteration": sum(s["pcg_iters"] for s in r["solves"]) / max(its, 1),
+                                     "first_solve": {k: v for k, v in r["solves"][0].items() if k != "loss_trajectory"},
+                                     "kernels_us": {k: v["avg_us"] for k, v in r["kernels"].items() if k.startswith("dn_")}}
+                    except Exception as exc:  # noqa: BLE001
+                        ent[mode] = {"error": repr(exc)}
+                    finally:
+                        os.environ.pop("B200BA_DENSE", None)
+                sec[wl] = ent
         try:
             r = ba_workload(D, b200ba, args, "final13682", 4, 3, want_e2e=False, maxiter=4)
             sec["final13682"] = {"lm_iterations_per_s": r["value"], "ms_per_lm_iteration": r["ms"] / 4, "n_gpus": world,

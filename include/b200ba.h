@@ -20,7 +20,8 @@ typedef struct b200ba_plan b200ba_plan;
 enum { B200BA_OK = 0, B200BA_EINVAL = 1, B200BA_ECUDA = 2, B200BA_ENCCL = 3 };
 /* per-solve status bits (b200ba_lm_result.status / pose status[]) */
 enum { B200BA_ST_CONVERGED = 0, B200BA_ST_MAXITER = 1, B200BA_ST_NAN = 2, B200BA_ST_PCG_MAXITER = 4,
-       B200BA_ST_XCHG_TIMEOUT = 8 /* multi-rank: a peer's partial sums never arrived; the solve returns B200BA_ENCCL */ };
+       B200BA_ST_XCHG_TIMEOUT = 8 /* multi-rank: a peer's partial sums never arrived; the solve returns B200BA_ENCCL */,
+       B200BA_ST_DENSE_NOT_SPD = 16 /* dense reduced-camera Cholesky met a non-positive pivot (NaN step, like LAPACK through jax) */ };
 enum { B200BA_LOSS_L2 = 0, B200BA_LOSS_CAUCHY = 1 }; /* loss.py:7-14 */
 
 const char* b200ba_last_error(void);
@@ -143,7 +144,8 @@ int b200ba_plan_info(b200ba_plan* plan, int* out /*[8]*/);
 /* ---- measurement: per-kernel-class CUDA-event timing on the launching stream.  Classes:
  * 0 residual+Jacobian (K1), 1 point blocks, 2 camera blocks, 3 point inverses, 4 Schur camera
  * corrections, 5 block-Jacobi inverses, 6 matvec point pass, 7 matvec camera pass, 8 PCG vector
- * kernels, 9 back-substitution, 10 trial cost, 11 other, 12 reprojection-error evaluator. */
+ * kernels, 9 back-substitution, 10 trial cost, 11 other, 12 reprojection-error evaluator, 13 dense S assembly, 14 dense Cholesky,
+ * 15 dense triangular solves. */
 int b200ba_profile_enable(b200ba_plan* plan, int on);
 int b200ba_profile_get(b200ba_plan* plan, double* ms_out /*[16]*/, int64_t* count_out /*[16]*/);
 

@@ -89,6 +89,13 @@ def load():
     return lib
 
 
+def default_pcg_rtol():
+    """The library's default PCG tolerance (b200ba_lm_default_opts)."""
+    o = LMOpts()
+    load().b200ba_lm_default_opts(C.byref(o))
+    return float(o.pcg_rtol)
+
+
 def check(rc, what=""):
     if rc != 0:
         msg = load().b200ba_last_error().decode(errors="replace")

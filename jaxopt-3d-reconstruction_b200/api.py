@@ -191,11 +191,18 @@ class B200BundleAdjustment:
     """Drop-in for JaxBundleAdjustment(cam_num, avg_cam_width)."""
 
     def __init__(self, cam_num, avg_cam_width, device=None, tol=1e-6, maxiter=100,
-                 damping_parameter=1e-6, pcg_rtol=1e-10, pcg_maxiter=1000, jac_f32=True,
+                 damping_parameter=1e-6, pcg_rtol=None, pcg_maxiter=1000, jac_f32=None,
                  verbose=False, process_group=None, distributed=None, residual_model="scalar"):
         if residual_model not in ("scalar", "vector2"):
-            raise ValueError("residual_model must be 'scalar' (the reference) or 'vector2' (COLMAP-style, experimental)")
+            raise ValueError("residual_model must be 'scalar' (the reference) or 'vector2' (the COLMAP comparator's cost)")
         self.residual_model = residual_model
+        if jac_f32 is None:
+            # stored Jacobian rows: fp32 (fp64 accumulation) for the reference's small-residual scalar model; the 2-vector
+            # model is a LARGE-residual problem whose last iterations stall on fp32 storage noise (measured: 21 LM
+            # iterations instead of 10 on the `small` scene, same final cost) -> fp64 rows
+            jac_f32 = residual_model == "scalar"
+        if pcg_rtol is None:
+            pcg_rtol = _lib.default_pcg_rtol()
         self.cam_num = int(cam_num)
         self.avg_cam_width_sqr = float(avg_cam_width) ** 2
         self.device = torch.device(device if device is not None else "cuda")

@@ -19,6 +19,7 @@
 #include "ba_cs_ring.cuh"
 #include "ba_cs_warp.cuh"
 #include "ba_ps_tile.cuh"
+#include "ba_dense.cuh"
 #include "pose_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -80,9 +81,17 @@ struct b200ba_plan {
   // tiled point-side kernel (ba_ps_tile.cuh): tiles of whole chunks, their rows in B order, A row -> slot in tile
   int32_t *tile_row = nullptr, *tile_pt = nullptr, *gpos = nullptr;
   uint16_t* lpos = nullptr;
-  int ntiles = 0, tile_rows = 0, use_tile = 0;
+  int ntiles = 0, tile_rows = 0, use_tile = 0, tile_grid = 0;
+  int* tile_ctr = nullptr;  // {next tile, CTAs finished}: zero between launches
   int fused_lin = 0;    // U_c / g_c accumulated inside the residual/Jacobian kernel
+  int exact_grad = 0;   // gradient from the unrounded rows instead of the stored ones (fp32-row build only; see k_resjac)
   int dense_schur = 0;  // small scenes: reduced camera system formed densely and factored (ba_dense.cuh)
+  int dn_T = 0, dn_npad = 0, dn_epoch = 0, dn_grid = 0, dn_grid_v = 0;
+  int64_t dn_M = 0;               // pairs
+  int32_t* dn_blk_ptr = nullptr;  // C*C + 1 segment offsets of the pair list
+  int2* dn_pairs = nullptr;
+  double *dn_S = nullptr, *dn_vec = nullptr;
+  int* dn_flags = nullptr;        // T*T tile flags | T + T solve flags
   int32_t* pt_B = nullptr;   // point of every B row (padding rows: -1)
   double2* obs_B = nullptr;  // observations in B order
   void* rec_A = nullptr;     // 32 B row records {b, r} in A order (K1 -> point blocks)
@@ -122,7 +131,7 @@ struct b200ba_plan {
   }
 };
 enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, PC_CAM_FINISH, PC_MV_PT, PC_MV_CAM,
-       PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_EVAL, PC_COUNT };
+       PC_PCG_VEC, PC_BACKSUB, PC_COST, PC_OTHER, PC_EVAL, PC_DN_ASM, PC_DN_CHOL, PC_DN_SOLVE, PC_COUNT };
 // k_cs_warp with the plan's unroll (see ba_cs_warp.cuh)
 #define CW_LAUNCH(p, cls, grid, st, ...)                                                                   \
   do {                                                                                                     \
@@ -250,6 +259,70 @@ __global__ void k_permute_obs(int64_t N, const int32_t* __restrict__ order_ps, c
     const int64_t o = order_ps[i];
     out_B[posB[i]] = make_double2(obs[2 * o], obs[2 * o + 1]);
   }
+}
+
+static int bits_for(int64_t v);
+
+// Dense reduced-camera path (ba_dense.cuh): pair list, S, flags.  Selected for 8C <= DENSE_MAX_N on a single rank
+// (B200BA_DENSE=0 keeps the PCG path, B200BA_DENSE_MAX_CAMS lowers the limit).
+static int dense_build(b200ba_plan* p, cudaStream_t s) {
+  const int C = p->C, P = p->P;
+  const int64_t N = p->N;
+  int max_cams = DENSE_MAX_N / 8;
+  if (const char* e = getenv("B200BA_DENSE_MAX_CAMS")) { const int v = atoi(e); if (v >= 0 && v < max_cams) max_cams = v; }
+  if (const char* e = getenv("B200BA_DENSE")) if (!atoi(e)) return 0;
+  if (N <= 0 || P <= 0 || C > max_cams) return 0;
+  int64_t *cnt = nullptr, *off = nullptr;
+  void* tmp = nullptr;
+  size_t tmp_bytes = 0, tb2 = 0;
+  if (pool_malloc((void**)&cnt, ((size_t)P + 1) * sizeof(int64_t)) != cudaSuccess || pool_malloc((void**)&off, ((size_t)P + 1) * sizeof(int64_t)) != cudaSuccess)
+    FAIL(B200BA_ECUDA, "dense_build: alloc");
+  cudaMemsetAsync(cnt, 0, ((size_t)P + 1) * sizeof(int64_t), s);
+  LAUNCH(k_dn_pair_count, cdiv(P, 256), 256, 0, s, P, p->pt_ptr, cnt);
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, cnt, off, P + 1, s);
+  if (pool_malloc(&tmp, tmp_bytes) != cudaSuccess) FAIL(B200BA_ECUDA, "dense_build: alloc");
+  cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, cnt, off, P + 1, s);
+  int64_t M = 0;
+  cudaMemcpyAsync(&M, off + P, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
+  CK(cudaStreamSynchronize(s));
+  pool_free(tmp); tmp = nullptr;
+  if (M <= 0 || M > (1LL << 27)) { pool_free(cnt); pool_free(off); return 0; }  // too many pairs: stay with PCG
+  int32_t *keys = nullptr, *keys2 = nullptr;
+  int64_t *vals = nullptr;
+  int rc = 0;
+  if ((rc = dalloc(p, &p->dn_pairs, (size_t)M)) || (rc = dalloc(p, &p->dn_blk_ptr, (size_t)C * C + 2))) return rc;
+  if (pool_malloc((void**)&keys, M * sizeof(int32_t)) != cudaSuccess || pool_malloc((void**)&keys2, M * sizeof(int32_t)) != cudaSuccess ||
+      pool_malloc((void**)&vals, M * sizeof(int64_t)) != cudaSuccess)
+    FAIL(B200BA_ECUDA, "dense_build: alloc");
+  LAUNCH(k_dn_pair_fill, cdiv(P, 256), 256, 0, s, P, C, p->pt_ptr, p->cam_ps, off, keys, (int2*)vals);
+  const int nbits = bits_for((int64_t)C * C);
+  cub::DeviceRadixSort::SortPairs(nullptr, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
+  if (pool_malloc(&tmp, tb2) != cudaSuccess) FAIL(B200BA_ECUDA, "dense_build: alloc");
+  cub::DeviceRadixSort::SortPairs(tmp, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
+  LAUNCH(k_segment_ptr, cdiv((int64_t)C * C + 1, 256), 256, 0, s, C * C, M, keys2, p->dn_blk_ptr);
+  const int Cpad = (C + 3) & ~3;
+  p->dn_npad = 8 * Cpad;
+  p->dn_T = p->dn_npad / DN_NB;
+  p->dn_M = M;
+  if ((rc = dalloc(p, &p->dn_S, (size_t)p->dn_npad * p->dn_npad)) || (rc = dalloc(p, &p->dn_vec, (size_t)p->dn_npad)) ||
+      (rc = dalloc(p, &p->dn_flags, (size_t)p->dn_T * p->dn_T + 2 * (size_t)p->dn_T)))
+    return rc;
+  cudaMemsetAsync(p->dn_flags, 0, ((size_t)p->dn_T * p->dn_T + 2 * (size_t)p->dn_T) * sizeof(int), s);
+  cudaMemsetAsync(p->dn_S, 0, (size_t)p->dn_npad * p->dn_npad * sizeof(double), s);
+  LAUNCH(k_dn_init_pad, cdiv((int64_t)p->dn_npad * p->dn_npad, 256), 256, 0, s, 8 * C, p->dn_npad, p->dn_S);
+  CK(cudaStreamSynchronize(s));
+  pool_free(cnt); pool_free(off); pool_free(keys); pool_free(keys2); pool_free(vals); pool_free(tmp);
+  int dev = 0, coop = 0, per_sm = 0, n_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_dn_factor, DN_T, 0));
+  if (!coop || per_sm < 1) return 0;
+  const int ntl = p->dn_T * (p->dn_T + 1) / 2;
+  p->dn_grid = std::min(ntl, std::min(per_sm, 4) * n_sm);
+  p->dn_grid_v = std::min(p->dn_T, n_sm);
+  p->dense_schur = 1;
+  return 0;
 }
 
 static int bits_for(int64_t v) {
@@ -512,6 +585,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     p->fused_lin = 1;
+    if (const char* e = getenv("B200BA_EXACT_GRAD")) p->exact_grad = atoi(e) != 0;
     if (cudaFuncSetAttribute(k_resjac<float, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
         cudaFuncSetAttribute(k_resjac<float, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
         cudaFuncSetAttribute(k_resjac<double, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
@@ -577,12 +651,11 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaMemcpyAsync(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaStreamSynchronize(s);
     lap("point chunks");
-    // Tiles of the tiled point-side kernel: consecutive chunks up to tile_rows rows.  Used when a tile still holds
-    // >= 2 rows of the average camera (then the tile's rows are piecewise contiguous in B order) and no single point
-    // exceeds a tile; otherwise the chunk kernel with its L2-window gather stays (Final-13682: 13 682 cameras).
-    int tr = 8192;
+    // Tiles of the tiled point-side kernel (ba_ps_tile.cuh; opt-in, measured equal to the chunk kernel at best):
+    // consecutive chunks up to tile_rows rows; needs every point to fit a tile.
+    int tr = 4096;
     if (const char* e = getenv("B200BA_TILE_ROWS")) { const int v = atoi(e); if (v >= 1024 && v <= 24576) tr = v; }
-    int want = N > 0 && tr >= 2 * C;
+    int want = 0;
     if (const char* e = getenv("B200BA_PS_TILE")) want = N > 0 && atoi(e) != 0;
     if (want) {
       std::vector<int32_t> trow, tpt;
@@ -606,11 +679,13 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
         const int nbits = 32 + bits_for(p->ntiles);
         cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, (int)N, 0, nbits, s);
         const bool a_ok = !dalloc(p, &p->tile_row, trow.size()) && !dalloc(p, &p->tile_pt, tpt.size()) && !dalloc(p, &p->gpos, (size_t)N) &&
+                          !dalloc(p, &p->tile_ctr, 4) &&
                           !dalloc(p, &p->lpos, (size_t)N) && pool_malloc((void**)&keys, N * sizeof(int64_t)) == cudaSuccess &&
                           pool_malloc((void**)&keys2, N * sizeof(int64_t)) == cudaSuccess && pool_malloc((void**)&vals, N * sizeof(int32_t)) == cudaSuccess &&
                           pool_malloc((void**)&vals2, N * sizeof(int32_t)) == cudaSuccess && pool_malloc(&tmp, tmp_bytes) == cudaSuccess;
         cudaError_t e = a_ok ? cudaSuccess : cudaErrorMemoryAllocation;
         if (a_ok) {
+          cudaMemsetAsync(p->tile_ctr, 0, 4 * sizeof(int), s);
           cudaMemcpyAsync(p->tile_row, trow.data(), trow.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
           cudaMemcpyAsync(p->tile_pt, tpt.data(), tpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
           LAUNCH(k_tile_keys, cdiv(N, 256), 256, 0, s, N, p->ntiles, p->tile_row, p->posB, keys, vals);
@@ -625,12 +700,20 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_ps_tile<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, std::string("plan_create: tile tables: ") + cudaGetErrorString(e)); }
+        // persistent grid: as many CTAs as fit (registers: PT_MINB per SM; shared memory: tile_rows x 8 B each)
+        int per_sm = 0;
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ps_tile<float, false>, PT_T, (size_t)smem);
+        if (e != cudaSuccess || per_sm < 1) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: tile kernel does not fit an SM"); }
+        p->tile_grid = std::min(p->ntiles, per_sm * p->n_sm);
+        if (const char* ev = getenv("B200BA_TILE_GRID")) { const int v = atoi(ev); if (v > 0) p->tile_grid = std::min(p->ntiles, v); }
         p->use_tile = 1;
         if (2 * (size_t)p->ntiles + 16 > 2 * mx + 16) { /* partN holds 2 doubles per tile: ntiles <= nchunks <= mx */ }
       }
     }
     lap("point tiles");
   }
+  if (int rc2 = dense_build(p, s)) { b200ba_plan_destroy(p); return rc2; }
+  lap("dense pair list");
   *out = p;
   return B200BA_OK;
 }
@@ -763,6 +846,7 @@ extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const 
   p->rank = rank;
   p->nranks = nranks;
   p->split = 1;
+  p->dense_schur = 0;  // the dense path would need S summed over the ranks; point-sharded solves use PCG
   {
     cudaStream_t xs = nullptr;
     int rc = xchg_setup(rank, nranks, (size_t)p->C * 8 + 8, xs);
@@ -812,6 +896,17 @@ static int read_state(b200ba_plan* p, cudaStream_t s) {
   return 0;
 }
 
+// cooperative launch (all CTAs co-resident: the dense kernels wait on each other's flags) with the profiling hooks of PLAUNCH
+static int coop_launch(b200ba_plan* p, int cls, const void* fn, int grid, int block, void** args, cudaStream_t s) {
+  size_t i0 = 0, i1 = 0;
+  if (p->prof) { i0 = p->ev_used; cudaEventRecord(p->get_event(), s); }
+  cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(block), args, 0, s);
+  ++g_launches;
+  if (p->prof) { i1 = p->ev_used; cudaEventRecord(p->get_event(), s); p->recs.push_back({cls, i0, i1}); }
+  if (e != cudaSuccess) FAIL(B200BA_ECUDA, std::string("cooperative launch: ") + cudaGetErrorString(e));
+  return 0;
+}
+
 // caller's P x 3 points <-> internal 32 B records {X, Y, Z, 0}
 __global__ void k_pts_to4(int64_t n4, const double* __restrict__ pts, double* __restrict__ pts4) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -837,13 +932,13 @@ struct Ops {
     // K0+K1+K2b in one launch: rows, A-order records, and the camera blocks U_c / g_c (ba_kernels.cuh)
     if (p->residual_model)
       PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 1, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-              pts4, sqrt(inv_w2), (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc);
+              pts4, sqrt(inv_w2), (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad);
     else
       PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 0, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-              pts4, inv_w2, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc);
+              pts4, inv_w2, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 1, 1, p->lin_scal, 0);
     if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec*)p->rec_A,
-                  (JT*)p->Jp_ps, p->V, p->gp, p->partN);
+                  (JT*)p->Jp_ps, p->V, p->gp, p->partN, p->exact_grad);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
     int rc;
@@ -898,9 +993,9 @@ struct Ops {
   // point-side kernel: omega from sigma (and the PCG scalars of iteration `it` when do_scalars)
   static void ps(b200ba_plan* p, int it, int do_scalars, double rtol, int maxiter, cudaStream_t s) {
     if (p->use_tile) {
-      PLAUNCH(p, PC_MV_PT, (k_ps_tile<JT, false>), p->ntiles, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
+      PLAUNCH(p, PC_MV_PT, (k_ps_tile<JT, false>), p->tile_grid, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
               p->ntiles, p->C, it, do_scalars, rtol, maxiter, p->st, p->part2, p->tile_row, p->tile_pt, p->pt_ptr, p->gpos, p->lpos,
-              (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr);
+              (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr, p->tile_ctr);
       return;
     }
     PLAUNCH(p, PC_MV_PT, (k_ps<JT, false>), p->nchunks > 0 ? p->nchunks : 1, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, it,
@@ -922,7 +1017,8 @@ struct Ops {
 
   // (V+mu)^-1, w/beta rows, Schur corrections, block-Jacobi inverses, reduced rhs, PCG start:
   // x = 0, r = rhs, u = Minv r, w = S u, m = Minv w, sigma = rows . m
-  static int prepare(b200ba_plan* p, cudaStream_t s) {
+  // everything of the Schur preparation that does not depend on HOW the reduced system is solved
+  static int prepare_blocks(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, P = p->P;
     if (P) PLAUNCH(p, PC_PT_PREPARE, (k_point_prepare<JT>), p->nblkP, 256, 0, s, P, (size_t)p->N, &p->st->mu, p->pt_ptr, p->posB,
                   (const JT*)p->Jp_ps, p->V, p->gp, p->Vinv, p->wb_B);
@@ -932,6 +1028,13 @@ struct Ops {
     if ((rc = allreduce(p, p->Sd, (size_t)C * 72, ncclSum, s))) return rc;
     PLAUNCH(p, PC_CAM_FINISH, k_cam_finish_prepare, cdiv(8 * (int64_t)C, CF_T), CF_T, 0, s, C, &p->st->mu, p->U, p->gc, p->Sd, p->rhs_part,
             p->Minv, p->rhs, p->cv, p->part2);
+    CK(cudaGetLastError());
+    return 0;
+  }
+  static int prepare(b200ba_plan* p, cudaStream_t s) {
+    const int C = p->C;
+    int rc;
+    if ((rc = prepare_blocks(p, s))) return rc;
     PLAUNCH(p, PC_PCG_VEC, k_pcg_init, 1, 256, 0, s, C, p->st, p->part2);
     cs(p, PC_MV_CAM, CS_A, CV_U, s);
     ps(p, 0, 0, 0.0, 0, s);
@@ -1002,12 +1105,43 @@ struct Ops {
     return 0;
   }
 
+  // Dense reduced-camera solve (ba_dense.cuh) after prepare_blocks(): assemble S, factor (DMMA tile Cholesky, one
+  // cooperative launch), two triangular sweeps; the solution lands in slot X of the camera records.
+  static int dense_solve(b200ba_plan* p, cudaStream_t s) {
+    const int C = p->C, T = p->dn_T, npad = p->dn_npad;
+    int epoch = ++p->dn_epoch;
+    PLAUNCH(p, PC_DN_ASM, (k_dn_assemble<JT>), cdiv(8 * (int64_t)C * C, 256), 256, 0, s, C, npad, (size_t)p->N, (size_t)p->P, &p->st->mu,
+            p->dn_blk_ptr, p->dn_pairs, p->posB, p->pt_ps, (const JT*)p->Jc_B, (const JT*)p->Jp_ps, p->Vinv, p->U, p->dn_S);
+    int* tflags = p->dn_flags;
+    int* yflag = p->dn_flags + (size_t)T * T;
+    int* xflag = yflag + T;
+    int Ti = T, np_ = npad;
+    {
+      void* args[] = {&Ti, &np_, &epoch, &p->dn_S, &tflags, &p->st};
+      int rc = coop_launch(p, PC_DN_CHOL, (const void*)k_dn_factor, p->dn_grid, DN_T, args, s);
+      if (rc) return rc;
+    }
+    PLAUNCH(p, PC_DN_SOLVE, k_dn_load_rhs, cdiv(npad, 256), 256, 0, s, 8 * C, npad, p->rhs, p->dn_vec);
+    {
+      const double* Lc = p->dn_S;
+      void* args[] = {&Ti, &np_, &epoch, &Lc, &p->dn_vec, &yflag};
+      int rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<false>, p->dn_grid_v, DN_T, args, s);
+      if (rc) return rc;
+      void* args2[] = {&Ti, &np_, &epoch, &Lc, &p->dn_vec, &xflag};
+      rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<true>, p->dn_grid_v, DN_T, args2, s);
+      if (rc) return rc;
+    }
+    PLAUNCH(p, PC_DN_SOLVE, k_dn_store_x, cdiv(8 * (int64_t)C, 256), 256, 0, s, C, p->dn_vec, p->cv);
+    CK(cudaGetLastError());
+    return 0;
+  }
+
   static int backsub(b200ba_plan* p, cudaStream_t s) {
     cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, CV_X, s);
     if (p->N && p->use_tile) {
-      PLAUNCH(p, PC_BACKSUB, (k_ps_tile<JT, true>), p->ntiles, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
+      PLAUNCH(p, PC_BACKSUB, (k_ps_tile<JT, true>), p->tile_grid, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
               p->ntiles, p->C, 0, 0, 0.0, 0, p->st, nullptr, p->tile_row, p->tile_pt, p->pt_ptr, p->gpos, p->lpos,
-              (const JT*)p->Jp_ps, p->Vinv, p->sig, nullptr, p->gp, p->vp, p->partN);
+              (const JT*)p->Jp_ps, p->Vinv, p->sig, nullptr, p->gp, p->vp, p->partN, p->tile_ctr);
       PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->ntiles, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
       return 0;
     }
@@ -1022,10 +1156,10 @@ struct Ops {
                   double* out_dev, cudaStream_t s) {
     if (p->residual_model)
       PLAUNCH(p, PC_COST, (k_resjac<JT, 1, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
-              sqrt(inv_w2), nullptr, nullptr, p->part, nullptr, nullptr);
+              sqrt(inv_w2), nullptr, nullptr, p->part, nullptr, nullptr, 0);
     else
       PLAUNCH(p, PC_COST, (k_resjac<JT, 0, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
-              inv_w2, nullptr, nullptr, p->part, nullptr, nullptr);
+              inv_w2, nullptr, nullptr, p->part, nullptr, nullptr, 0);
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, p->C, 1, 1, out_dev, 0);
     return 0;
   }
@@ -1127,7 +1261,10 @@ extern "C" int b200ba_schur_solve(b200ba_plan* p, double rtol, int maxiter, doub
   if (!p) FAIL(B200BA_EINVAL, "null plan");
   cudaStream_t s = (cudaStream_t)stream_;
   int rc;
-  if ((rc = DISPATCH(p, pcg_solve, p, rtol, maxiter, 0, iters_host, s))) return rc;
+  if (p->dense_schur) {  // the preparation has run (b200ba_schur_prepare); rtol / maxiter do not apply to the direct solve
+    if ((rc = DISPATCH(p, dense_solve, p, s))) return rc;
+    if (iters_host) *iters_host = 0;
+  } else if ((rc = DISPATCH(p, pcg_solve, p, rtol, maxiter, 0, iters_host, s))) return rc;
   if ((rc = DISPATCH(p, backsub, p, s))) return rc;
   if (vc) CK(cudaMemcpy2DAsync(vc, 64, p->cv + 8 * CV_X, CV_STRIDE * sizeof(double), 64, p->C, cudaMemcpyDeviceToDevice, s));
   if (vp) CK(cudaMemcpyAsync(vp, p->vp, (size_t)p->P * 3 * 8, cudaMemcpyDeviceToDevice, s));
@@ -1185,7 +1322,7 @@ extern "C" void b200ba_lm_default_opts(b200ba_lm_opts* o) {
   o->maxiter = 100;
   o->tol = 1e-6;
   o->damping_parameter = 1e-6;
-  o->pcg_rtol = 1e-10;
+  o->pcg_rtol = 1e-9;  // loosest tolerance that keeps every golden shape >= 6x inside the 1e-5 trajectory bar (tools/rtol_sweep.py, profiles/r2_rtol_sweep.md)
   o->pcg_maxiter = 1000;
   o->fixed_pcg_iters = 0;
   o->verbose = 0;
@@ -1212,9 +1349,14 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   int status = 0;
   while (opts->maxiter > 0) {
     // ---- update(): solve (J^T J + mu I) v = g through the reduced camera system
-    if ((rc = DISPATCH(p, prepare, p, s))) return rc;
     int pcg_iters = 0;
-    if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
+    if (p->dense_schur) {  // small scenes: exact dense solve of the reduced camera system (ba_dense.cuh)
+      if ((rc = DISPATCH(p, prepare_blocks, p, s))) return rc;
+      if ((rc = DISPATCH(p, dense_solve, p, s))) return rc;
+    } else {
+      if ((rc = DISPATCH(p, prepare, p, s))) return rc;
+      if ((rc = DISPATCH(p, pcg_solve, p, opts->pcg_rtol, opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
+    }
     res->n_pcg_iters_total += pcg_iters;
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);

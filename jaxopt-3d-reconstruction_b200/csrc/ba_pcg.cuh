@@ -197,6 +197,7 @@ k_cs(int C, int nPB, int flags, int stash_rows, const SolverState* __restrict__ 
 // gamma = (r,u), delta = (w,u), rr = (r,r) from the per-camera partials of the last k_cs;
 // beta = gamma/gamma_old, alpha = gamma/(delta - beta gamma/alpha_old)  (first iteration: 0, gamma/delta).
 // Ordered reduction: the result does not depend on the launch geometry of anything else.
+template <int NBATCH = 8>
 __device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restrict__ st,
                                             const double* __restrict__ part, double rtol, int maxiter,
                                             double* sm3 /*3*32*/) {
@@ -205,12 +206,12 @@ __device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restri
   double v3[3] = {0.0, 0.0, 0.0};
   const int bd = blockDim.x;
   int i = threadIdx.x;
-  for (; i + 7 * bd < C; i += 8 * bd) {
-    double q[8][4];
+  for (; i + (NBATCH - 1) * bd < C; i += NBATCH * bd) {
+    double q[NBATCH][4];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) ld256(part + 4 * (size_t)(i + u * bd), q[u]);
+    for (int u = 0; u < NBATCH; ++u) ld256(part + 4 * (size_t)(i + u * bd), q[u]);
 #pragma unroll
-    for (int u = 0; u < 8; ++u) { v3[0] += q[u][0]; v3[1] += q[u][1]; v3[2] += q[u][2]; }
+    for (int u = 0; u < NBATCH; ++u) { v3[0] += q[u][0]; v3[1] += q[u][1]; v3[2] += q[u][2]; }
   }
   for (; i < C; i += bd) {
     double q[4];
@@ -342,6 +343,16 @@ __device__ __forceinline__ void ps_scatter(double* p, double v) {
   *p = v;
 #endif
 }
+// z = Vinv t and omega = b . z with an explicit operation order (fma chains are never re-associated): shared by the chunk
+// kernel and the tiled kernel (ba_ps_tile.cuh), which therefore agree to the last bit
+__device__ __forceinline__ void ps_apply_vinv(const double* vi, double t0, double t1, double t2, double& z0, double& z1, double& z2) {
+  z0 = fma(vi[2], t2, fma(vi[1], t1, vi[0] * t0));
+  z1 = fma(vi[4], t2, fma(vi[3], t1, vi[1] * t0));
+  z2 = fma(vi[5], t2, fma(vi[4], t1, vi[2] * t0));
+}
+__device__ __forceinline__ double ps_dot3(double b0, double b1, double b2, double z0, double z1, double z2) {
+  return fma(b2, z2, fma(b1, z1, b0 * z0));
+}
 template <typename JT, bool BACKSUB>
 #ifdef PS_MINB
 __global__ void __launch_bounds__(PS_T, PS_MINB)
@@ -418,16 +429,15 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
       }
       if (BACKSUB) {
         t0 = g0 - t0; t1 = g1 - t1; t2 = g2 - t2;
-        const double z0 = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
-        const double z1 = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
-        const double z2 = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
+        double z0, z1, z2;
+        ps_apply_vinv(vi, t0, t1, t2, z0, z1, z2);
         vp[3 * (size_t)p] = z0; vp[3 * (size_t)p + 1] = z1; vp[3 * (size_t)p + 2] = z2;
-        acc[0] = z0 * g0 + z1 * g1 + z2 * g2;
-        acc[1] = z0 * z0 + z1 * z1 + z2 * z2;
+        acc[0] = ps_dot3(z0, z1, z2, g0, g1, g2);
+        acc[1] = ps_dot3(z0, z1, z2, z0, z1, z2);
       } else {
-        sz[0][tid] = vi[0] * t0 + vi[1] * t1 + vi[2] * t2;
-        sz[1][tid] = vi[1] * t0 + vi[3] * t1 + vi[4] * t2;
-        sz[2][tid] = vi[2] * t0 + vi[4] * t1 + vi[5] * t2;
+        double z0, z1, z2;
+        ps_apply_vinv(vi, t0, t1, t2, z0, z1, z2);
+        sz[0][tid] = z0; sz[1][tid] = z1; sz[2][tid] = z2;
       }
     }
     if (!BACKSUB) {
@@ -440,7 +450,7 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
 #ifdef PS_DEBUG
           if (q < 0 || q >= npts || dst[j] < 0) { printf("k_ps: ch %d tid %d i %d q %d npts %d nrows %d dst %d\n", ch, tid, i, q, npts, nrows, dst[j]); q = 0; }
 #endif
-          ps_scatter(omg + dst[j], (double)b[j][0] * sz[0][q] + (double)b[j][1] * sz[1][q] + (double)b[j][2] * sz[2][q]);
+          ps_scatter(omg + dst[j], ps_dot3((double)b[j][0], (double)b[j][1], (double)b[j][2], sz[0][q], sz[1][q], sz[2][q]));
         }
       }
     }

@@ -23,6 +23,7 @@ import numpy as np
 SHAPES = {
     "tiny": (3, 8, 20),
     "small": (15, 300, 1500),
+    "ref15x400": (15, 400, 2000),   # the reference's own BA benchmark size (benchmark_impl_bundle_adjustment.py:28-32)
     "ladybug49": (49, 7776, 31843),
     "trafalgar257": (257, 65132, 225911),
     "venice1778": (1778, 993923, 5001946),

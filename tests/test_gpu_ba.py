@@ -10,6 +10,13 @@ from oracle import ba_oracle as bo
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _pcg_path(monkeypatch):
+    """These tests exercise the PCG machinery (implicit Schur matvec, ring / warp-task / chunk / tile kernels) on shapes
+    small enough for the dense reduced-camera path, which would otherwise be selected (tests/test_gpu_dense.py covers it)."""
+    monkeypatch.setenv("B200BA_DENSE", "0")
+
+
 def _setup(shape, seed=0, jac_f32=False, **kw):  # building-block tests use fp64 rows (tight row tolerances)
     sc = b200ba.synth.make_ba_scene(shape, seed=seed, **kw)
     ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=jac_f32)
@@ -147,8 +154,13 @@ def test_tiled_and_chunk_point_kernels_agree(monkeypatch):
         monkeypatch.setenv("B200BA_PS_TILE", tile)
         monkeypatch.setenv("B200BA_TILE_ROWS", "1024")
         ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width)
+        info_expected = tile == "1" 
         x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
-        params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+        prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+        info = (__import__("ctypes").c_int * 8)()
+        prob.lib.b200ba_plan_info(prob.plan, info)
+        assert bool(info[0]) == info_expected and (not info_expected or info[2] > 100)   # really the tiled kernel, many tiles
+        params, st = ba.optimize(x0, prob, None, k3, None)
         assert st.iter_num == int(gold["iter_num"])
         np.testing.assert_allclose(st.loss_trajectory, gold["loss"], rtol=1e-5)
         out.append((params, st.loss_trajectory))
