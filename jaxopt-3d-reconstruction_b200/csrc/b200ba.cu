@@ -268,8 +268,9 @@ static int bits_for(int64_t v);
 static int dense_build(b200ba_plan* p, cudaStream_t s) {
   const int C = p->C, P = p->P;
   const int64_t N = p->N;
-  int max_cams = DENSE_MAX_N / 8;
-  if (const char* e = getenv("B200BA_DENSE_MAX_CAMS")) { const int v = atoi(e); if (v >= 0 && v < max_cams) max_cams = v; }
+  int max_cams = DENSE_DEFAULT_CAMS;
+  if (const char* e = getenv("B200BA_DENSE_MAX_CAMS")) { const int v = atoi(e); if (v >= 0 && v <= DENSE_MAX_N / 8) max_cams = v; }
+  if (const char* e = getenv("B200BA_DENSE")) if (atoi(e) == 1 && !getenv("B200BA_DENSE_MAX_CAMS")) max_cams = DENSE_MAX_N / 8;  // forced on
   if (const char* e = getenv("B200BA_DENSE")) if (!atoi(e)) return 0;
   if (N <= 0 || P <= 0 || C > max_cams) return 0;
   int64_t *cnt = nullptr, *off = nullptr;
@@ -286,7 +287,8 @@ static int dense_build(b200ba_plan* p, cudaStream_t s) {
   cudaMemcpyAsync(&M, off + P, sizeof(int64_t), cudaMemcpyDeviceToHost, s);
   CK(cudaStreamSynchronize(s));
   pool_free(tmp); tmp = nullptr;
-  if (M <= 0 || M > (1LL << 27)) { pool_free(cnt); pool_free(off); return 0; }  // too many pairs: stay with PCG
+  if (M > (1LL << 27)) { pool_free(cnt); pool_free(off); return 0; }  // too many pairs: stay with PCG
+  if (M <= 0) M = 0;
   int32_t *keys = nullptr, *keys2 = nullptr;
   int64_t *vals = nullptr;
   int rc = 0;
@@ -294,11 +296,13 @@ static int dense_build(b200ba_plan* p, cudaStream_t s) {
   if (pool_malloc((void**)&keys, M * sizeof(int32_t)) != cudaSuccess || pool_malloc((void**)&keys2, M * sizeof(int32_t)) != cudaSuccess ||
       pool_malloc((void**)&vals, M * sizeof(int64_t)) != cudaSuccess)
     FAIL(B200BA_ECUDA, "dense_build: alloc");
-  LAUNCH(k_dn_pair_fill, cdiv(P, 256), 256, 0, s, P, C, p->pt_ptr, p->cam_ps, off, keys, (int2*)vals);
-  const int nbits = bits_for((int64_t)C * C);
-  cub::DeviceRadixSort::SortPairs(nullptr, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
-  if (pool_malloc(&tmp, tb2) != cudaSuccess) FAIL(B200BA_ECUDA, "dense_build: alloc");
-  cub::DeviceRadixSort::SortPairs(tmp, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
+  if (M) {
+    LAUNCH(k_dn_pair_fill, cdiv(P, 256), 256, 0, s, P, C, p->pt_ptr, p->cam_ps, off, keys, (int2*)vals);
+    const int nbits = bits_for((int64_t)C * C);
+    cub::DeviceRadixSort::SortPairs(nullptr, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
+    if (pool_malloc(&tmp, tb2) != cudaSuccess) FAIL(B200BA_ECUDA, "dense_build: alloc");
+    cub::DeviceRadixSort::SortPairs(tmp, tb2, keys, keys2, vals, (int64_t*)p->dn_pairs, (int)M, 0, nbits, s);
+  }
   LAUNCH(k_segment_ptr, cdiv((int64_t)C * C + 1, 256), 256, 0, s, C * C, M, keys2, p->dn_blk_ptr);
   const int Cpad = (C + 3) & ~3;
   p->dn_npad = 8 * Cpad;
@@ -1110,8 +1114,9 @@ struct Ops {
   static int dense_solve(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, T = p->dn_T, npad = p->dn_npad;
     int epoch = ++p->dn_epoch;
-    PLAUNCH(p, PC_DN_ASM, (k_dn_assemble<JT>), cdiv(8 * (int64_t)C * C, 256), 256, 0, s, C, npad, (size_t)p->N, (size_t)p->P, &p->st->mu,
-            p->dn_blk_ptr, p->dn_pairs, p->posB, p->pt_ps, (const JT*)p->Jc_B, (const JT*)p->Jp_ps, p->Vinv, p->U, p->dn_S);
+    PLAUNCH(p, PC_DN_ASM, (k_dn_assemble<JT>), dim3(cdiv(C, DN_ASM_T / 32), C), DN_ASM_T, 0, s, C, npad, (size_t)p->N, (size_t)p->P,
+            &p->st->mu, p->dn_blk_ptr, p->dn_pairs, p->posB, p->pt_ps, (const JT*)p->Jc_B, (const JT*)p->Jp_ps, p->Vinv, p->U, p->Sd,
+            p->dn_S);
     int* tflags = p->dn_flags;
     int* yflag = p->dn_flags + (size_t)T * T;
     int* xflag = yflag + T;

@@ -23,7 +23,8 @@
 #define DN_NB 32          // tile size
 #define DN_T 128          // threads per CTA of the factorisation / solve kernels (4 warps)
 #define DN_LD 36          // shared-memory tile stride in doubles (== 4 mod 16: the DMMA fragment loads are conflict-free)
-#define DENSE_MAX_N 2560  // 8C limit (320 cameras): S is n^2 * 8 B = 52 MB at the limit
+#define DENSE_MAX_N 2560  // hard 8C limit (320 cameras): S is n^2 * 8 B = 52 MB at the limit
+#define DENSE_DEFAULT_CAMS 128  // selected automatically up to this many cameras (measured crossover with the PCG path)
 
 __device__ __forceinline__ int dn_ld_acquire(const int* p) {
   int v;
@@ -43,12 +44,14 @@ __device__ __forceinline__ void dn_wait(const int* f, int epoch) {
 }
 
 // ---------------------------------------------------------------- plan time: the pair list
-// pairs of point p: rows ia >= ib of its A run (A rows of a point are sorted by camera, so cam[ia] >= cam[ib])
+// pairs of point p: rows ia > ib of its A run (A rows of a point are sorted by camera, so cam[ia] >= cam[ib]).  The self
+// pairs ia == ib (one per row: they would make every diagonal block a chain as long as the camera has rows) are not
+// listed: their sum  -sum_i beta_i a_i a_i^T  is the block-Jacobi correction Sd_c that k_cam_blocks already reduces.
 __global__ void k_dn_pair_count(int P, const int32_t* __restrict__ pt_ptr, int64_t* __restrict__ cnt) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const int64_t d = pt_ptr[p + 1] - pt_ptr[p];
-  cnt[p] = d * (d + 1) / 2;
+  cnt[p] = d * (d - 1) / 2;
 }
 __global__ void k_dn_pair_fill(int P, int C, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ cam_ps,
                                const int64_t* __restrict__ off, int32_t* __restrict__ keys, int2* __restrict__ vals) {
@@ -57,7 +60,7 @@ __global__ void k_dn_pair_fill(int P, int C, const int32_t* __restrict__ pt_ptr,
   const int beg = pt_ptr[p], end = pt_ptr[p + 1];
   int64_t o = off[p];
   for (int ia = beg; ia < end; ++ia)
-    for (int ib = beg; ib <= ia; ++ib) {
+    for (int ib = beg; ib < ia; ++ib) {
       keys[o] = cam_ps[ia] * C + cam_ps[ib];
       vals[o] = make_int2(ia, ib);
       ++o;
@@ -73,90 +76,104 @@ __global__ void k_dn_init_pad(int n, int npad, double* __restrict__ S) {
 }
 
 // ---------------------------------------------------------------- assemble
-// 8 lanes per block (c, d), d <= c; lane k owns row k of the 8x8 block.
+// One WARP per block (c, d), d <= c: four groups of 8 lanes take every fourth pair of the block's segment (lane k of a
+// group owns row k of the 8x8 block), the four partial blocks are added by two shuffle steps in a fixed order.
+// S_cd = [c == d](U_c + mu I + Sd_c) - sum_pairs a_i (b_i^T Vinv_p b_j) a_j^T   (Sd_c: the self pairs, from k_cam_blocks)
+#define DN_ASM_T 256
 template <typename JT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(DN_ASM_T)
 k_dn_assemble(int C, int npad, size_t N, size_t Pst, const double* __restrict__ mu_ptr, const int32_t* __restrict__ blk_ptr,
               const int2* __restrict__ pairs, const int32_t* __restrict__ posB, const int32_t* __restrict__ pt_ps,
               const JT* __restrict__ Jc_B, const JT* __restrict__ Jp_ps, const double* __restrict__ Vinv,
-              const double* __restrict__ U, double* __restrict__ S) {
-  const int64_t gq = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-  const int k = threadIdx.x & 7;
-  if (gq >= (int64_t)C * C) return;
-  const int c = (int)(gq / C), d = (int)(gq % C);
-  if (d > c) return;
+              const double* __restrict__ U, const double* __restrict__ Sd, double* __restrict__ S) {
+  const int c = blockIdx.y;
+  const int d = blockIdx.x * (DN_ASM_T / 32) + (threadIdx.x >> 5);
+  if (d > c) return;  // warp-uniform
+  const int lane = threadIdx.x & 31, k = lane & 7, sg = lane >> 3;
+  const int64_t gq = (int64_t)c * C + d;
   double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int beg = __ldg(blk_ptr + gq), end = __ldg(blk_ptr + gq + 1);
-  for (int q = beg; q < end; ++q) {
+  for (int q = beg + sg; q < end; q += 4) {
     const int2 pr = __ldg(pairs + q);
     const int ia = pr.x, ib = pr.y;
     const int p = __ldg(pt_ps + ia);
+    const int ja = __ldg(posB + ia), jb = __ldg(posB + ib);
     double vi[6];
 #pragma unroll
     for (int m = 0; m < 6; ++m) vi[m] = __ldg(Vinv + (size_t)m * Pst + p);
     const double a0 = (double)__ldg(Jp_ps + ia), a1 = (double)__ldg(Jp_ps + N + ia), a2 = (double)__ldg(Jp_ps + 2 * N + ia);
     const double b0 = (double)__ldg(Jp_ps + ib), b1 = (double)__ldg(Jp_ps + N + ib), b2 = (double)__ldg(Jp_ps + 2 * N + ib);
+    double ra[8], rb[8];
+    load8<JT>(Jc_B + 8 * (size_t)ja, ra);
+    load8<JT>(Jc_B + 8 * (size_t)jb, rb);
     const double t0 = vi[0] * b0 + vi[1] * b1 + vi[2] * b2;
     const double t1 = vi[1] * b0 + vi[3] * b1 + vi[4] * b2;
     const double t2 = vi[2] * b0 + vi[4] * b1 + vi[5] * b2;
     const double beta = a0 * t0 + a1 * t1 + a2 * t2;
-    double ra[8], rb[8];
-    load8<JT>(Jc_B + 8 * (size_t)__ldg(posB + ia), ra);
-    load8<JT>(Jc_B + 8 * (size_t)__ldg(posB + ib), rb);
     double ak = 0.0, bk = 0.0;
 #pragma unroll
     for (int l = 0; l < 8; ++l) { if (l == k) { ak = ra[l]; bk = rb[l]; } }
     const double wa = ak * beta;
 #pragma unroll
     for (int l = 0; l < 8; ++l) acc[l] += wa * rb[l];
-    if (c == d && ia != ib) {  // the same camera sees the point twice: both orders belong to the diagonal block
+    if (c == d) {  // the same camera sees the point twice (ia != ib): both orders belong to the diagonal block
       const double wb = bk * beta;
 #pragma unroll
       for (int l = 0; l < 8; ++l) acc[l] += wb * ra[l];
     }
   }
+#pragma unroll
+  for (int l = 0; l < 8; ++l) {
+    acc[l] += __shfl_xor_sync(0xffffffffu, acc[l], 8);
+    acc[l] += __shfl_xor_sync(0xffffffffu, acc[l], 16);
+  }
+  if (sg) return;
   const double mu = *mu_ptr;
   double* out = S + (size_t)(8 * c + k) * npad + 8 * d;
 #pragma unroll
   for (int l = 0; l < 8; ++l) {
-    double s = -acc[l];
-    if (c == d) s += U[64 * (size_t)c + 8 * k + l] + (l == k ? mu : 0.0);
-    out[l] = s;
+    double v = -acc[l];
+    if (c == d) v += U[64 * (size_t)c + 8 * k + l] + Sd[64 * (size_t)c + 8 * k + l] + (l == k ? mu : 0.0);
+    out[l] = v;
   }
 }
 
 // ---------------------------------------------------------------- factor
-// Warp-level Cholesky of a 32x32 tile in SHARED memory (stride DN_LD), lane = row; only the lower triangle is read.
-// Right-looking; a non-positive pivot gives NaN (like LAPACK potrf through jax).  (A register-resident version with the
-// 32 x 32 / 2 shuffle updates fully unrolled compiled to 19 K instructions and put the row in local memory.)
-__device__ __forceinline__ void dn_warp_potrf(double* __restrict__ A, int lane) {
-  for (int c = 0; c < DN_NB; ++c) {
-    __syncwarp();
-    const double dd = sqrt(A[c * DN_LD + c]);
-    const double inv = 1.0 / dd;
-    double l = 0.0;
-    if (lane > c) l = A[lane * DN_LD + c] * inv;
-    __syncwarp();
-    if (lane > c) A[lane * DN_LD + c] = l;
-    else if (lane == c) A[c * DN_LD + c] = dd;
-    __syncwarp();
-    // A[r][q] -= L[r][c] L[q][c] for c < q <= r
-    for (int q = c + 1; q <= lane; ++q) A[lane * DN_LD + q] -= l * A[q * DN_LD + c];
+// Warp-level Cholesky (Cholesky-Crout, left-looking) of a 32x32 tile in SHARED memory (stride DN_LD); lane = row, kept in
+// REGISTERS with static indices (the column loop is unrolled at compile time by template recursion), finished columns are
+// published to shared memory as they appear and read back as broadcasts.  Only the lower triangle is read.  A non-positive
+// pivot gives NaN (like LAPACK potrf through jax).  The dot products run as four independent chains.
+// History (GPU, per tile): right-looking with shared-memory read-modify-write chains 18 us; left-looking with run-time
+// loops over shared memory ~7 us; a right-looking register version with 496 unrolled shuffles compiled to 19 K instructions.
+template <int C>
+struct DnCol {
+  static __device__ __forceinline__ double dot(const double (&row)[DN_NB], const double* __restrict__ rc) {
+    double s[4] = {row[C], 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int q = 0; q < C; ++q) s[q & 3] -= row[q] * rc[q];
+    return (s[0] + s[1]) + (s[2] + s[3]);
   }
-  __syncwarp();
-}
-// X L^T = R, lane = row of R (in place, shared memory): x[c] = (r[c] - sum_{q<c} x[q] L[c][q]) / L[c][c]
-__device__ __forceinline__ void dn_warp_trsm(double* __restrict__ R, const double* __restrict__ Ls, int lane) {
-  double* row = R + lane * DN_LD;
-  for (int c = 0; c < DN_NB; ++c) {
-    double s0 = row[c], s1 = 0.0;
-    int q = 0;
-    for (; q + 1 < c; q += 2) { s0 -= row[q] * Ls[c * DN_LD + q]; s1 -= row[q + 1] * Ls[c * DN_LD + q + 1]; }
-    if (q < c) s0 -= row[q] * Ls[c * DN_LD + q];
-    row[c] = (s0 + s1) / Ls[c * DN_LD + c];
+  static __device__ __forceinline__ void potrf(double (&row)[DN_NB], double* __restrict__ A, int lane) {
+    DnCol<C - 1>::potrf(row, A, lane);
+    const double sv = dot(row, A + C * DN_LD);
+    if (lane == C) A[C * DN_LD + C] = sqrt(sv);
+    __syncwarp();
+    const double v = (lane == C) ? A[C * DN_LD + C] : sv / A[C * DN_LD + C];
+    row[C] = v;
+    if (lane > C) A[lane * DN_LD + C] = v;
+    __syncwarp();
   }
-  __syncwarp();
-}
+  // X L^T = R for one row per lane: row[C] = (row[C] - sum_{q<C} row[q] L[C][q]) / L[C][C]; L in shared memory (broadcasts)
+  static __device__ __forceinline__ void trsm(double (&row)[DN_NB], const double* __restrict__ Ls) {
+    DnCol<C - 1>::trsm(row, Ls);
+    row[C] = dot(row, Ls + C * DN_LD) / Ls[C * DN_LD + C];
+  }
+};
+template <>
+struct DnCol<-1> {
+  static __device__ __forceinline__ void potrf(double (&)[DN_NB], double* __restrict__, int) {}
+  static __device__ __forceinline__ void trsm(double (&)[DN_NB], const double* __restrict__) {}
+};
 
 // One persistent cooperative launch.  Lower tiles in column-major order idx = 0, 1, ...; CTA b owns idx = b, b + G, ...
 // and processes them in that order (every dependency of a tile has a smaller idx: no cycles, all CTAs resident).
@@ -180,25 +197,30 @@ k_dn_factor(int T, int npad, int epoch, double* __restrict__ S, int* __restrict_
       const double2 v = *reinterpret_cast<const double2*>(Cg + (size_t)(8 * w + g) * npad + 8 * nt + 2 * t);
       acc[nt][0] = v.x; acc[nt][1] = v.y;
     }
-    for (int k = 0; k < j; ++k) {
+    double va[8], vb[8];
+    auto wait_k = [&](int k) {
       if (tid == 0) dn_wait(flags + i * T + k, epoch);
       if (tid == 1 && i != j) dn_wait(flags + j * T + k, epoch);
-      __syncthreads();
-      {
-        const double* Ag = S + (size_t)(DN_NB * i + lr) * npad + DN_NB * k + lc;
-        double va[8];
-        ld256cg(Ag, va); ld256cg(Ag + 4, va + 4);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) As[lr * DN_LD + lc + e] = va[e];
-        if (i != j) {
-          const double* Bg = S + (size_t)(DN_NB * j + lr) * npad + DN_NB * k + lc;
-          double vb[8];
-          ld256cg(Bg, vb); ld256cg(Bg + 4, vb + 4);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) Bs[lr * DN_LD + lc + e] = vb[e];
-        }
+    };
+    auto load_k = [&](int k) {
+      const double* Ag = S + (size_t)(DN_NB * i + lr) * npad + DN_NB * k + lc;
+      ld256cg(Ag, va); ld256cg(Ag + 4, va + 4);
+      if (i != j) {
+        const double* Bg = S + (size_t)(DN_NB * j + lr) * npad + DN_NB * k + lc;
+        ld256cg(Bg, vb); ld256cg(Bg + 4, vb + 4);
       }
+    };
+    if (j > 0) { wait_k(0); __syncthreads(); load_k(0); }
+    for (int k = 0; k < j; ++k) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) As[lr * DN_LD + lc + e] = va[e];
+      if (i != j) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) Bs[lr * DN_LD + lc + e] = vb[e];
+      }
+      if (k + 1 < j) wait_k(k + 1);
       __syncthreads();
+      if (k + 1 < j) load_k(k + 1);  // in flight while the tensor core works on step k
       const double* Bt = (i != j) ? Bs : As;
 #pragma unroll
       for (int kk = 0; kk < DN_NB; kk += 4) {
@@ -225,20 +247,24 @@ k_dn_factor(int T, int npad, int epoch, double* __restrict__ S, int* __restrict_
     }
     __syncthreads();
     if (w == 0) {
+      double row[DN_NB];
+#pragma unroll
+      for (int cc = 0; cc < DN_NB; ++cc) row[cc] = As[lane * DN_LD + cc];
       if (i == j) {
-        dn_warp_potrf(As, lane);
+        DnCol<DN_NB - 1>::potrf(row, As, lane);
         bool bad = false;
-        for (int cc = 0; cc <= lane; ++cc) bad |= !(As[lane * DN_LD + cc] == As[lane * DN_LD + cc]);
+#pragma unroll
+        for (int cc = 0; cc < DN_NB; ++cc) {
+          if (cc > lane) row[cc] = 0.0;  // clean upper triangle of the diagonal tile
+          else bad |= !(row[cc] == row[cc]);
+        }
         if (bad) atomicOr(&st->status, 16);  // not positive definite -> NaN, reported as B200BA_ST_DENSE_NOT_SPD
       } else {
-        dn_warp_trsm(As, Bs, lane);
+        DnCol<DN_NB - 1>::trsm(row, Bs);
       }
       double* out = Cg + (size_t)lane * npad;
-      for (int cc = 0; cc < DN_NB; cc += 2) {
-        double v0 = As[lane * DN_LD + cc], v1 = As[lane * DN_LD + cc + 1];
-        if (i == j) { if (cc > lane) v0 = 0.0; if (cc + 1 > lane) v1 = 0.0; }  // clean upper triangle of the diagonal tile
-        *reinterpret_cast<double2*>(out + cc) = make_double2(v0, v1);
-      }
+#pragma unroll
+      for (int cc = 0; cc < DN_NB; cc += 2) *reinterpret_cast<double2*>(out + cc) = make_double2(row[cc], row[cc + 1]);
       __threadfence();
       __syncwarp();
       if (lane == 0) dn_st_release(flags + i * T + j, epoch);
