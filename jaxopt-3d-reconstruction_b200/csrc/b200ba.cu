@@ -92,6 +92,21 @@ struct b200ba_plan {
   int2* dn_pairs = nullptr;
   double *dn_S = nullptr, *dn_vec = nullptr;
   int* dn_flags = nullptr;        // T*T tile flags | T + T solve flags
+  // device-resident LM loop (dense path): ONE CUDA graph per solve, WHILE / IF conditional nodes, no host synchronisation
+  // inside the loop (lm_solve_graph below)
+  struct GraphLM {
+    cudaGraphExec_t exec = nullptr;
+    cudaGraph_t graph = nullptr;
+    double inv_w2 = 0, tol = 0, damping = 0;
+    int maxiter = -1, model = -1;
+    int64_t launches_init = 0, launches_body = 0, launches_lin = 0;
+    cudaStream_t cs = nullptr;                  // capture stream
+    double *cam_work = nullptr, *k3_work = nullptr;
+    double* traj = nullptr;                     // device: loss | grad | mu, (cap + 1) each, then cap ints `accepted`
+    double* traj_host = nullptr;                // pinned mirror
+    int cap = 0;
+    bool failed = false;                        // capture / instantiate failed once: stay on the host-driven loop
+  } glm;
   int32_t* pt_B = nullptr;   // point of every B row (padding rows: -1)
   double2* obs_B = nullptr;  // observations in B order
   void* rec_A = nullptr;     // 32 B row records {b, r} in A order (K1 -> point blocks)
@@ -722,10 +737,17 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   return B200BA_OK;
 }
 
+static void graph_release(b200ba_plan* p);
 extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
   if (!p) return B200BA_OK;
   cudaDeviceSynchronize();  // frees are stream ordered on the allocation stream: nothing of this plan may still run
   for (void* q : p->allocs) pool_free(q);
+  graph_release(p);
+  if (p->glm.cs) cudaStreamDestroy(p->glm.cs);
+  if (p->glm.cam_work) cudaFree(p->glm.cam_work);
+  if (p->glm.k3_work) cudaFree(p->glm.k3_work);
+  if (p->glm.traj) cudaFree(p->glm.traj);
+  if (p->glm.traj_host) cudaFreeHost(p->glm.traj_host);
   if (p->st_host) cudaFreeHost(p->st_host);
   if (p->scal_host) cudaFreeHost(p->scal_host);
   for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
@@ -1113,7 +1135,7 @@ struct Ops {
   // cooperative launch), two triangular sweeps; the solution lands in slot X of the camera records.
   static int dense_solve(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, T = p->dn_T, npad = p->dn_npad;
-    int epoch = ++p->dn_epoch;
+    PLAUNCH(p, PC_DN_ASM, k_dn_next_epoch, 1, 32, 0, s, p->st);
     PLAUNCH(p, PC_DN_ASM, (k_dn_assemble<JT>), dim3(cdiv(C, DN_ASM_T / 32), C), DN_ASM_T, 0, s, C, npad, (size_t)p->N, (size_t)p->P,
             &p->st->mu, p->dn_blk_ptr, p->dn_pairs, p->posB, p->pt_ps, (const JT*)p->Jc_B, (const JT*)p->Jp_ps, p->Vinv, p->U, p->Sd,
             p->dn_S);
@@ -1122,17 +1144,17 @@ struct Ops {
     int* xflag = yflag + T;
     int Ti = T, np_ = npad;
     {
-      void* args[] = {&Ti, &np_, &epoch, &p->dn_S, &tflags, &p->st};
+      void* args[] = {&Ti, &np_, &p->dn_S, &tflags, &p->st};
       int rc = coop_launch(p, PC_DN_CHOL, (const void*)k_dn_factor, p->dn_grid, DN_T, args, s);
       if (rc) return rc;
     }
     PLAUNCH(p, PC_DN_SOLVE, k_dn_load_rhs, cdiv(npad, 256), 256, 0, s, 8 * C, npad, p->rhs, p->dn_vec);
     {
       const double* Lc = p->dn_S;
-      void* args[] = {&Ti, &np_, &epoch, &Lc, &p->dn_vec, &yflag};
+      void* args[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &yflag};
       int rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<false>, p->dn_grid_v, DN_T, args, s);
       if (rc) return rc;
-      void* args2[] = {&Ti, &np_, &epoch, &Lc, &p->dn_vec, &xflag};
+      void* args2[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &xflag};
       rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<true>, p->dn_grid_v, DN_T, args2, s);
       if (rc) return rc;
     }
@@ -1333,6 +1355,223 @@ extern "C" void b200ba_lm_default_opts(b200ba_lm_opts* o) {
   o->verbose = 0;
 }
 
+// ---------------------------------------------------------------- device-resident LM loop (CUDA graph)
+// The reference's whole LM run is ONE device program (`lax.while_loop` under jit, bundle_adjustment.py:104-120); the
+// host-driven loop above synchronises after every decision.  For the dense path (small scenes, where an LM iteration is
+// ~30 short launches) the loop itself moves onto the device:
+//     linearise, init_state  ->  WHILE(it < maxiter && ||g|| > tol) { solve; trial; decide; IF(accepted) { linearise } ; ++it }
+// as one CUDA graph with conditional nodes (CUDA >= 12.4); kernels set the conditions with cudaGraphSetConditional.
+// The caller's parameters are copied into plan-owned buffers first so that the captured arguments never change;
+// trajectories are recorded on the device and read back once.
+__global__ void k_g_record0(SolverState* st, cudaGraphConditionalHandle loop_h, int maxiter, int cap, double* traj) {
+  if (threadIdx.x || blockIdx.x) return;
+  st->lm_it = 0;
+  traj[0] = st->loss;
+  traj[(cap + 1)] = sqrt(st->grad2);
+  traj[2 * (cap + 1)] = st->mu;
+  cudaGraphSetConditional(loop_h, maxiter > 0 ? 1 : 0);  // run(): the first update is unconditional
+}
+__global__ void k_g_accept(const SolverState* st, cudaGraphConditionalHandle if_h) {
+  if (threadIdx.x || blockIdx.x) return;
+  cudaGraphSetConditional(if_h, st->accepted ? 1 : 0);
+}
+__global__ void k_g_advance(SolverState* st, cudaGraphConditionalHandle loop_h, int maxiter, double tol, int cap, double* traj) {
+  if (threadIdx.x || blockIdx.x) return;
+  const int it = st->lm_it + 1;
+  st->lm_it = it;
+  const double err = sqrt(st->grad2);
+  if (it <= cap) {
+    traj[it] = st->loss;
+    traj[(cap + 1) + it] = err;
+    traj[2 * (cap + 1) + it] = st->mu;
+    reinterpret_cast<int*>(traj + 3 * (cap + 1))[it - 1] = st->accepted;
+  }
+  cudaGraphSetConditional(loop_h, (it < maxiter && err > tol) ? 1 : 0);  // NaN error also stops (NaN > tol is false)
+}
+
+static int leaf_nodes(cudaGraph_t g, std::vector<cudaGraphNode_t>& out) {
+  size_t n = 0;
+  CK(cudaGraphGetNodes(g, nullptr, &n));
+  std::vector<cudaGraphNode_t> all(n);
+  if (n) CK(cudaGraphGetNodes(g, all.data(), &n));
+  out.clear();
+  for (cudaGraphNode_t nd : all) {
+    size_t m = 0;
+    CK(cudaGraphNodeGetDependentNodes(nd, nullptr, &m));
+    if (m == 0) out.push_back(nd);
+  }
+  return 0;
+}
+// conditional node on the current leaves of g; the handle was created before (the kernels that set it are captured first)
+static int add_cond_node(cudaGraph_t g, cudaGraphConditionalNodeType type, cudaGraphConditionalHandle h, cudaGraphNode_t* node,
+                         cudaGraph_t* body) {
+  std::vector<cudaGraphNode_t> deps;
+  int rc = leaf_nodes(g, deps);
+  if (rc) return rc;
+  cudaGraphNodeParams np = {};
+  np.type = cudaGraphNodeTypeConditional;
+  np.conditional.handle = h;
+  np.conditional.type = type;
+  np.conditional.size = 1;
+  CK(cudaGraphAddNode(node, g, deps.data(), deps.size(), &np));
+  *body = np.conditional.phGraph_out[0];
+  return 0;
+}
+
+static void graph_release(b200ba_plan* p) {
+  auto& G = p->glm;
+  if (G.exec) cudaGraphExecDestroy(G.exec);
+  if (G.graph) cudaGraphDestroy(G.graph);
+  G.exec = nullptr; G.graph = nullptr; G.maxiter = -1;
+}
+
+template <typename JT>
+static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
+  auto& G = p->glm;
+  graph_release(p);
+  const int C = p->C, P = p->P;
+  const int cap = o->maxiter > 0 ? o->maxiter : 1;
+  if (!G.cs) CK(cudaStreamCreateWithFlags(&G.cs, cudaStreamNonBlocking));
+  if (!G.cam_work) {
+    CK(cudaMalloc((void**)&G.cam_work, (size_t)C * 8 * sizeof(double)));
+    CK(cudaMalloc((void**)&G.k3_work, (size_t)C * 3 * sizeof(double)));
+  }
+  if (cap > G.cap) {
+    if (G.traj) cudaFree(G.traj);
+    if (G.traj_host) cudaFreeHost(G.traj_host);
+    const size_t bytes = (3 * (size_t)(cap + 1) + (size_t)cap) * sizeof(double);
+    CK(cudaMalloc((void**)&G.traj, bytes));
+    CK(cudaMallocHost((void**)&G.traj_host, bytes));
+    G.cap = cap;
+  }
+  const bool prof = p->prof;
+  p->prof = false;  // no event records inside a capture
+  cudaStream_t s = G.cs;
+  int rc = 0;
+  cudaGraphConditionalHandle loop_h, if_h;
+  cudaGraphNode_t wnode, inode;
+  cudaGraph_t body = nullptr, ifbody = nullptr;
+  const bool cap_relaxed = true;
+  (void)cap_relaxed;
+#define GCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cudaStreamEndCapture(s, nullptr); cudaGetLastError(); p->prof = prof; \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_); return B200BA_ECUDA; } } while (0)
+  CK(cudaGraphCreate(&G.graph, 0));
+  CK(cudaGraphConditionalHandleCreate(&loop_h, G.graph, 0, cudaGraphCondAssignDefault));
+  // ---- segment A: init_state
+  int64_t l0 = g_launches.load();
+  GCK(cudaStreamBeginCaptureToGraph(s, G.graph, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, o->damping_parameter);
+  LAUNCH(k_g_record0, 1, 32, 0, s, p->st, loop_h, o->maxiter, G.cap, G.traj);
+  GCK(cudaStreamEndCapture(s, nullptr));
+  G.launches_init = g_launches.load() - l0;
+  if ((rc = add_cond_node(G.graph, cudaGraphCondTypeWhile, loop_h, &wnode, &body))) { p->prof = prof; return rc; }
+  // ---- segment B: one update() up to the accept decision
+  CK(cudaGraphConditionalHandleCreate(&if_h, body, 0, cudaGraphCondAssignDefault));
+  l0 = g_launches.load();
+  GCK(cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+  rc = Ops<JT>::prepare_blocks(p, s);
+  if (!rc) rc = Ops<JT>::dense_solve(p, s);
+  if (!rc) rc = Ops<JT>::backsub(p, s);
+  if (rc) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  LAUNCH(k_trial_cams, cdiv(C, 128), 128, 0, s, C, G.cam_work, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);
+  LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
+  if (P) LAUNCH(k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
+  if ((rc = Ops<JT>::cost(p, p->cam_trial, G.k3_work, p->pts4_trial, inv_w2, p->scal + 8, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  LAUNCH(k_pack_decide, 1, 1, 0, s, p->scal);
+  LAUNCH(k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
+  LAUNCH(k_g_accept, 1, 32, 0, s, p->st, if_h);
+  LAUNCH(k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, G.cam_work);
+  if (P) LAUNCH(k_accept_copy, cdiv(4 * (int64_t)P, 256), 256, 0, s, p->st, 4 * (int64_t)P, p->pts4_trial, p->pts4);
+  GCK(cudaStreamEndCapture(s, nullptr));
+  G.launches_body = g_launches.load() - l0;
+  if ((rc = add_cond_node(body, cudaGraphCondTypeIf, if_h, &inode, &ifbody))) { p->prof = prof; return rc; }
+  // ---- segment C (after the IF node): iteration count, trajectories, loop condition
+  GCK(cudaStreamBeginCaptureToGraph(s, body, &inode, nullptr, 1, cudaStreamCaptureModeRelaxed));
+  LAUNCH(k_g_advance, 1, 32, 0, s, p->st, loop_h, o->maxiter, o->tol, G.cap, G.traj);
+  GCK(cudaStreamEndCapture(s, nullptr));
+  G.launches_body += 1;
+  // ---- IF(accepted): re-linearise
+  l0 = g_launches.load();
+  GCK(cudaStreamBeginCaptureToGraph(s, ifbody, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
+  GCK(cudaStreamEndCapture(s, nullptr));
+  G.launches_lin = g_launches.load() - l0;
+#undef GCK
+  p->prof = prof;
+  cudaError_t e = cudaGraphInstantiate(&G.exec, G.graph, 0);
+  if (e != cudaSuccess) { cudaGetLastError(); graph_release(p); FAIL(B200BA_ECUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
+  G.inv_w2 = inv_w2; G.tol = o->tol; G.damping = o->damping_parameter; G.maxiter = o->maxiter; G.model = p->residual_model;
+  return 0;
+}
+
+// One LM solve as one graph launch.  Returns -1 if the graph path is not available (the caller falls back to the
+// host-driven loop), otherwise a B200BA_* code.
+template <typename JT>
+static int lm_solve_graph(b200ba_plan* p, double* cam8, const double* k3, double* pts, double inv_w2,
+                          const b200ba_lm_opts* o, b200ba_lm_result* res, cudaStream_t s) {
+  auto& G = p->glm;
+  if (G.failed) return -1;
+  if (!G.exec || G.inv_w2 != inv_w2 || G.tol != o->tol || G.damping != o->damping_parameter || G.maxiter != o->maxiter ||
+      G.model != p->residual_model) {
+    CK(cudaStreamSynchronize(s));  // the capture stream is a different one: nothing of this plan may still be running
+    const int64_t l0 = g_launches.load();
+    const int rc = graph_build<JT>(p, inv_w2, o);
+    g_launches.store(l0);  // launches recorded into the graph are counted per replay below
+    if (rc) {
+      G.failed = true;
+      graph_release(p);
+      if (getenv("B200BA_VERBOSE")) fprintf(stderr, "[b200ba] graph LM unavailable (%s): host-driven loop\n", g_err.c_str());
+      return -1;
+    }
+  }
+  const int C = p->C, cap = G.cap;
+  CK(cudaMemcpyAsync(G.cam_work, cam8, (size_t)C * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  CK(cudaMemcpyAsync(G.k3_work, k3, (size_t)C * 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  pts_to4(p, pts, p->pts4, s);
+  CK(cudaGraphLaunch(G.exec, s));
+  CK(cudaMemcpyAsync(cam8, G.cam_work, (size_t)C * 8 * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  pts_from4(p, p->pts4, pts, s);
+  const size_t tbytes = (3 * (size_t)(cap + 1) + (size_t)cap) * sizeof(double);
+  CK(cudaMemcpyAsync(G.traj_host, G.traj, tbytes, cudaMemcpyDeviceToHost, s));
+  int rc = read_state(p, s);  // the ONE synchronisation of the solve
+  if (rc) return rc;
+  const SolverState& h = *p->st_host;
+  const int it = h.lm_it;
+  const double* loss_t = G.traj_host;
+  const double* grad_t = G.traj_host + (cap + 1);
+  const double* mu_t = G.traj_host + 2 * (cap + 1);
+  const int* acc_t = reinterpret_cast<const int*>(G.traj_host + 3 * (cap + 1));
+  int n_acc = 0;
+  for (int k = 0; k < it && k < cap; ++k) n_acc += acc_t[k] != 0;
+  for (int k = 0; k <= it && k <= cap; ++k) {
+    if (res->loss_trajectory_host) res->loss_trajectory_host[k] = loss_t[k];
+    if (res->grad_trajectory_host) res->grad_trajectory_host[k] = grad_t[k];
+    if (res->mu_trajectory_host) res->mu_trajectory_host[k] = mu_t[k];
+    if (k < it) {
+      if (res->pcg_iters_host) res->pcg_iters_host[k] = 0;
+      if (res->accepted_host) res->accepted_host[k] = acc_t[k];
+    }
+  }
+  g_launches += G.launches_init + (int64_t)it * G.launches_body + (int64_t)n_acc * G.launches_lin;
+  const double err = sqrt(h.grad2);
+  int status = h.status;
+  if (err > o->tol) status |= B200BA_ST_MAXITER;
+  if (!(h.loss == h.loss) || !(err == err)) status |= B200BA_ST_NAN;
+  res->iter_num = it;
+  res->status = status;
+  res->loss = h.loss;
+  res->grad_l2 = err;
+  res->damping_factor = h.mu;
+  res->increase_factor = h.nu;
+  res->n_jac_evals = 1 + n_acc;
+  res->n_res_evals = it;
+  res->n_pcg_iters_total = 0;
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
+
 extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, double* pts, double inv_w2,
                                const b200ba_lm_opts* opts, b200ba_lm_result* res, void* stream_) {
   if (!p || !cam8 || !k3 || (p->P && !pts) || !opts || !res) FAIL(B200BA_EINVAL, "lm_solve: null");
@@ -1340,6 +1579,15 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   const int C = p->C, P = p->P;
   int rc;
   res->n_jac_evals = res->n_res_evals = res->n_pcg_iters_total = 0;
+  // small scenes (dense reduced-camera path): the whole loop as ONE CUDA graph; B200BA_GRAPH=0 keeps the host-driven loop
+  if (p->dense_schur && p->nranks == 1 && !p->prof && !opts->verbose && opts->fixed_pcg_iters == 0) {
+    const char* ge = getenv("B200BA_GRAPH");
+    const bool graph_on = !(ge && !atoi(ge));
+    if (graph_on) {
+      rc = p->jac_f32 ? lm_solve_graph<float>(p, cam8, k3, pts, inv_w2, opts, res, s) : lm_solve_graph<double>(p, cam8, k3, pts, inv_w2, opts, res, s);
+      if (rc >= 0) return rc;
+    }
+  }
   // init_state (points live as 32 B records inside the solve; the caller's P x 3 array is written back at the end)
   pts_to4(p, pts, p->pts4, s);
   if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;

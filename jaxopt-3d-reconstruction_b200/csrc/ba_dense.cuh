@@ -178,7 +178,8 @@ struct DnCol<-1> {
 // One persistent cooperative launch.  Lower tiles in column-major order idx = 0, 1, ...; CTA b owns idx = b, b + G, ...
 // and processes them in that order (every dependency of a tile has a smaller idx: no cycles, all CTAs resident).
 __global__ void __launch_bounds__(DN_T)
-k_dn_factor(int T, int npad, int epoch, double* __restrict__ S, int* __restrict__ flags, SolverState* __restrict__ st) {
+k_dn_factor(int T, int npad, double* __restrict__ S, int* __restrict__ flags, SolverState* __restrict__ st) {
+  const int epoch = st->dn_epoch;  // device-side counter (k_dn_next_epoch): the launch sequence can be replayed from a CUDA graph
   __shared__ __align__(16) double As[DN_NB * DN_LD];
   __shared__ __align__(16) double Bs[DN_NB * DN_LD];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -278,7 +279,8 @@ k_dn_factor(int T, int npad, int epoch, double* __restrict__ S, int* __restrict_
 // in processing order.  vec: in/out (npad doubles); vflag[T]: block row published (epoch).
 template <bool BACKWARD>
 __global__ void __launch_bounds__(DN_T)
-k_dn_trsv(int T, int npad, int epoch, const double* __restrict__ L, double* __restrict__ vec, int* __restrict__ vflag) {
+k_dn_trsv(int T, int npad, const SolverState* __restrict__ st, const double* __restrict__ L, double* __restrict__ vec, int* __restrict__ vflag) {
+  const int epoch = st->dn_epoch;
   __shared__ double Ls[DN_NB * (DN_NB + 1)];
   __shared__ double xs[DN_NB];
   __shared__ double part[DN_T];
@@ -340,6 +342,9 @@ k_dn_trsv(int T, int npad, int epoch, const double* __restrict__ L, double* __re
   }
 }
 
+__global__ void k_dn_next_epoch(SolverState* st) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) st->dn_epoch += 1;
+}
 // rhs (C x 8) -> dense vector (padded with zeros);  solution -> slot X of the camera records
 __global__ void k_dn_load_rhs(int n, int npad, const double* __restrict__ rhs, double* __restrict__ vec) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;

@@ -21,6 +21,7 @@ struct SolverState {
   double rr_best, rr_true;
   int accepted, pcg_done, pcg_iters, status;
   int pcg_first, pcg_stop /*0 converged, 1 maxiter, 2 NaN, 3 stagnated*/, since_best, pad_;
+  int lm_it, dn_epoch;  // device-resident LM loop (CUDA graph): iterations done; epoch of the dense solver's tile flags
 };
 
 #ifndef B200BA_HOST_MATH

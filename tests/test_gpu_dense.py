@@ -108,3 +108,44 @@ def test_dense_with_a_camera_seeing_a_point_twice(monkeypatch):
     ref = bo.lm_solve(x0, sc.C, sc.P, ci, pi, ob, k3, sc.avg_cam_width)
     assert st.iter_num == ref.iter_num
     np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+
+
+@pytest.mark.parametrize("shape", ["small", "ladybug49"])
+def test_device_resident_lm_loop_equals_host_driven_loop(monkeypatch, shape):
+    """The dense path runs the whole LM loop as ONE CUDA graph (WHILE / IF conditional nodes, conditions set by kernels; no
+    host synchronisation inside the loop).  Same kernels, same order: it must reproduce the host-driven loop bit for bit —
+    iteration count, trajectories, accept pattern, parameters — and solving twice from the same plan must replay cleanly."""
+    monkeypatch.setenv("B200BA_DENSE", "1")
+    sc = b200ba.synth.make_ba_scene(shape, seed=0)
+    out = []
+    for graph in ("1", "0"):
+        monkeypatch.setenv("B200BA_GRAPH", graph)
+        ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width)
+        x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+        prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+        n0 = b200ba.launch_count()
+        params, st = ba.optimize(x0, prob, None, k3, None)
+        launches = b200ba.launch_count() - n0
+        params2, st2 = ba.optimize(x0, prob, None, k3, None)   # replay of the same graph / same plan
+        np.testing.assert_array_equal(params, params2)
+        assert st.iter_num == st2.iter_num
+        out.append((params, st, launches))
+    (pa, sa, la), (pb, sb, lb) = out
+    assert sa.iter_num == sb.iter_num and sa.status == sb.status == 0
+    np.testing.assert_array_equal(sa.loss_trajectory, sb.loss_trajectory)
+    np.testing.assert_array_equal(sa.grad_trajectory, sb.grad_trajectory)
+    np.testing.assert_array_equal(sa.mu_trajectory, sb.mu_trajectory)
+    np.testing.assert_array_equal(sa.accepted, sb.accepted)
+    np.testing.assert_array_equal(pa, pb)
+    assert sa.n_jac_evals == sb.n_jac_evals and sa.n_res_evals == sb.n_res_evals
+    assert la - lb == 1 + 2 * sa.iter_num   # the same kernels, plus the graph's bookkeeping: 1 at init, 2 per iteration (IF / WHILE conditions)
+
+
+def test_device_resident_lm_loop_respects_maxiter(monkeypatch):
+    monkeypatch.setenv("B200BA_DENSE", "1")
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    for mi in (1, 3):
+        ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, maxiter=mi)
+        x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+        params, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None)
+        assert st.iter_num == mi and (st.status & 1) and len(st.loss_trajectory) == mi + 1
