@@ -18,6 +18,7 @@
 #include "ba_pcg.cuh"
 #include "ba_cs_ring.cuh"
 #include "ba_cs_warp.cuh"
+#include "ba_cs_ringx.cuh"
 #include "ba_ps_tile.cuh"
 #include "ba_dense.cuh"
 #include "pose_kernels.cuh"
@@ -74,6 +75,8 @@ struct b200ba_plan {
   int use_warp = 0;                                                  // route the split / sigma-only camera passes to it
   int64_t NB = 0;                                                    // rows in B order incl. run padding
   int ring_slots = 0, n_sm = 0;
+  int ringx_ok = 0, ringx_D = 0, ringx_slots = 0;  // fused multi-rank camera kernel (ba_cs_ringx.cuh)
+  size_t ringx_smem = 0;
   size_t ring_smem = 0;
   int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
   int nchunks = 0, nPB = 1, block_rows = 0, max_cam_rows = 0, stash_rows = 0;
@@ -635,6 +638,29 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       if (e1 != cudaSuccess || e2 != cudaSuccess) p->ring_slots = 0;
     }
   }
+  {
+    // fused multi-rank ring kernel: the deepest camera pipeline D whose (D + 1) cameras' worth of slots (+1) fit the ring
+    int dev = 0, smem_max = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    const size_t budget = (size_t)smem_max - 1024;
+    const size_t slotb = p->jac_f32 ? RingCfg<float>::slot_bytes : RingCfg<double>::slot_bytes;
+    const int spc = std::max(1, (p->max_cam_rows + RING_R - 1) / RING_R);
+    p->ringx_ok = 0;
+    for (int D = RX_DMAX; D >= 1 && !p->ringx_ok && p->nPB <= MAXPB; --D) {
+      const size_t fixed = rx_fixed_bytes(p->nPB, D);
+      if (fixed >= budget) continue;
+      const int slots = (int)((budget - fixed) / slotb);
+      if (slots >= (D + 1) * spc + 1) {
+        p->ringx_D = D; p->ringx_slots = slots; p->ringx_smem = fixed + (size_t)slots * slotb;
+        if (cudaFuncSetAttribute(k_cs_ringx<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->ringx_smem) == cudaSuccess &&
+            cudaFuncSetAttribute(k_cs_ringx<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->ringx_smem) == cudaSuccess)
+          p->ringx_ok = 1;
+      }
+    }
+    if (const char* e = getenv("B200BA_RINGX")) if (!atoi(e)) p->ringx_ok = 0;
+    if (const char* e = getenv("B200BA_RINGX_D")) { const int v = atoi(e); if (v >= 1 && v < p->ringx_D) p->ringx_D = v; }
+  }
   lap("camera tables, B arrays, smem config");
   {
     // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk)
@@ -784,6 +810,8 @@ static struct {
   size_t ycap = 0;
   XPeers peers{};
   int nranks = 0, ok = 0, seq = 0;
+  XCam xc{};     // camera-level region (fused multi-rank ring kernel, ba_cs_ringx.cuh)
+  int cseq = 0;  // its launch sequence number
 } g_x;
 // Collective when a communicator exists: every rank first unmaps its peers' blocks, then all ranks meet (a 1-byte
 // all-gather as the barrier), and only then each rank frees its own block — no block is freed while a peer still
@@ -809,7 +837,12 @@ static int xchg_setup(int rank, int nranks, size_t need, cudaStream_t s) {
   if (nranks > X_MAXR) return 0;
   if (const char* e = getenv("B200BA_P2P")) if (!atoi(e)) return 0;
   const size_t ycap = (need + 511) & ~(size_t)511;
-  const size_t bytes = XF_INTS * sizeof(int) + 2 * ycap * sizeof(double);
+  // layout: XF_INTS flag ints | 2 x ycap doubles (vector-level exchange) | camera-level flags [nranks][Ccap] ints |
+  //         camera-level data [2][nranks][Ccap][8] doubles
+  const size_t Ccap = ycap / 8;
+  const size_t off_cflag = XF_INTS * sizeof(int) + 2 * ycap * sizeof(double);
+  const size_t off_cdata = (off_cflag + (size_t)nranks * Ccap * sizeof(int) + 63) & ~(size_t)63;
+  const size_t bytes = off_cdata + 2 * (size_t)nranks * Ccap * 8 * sizeof(double);
   int good = 1;
   cudaIpcMemHandle_t mine{};
   if (cudaMalloc((void**)&g_x.base, bytes) != cudaSuccess) { g_x.base = nullptr; good = 0; cudaGetLastError(); }
@@ -853,6 +886,10 @@ static int xchg_setup(int rank, int nranks, size_t need, cudaStream_t s) {
   g_x.ycap = ycap;
   g_x.ok = 1;
   g_x.seq = 0;
+  g_x.cseq = 0;
+  g_x.xc.flag_off = off_cflag / sizeof(int);
+  g_x.xc.data_off = off_cdata / sizeof(double);
+  g_x.xc.Ccap = (int)Ccap;
   return 0;
 }
 extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const char* uid) {
@@ -1032,6 +1069,15 @@ struct Ops {
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
     if (!p->split) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
+    } else if (p->ringx_ok && (p->nranks == 1 || p->xchg == 1)) {
+      // multi-rank: ONE launch — partial sums pushed to the peers and summed inside the kernel (ba_cs_ringx.cuh)
+      static long long timeout_ns = -1;
+      if (timeout_ns < 0) { const char* e = getenv("B200BA_XCHG_TIMEOUT_MS"); timeout_ns = (e && atol(e) > 0 ? atol(e) : 2000) * 1000000LL; }
+      const int grid = p->C < p->n_sm ? p->C : p->n_sm;
+      const int seq = ++g_x.cseq;
+      PLAUNCH(p, PC_MV_CAM, (k_cs_ringx<JT>), grid, RING_T, p->ringx_smem, s, p->C, p->nPB, CS_C | CS_UX | upd_flag | CS_A, p->ringx_slots,
+              p->ringx_D, p->st, p->camtab, p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin, p->cv, p->part2,
+              g_x.peers, g_x.xc, p->rank, p->nranks, seq, timeout_ns);
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, -1, s);
       int rc;
@@ -1196,10 +1242,14 @@ struct Ops {
 // replicated camera parts -> decide input [8],[11],[12]
 __global__ void k_pack_decide(double* scal) {
   if (threadIdx.x || blockIdx.x) return;
-  scal[11] = scal[9] + scal[13];   // vg
-  scal[12] = scal[10] + scal[14];  // vv
-  scal[9] = scal[11];
-  scal[10] = scal[12];
+  scal[9] += scal[13];   // vg
+  scal[10] += scal[14];  // vv
+}
+// multi-rank: scal[11] = 1 if this rank's peer-memory exchange timed out during the solve of this iteration; summed over
+// the ranks with the trial scalars, so that EVERY rank rejects the step and returns B200BA_ENCCL together
+__global__ void k_status_flag(const SolverState* st, double* scal) {
+  if (threadIdx.x || blockIdx.x) return;
+  scal[11] = (st->status & 8) ? 1.0 : 0.0;
 }
 
 #define DISPATCH(p, fn, ...) ((p)->jac_f32 ? Ops<float>::fn(__VA_ARGS__) : Ops<double>::fn(__VA_ARGS__))
@@ -1478,6 +1528,7 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
   if (P) LAUNCH(k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
   if ((rc = Ops<JT>::cost(p, p->cam_trial, G.k3_work, p->pts4_trial, inv_w2, p->scal + 8, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  LAUNCH(k_status_flag, 1, 1, 0, s, p->st, p->scal);
   LAUNCH(k_pack_decide, 1, 1, 0, s, p->scal);
   LAUNCH(k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
   LAUNCH(k_g_accept, 1, 32, 0, s, p->st, if_h);
@@ -1617,7 +1668,8 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
     if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts4_trial, inv_w2, p->scal + 8, s))) return rc;
     res->n_res_evals++;
-    if ((rc = allreduce(p, p->scal + 8, 3, ncclSum, s))) return rc;
+    PLAUNCH(p, PC_OTHER, k_status_flag, 1, 1, 0, s, p->st, p->scal);
+    if ((rc = allreduce(p, p->scal + 8, 4, ncclSum, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_pack_decide, 1, 1, 0, s, p->scal);
     PLAUNCH(p, PC_OTHER, k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
     PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
@@ -1641,7 +1693,8 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
       fprintf(stderr, "[b200ba] it %d loss %.9e |g| %.3e mu %.3e rho %.3e acc %d pcg %d\n", it, p->st_host->loss, err,
               p->st_host->mu, p->st_host->rho, accepted, pcg_iters);
     status |= p->st_host->status;
-    if (status & B200BA_ST_XCHG_TIMEOUT) FAIL(B200BA_ENCCL, "lm_solve: timed out waiting for a peer's partial sums (peer-memory exchange)");
+    if (status & B200BA_ST_XCHG_TIMEOUT)  // set on EVERY rank by k_lm_decide (the flag travels with the trial scalars); the step was rejected
+      FAIL(B200BA_ENCCL, "lm_solve: timed out waiting for a peer's partial sums (peer-memory exchange); parameters hold the last accepted step");
     if (!(it < opts->maxiter && err > opts->tol)) break;  // run(): NaN error also stops (NaN > tol is false)
   }
   pts_from4(p, p->pts4, pts, s);
@@ -1691,7 +1744,7 @@ extern "C" int b200ba_plan_info(b200ba_plan* p, int* out) {
   if (!p || !out) FAIL(B200BA_EINVAL, "null");
   for (int k = 0; k < 8; ++k) out[k] = 0;
   out[0] = p->use_tile; out[1] = p->tile_rows; out[2] = p->ntiles; out[3] = p->fused_lin; out[4] = p->nPB; out[5] = p->dense_schur;
-  out[6] = p->nchunks; out[7] = p->split;
+  out[6] = p->nchunks; out[7] = p->split | (p->ringx_ok << 1) | (p->ringx_D << 8);
   return B200BA_OK;
 }
 

@@ -250,9 +250,11 @@ k_cs_vec(int C, int flags, SolverState* __restrict__ st, const double* __restric
     // two-buffer invariant above holds for whatever comes next (bounded: a lost peer must not hang the GPU)
     if (threadIdx.x < nr && threadIdx.x != rank) {
       const int* f = reinterpret_cast<const int*>(px.base[rank]) + threadIdx.x;
-      const long long t0 = clock64();
+      long long t0, t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
       while (ld_acquire_sys(f) - seq < 0) {
-        if (clock64() - t0 > (5LL << 30)) { atomicOr(&st->status, 8); break; }
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 2000000000LL) { atomicOr(&st->status, 8); break; }  // 2 s of wall time; k_lm_decide then rejects on every rank
         __nanosleep(100);
       }
     }

@@ -584,6 +584,11 @@ k_reduce(const double* __restrict__ in, int n, int stride, int nout, double* __r
 // instead of the arithmetic blend.
 __global__ void k_lm_decide(SolverState* __restrict__ st, const double* __restrict__ scal) {
   if (threadIdx.x || blockIdx.x) return;
+  if (scal[3] > 0.0) {  // a rank's peer-memory exchange timed out (k_status_flag, summed over the ranks): the step was built
+    st->status |= 8;    // from incomplete sums -> reject on every rank, nothing is copied, the host returns B200BA_ENCCL
+    st->accepted = 0;
+    return;
+  }
   const double loss_next = 0.5 * scal[0];
   const double mu = st->mu;
   // delta = -v:  0.5 * delta^T (mu delta - g) = 0.5 * (mu |v|^2 + v.g)

@@ -221,6 +221,28 @@ def test_point_block_size_does_not_matter(monkeypatch):
     np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
 
 
+@pytest.mark.parametrize("ringx_d", ["1", "3", "8"])
+def test_fused_multi_rank_ring_kernel_on_one_rank(monkeypatch, ringx_d):
+    """ba_cs_ringx.cuh (the multi-rank camera kernel: partial sums exchanged inside the kernel, D cameras in flight per
+    CTA, pass A from the rows retained in shared memory) forced onto one rank: same trajectory as the single-rank ring
+    kernel, for pipeline depths 1, 3 and the maximum, on a shape with several slots per camera (ladybug49: ~650 rows)."""
+    sc, ba, x0, k3 = _setup("ladybug49", jac_f32=True)
+    out = []
+    for split in ("0", "1"):
+        monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
+        monkeypatch.setenv("B200BA_RINGX", "1")
+        monkeypatch.setenv("B200BA_RINGX_D", ringx_d)
+        prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+        info = (__import__("ctypes").c_int * 8)()
+        prob.lib.b200ba_plan_info(prob.plan, info)
+        assert (info[7] & 1) == int(split) and (info[7] & 2)
+        out.append(ba.optimize(x0, prob, None, k3, None))
+    (pa, sa), (pb, sb) = out
+    assert sa.iter_num == sb.iter_num
+    np.testing.assert_allclose(sa.loss_trajectory, sb.loss_trajectory, rtol=2e-6)
+    np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
+
+
 @pytest.mark.parametrize("cw_u", ["3", "4", "6"])
 @pytest.mark.parametrize("task_rows", ["64", "100000"])
 def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows, cw_u):
@@ -231,6 +253,7 @@ def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows, c
     out = []
     for split in ("0", "1"):
         monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
+        monkeypatch.setenv("B200BA_RINGX", "0")  # the three-launch sequence (fallback when peer memory cannot be mapped)
         monkeypatch.setenv("B200BA_TASK_ROWS", task_rows)
         monkeypatch.setenv("B200BA_CW_U", cw_u)  # all three unroll instantiations of k_cs_warp
         out.append(ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), None, k3, None))
