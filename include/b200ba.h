@@ -52,7 +52,8 @@ int b200ba_plan_set_comm(b200ba_plan* plan, int rank, int nranks, const char* un
  * principal point fixed (colmap/src/base/cost_functions.h:44-86; refine_principal_point = 0,
  * src/benchmark/colmap_benchmark/bundle_adjuster.py:25-38) run as the same pipeline over 2N rows: list every observation twice in
  * plan_create and pass (x, NaN) for its x row and (NaN, y) for its y row to plan_set_observations.  Objective
- * 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 (TrivialLoss).  EXPERIMENTAL: not yet run on a GPU. */
+ * 0.5 sum r^2 = 0.5 sum |projection - observation|^2 / w^2 (TrivialLoss).  GPU parity: tests/test_gpu_vector2.py (fp64 rows are the
+ * facade's default for this large-residual model). */
 int b200ba_plan_set_residual_model(b200ba_plan* plan, int model);
 
 /* ---- K1: residual + analytic Jacobian rows (BundleAdjustment.get_residuals,
@@ -124,6 +125,18 @@ int b200ba_cost(b200ba_plan* plan, const double* cam8, const double* cam_const3,
 int b200ba_reprojection_errors(b200ba_plan* plan, const double* cam8, const double* cam_const3,
                                const double* pts, int loss, double loss_scale, double* err_rows /*N*/,
                                double* cam_sum /*C*/, void* stream);
+
+/* ---- noise model of the benchmarks: Dataset.with_noise (src/dataset/dataset.py:43-63) applied IN PLACE to device arrays.
+ * poses: C x 12 world-to-camera [R|t], row-major; intr: C x 5 = [fx, fy, cx, cy, skew]; pts: P x 3; obs: N x 2.
+ * Every perturbation = magnitude x random unit direction in the positive orthant (dataset.py:32-41); intrinsics += U[0, intr_noise)
+ * per entry (camera.py:30-47); pose: apply_move then apply_transform_3d(from_rotvec) (camera_pose.py:93-106).  move_cameras = 0
+ * reproduces the reference as it BEHAVES (its apply_move is a no-op on W2C poses), 1 displaces the camera centre as intended.
+ * Counter-based generator: the result depends on `seed` only, not on the launch geometry.  The optional *_vec / intr_add arrays
+ * (P x 3, C x 3, C x 3, C x 5, N x 2; NULL = generate) replace the generated perturbations. */
+int b200ba_with_noise(int C, int P, int64_t N, double* poses, double* intr, double* pts, double* obs, uint64_t seed,
+                      double point3d_noise, double rot_noise, double trans_noise, double intr_noise, double point2d_noise,
+                      int move_cameras, const double* pts_vec, const double* move_vec, const double* rot_vec, const double* intr_add,
+                      const double* obs_vec, void* stream);
 
 /* ---- K4: batched single-pose LM (JaxPoseOptimizer.optimize, pose_optimization.py:86-89 =
  * jit(vmap(LevenbergMarquardt(tol=1e-7, maxiter=100, solver="cholesky").run)) over

@@ -5,5 +5,5 @@ The directory name carries a hyphen (the contract's package name), so import it 
 """
 from . import model_io, synth  # noqa: F401
 from .api import (B200BundleAdjustment, B200PoseOptimizer, BAKernels, BAProblem, LMState,  # noqa: F401
-                  LossFunction, launch_count, pose_mat_to_vec, rot_vec_to_mat, shard_points, shard_rows, unpack_params)
+                  LossFunction, launch_count, pose_mat_to_vec, rot_vec_to_mat, shard_points, shard_rows, unpack_params, with_noise)
 from ._lib import B200BAError, LIB_PATH, SYMBOLS, load  # noqa: F401

@@ -16,7 +16,7 @@ SYMBOLS = [
     "b200ba_residual_jacobian", "b200ba_lm_default_opts", "b200ba_lm_solve", "b200ba_linearize",
     "b200ba_schur_prepare", "b200ba_schur_matvec", "b200ba_schur_solve", "b200ba_cost",
     "b200ba_pose_lm_batched", "b200ba_launch_count", "b200ba_profile_enable", "b200ba_profile_get",
-    "b200ba_reprojection_errors", "b200ba_plan_set_residual_model", "b200ba_plan_info",
+    "b200ba_reprojection_errors", "b200ba_plan_set_residual_model", "b200ba_plan_info", "b200ba_with_noise",
 ]
 
 
@@ -80,6 +80,7 @@ def load():
     lib.b200ba_pose_lm_batched.argtypes = [i32, i32, vp, vp, vp, vp, vp, dbl, i32, i32, dbl, dbl,
                                            vp, vp, vp, vp, vp, vp]
     lib.b200ba_plan_info.argtypes = [vp, C.POINTER(i32)]
+    lib.b200ba_with_noise.argtypes = [i32, i32, i64, vp, vp, vp, vp, C.c_uint64, dbl, dbl, dbl, dbl, dbl, i32, vp, vp, vp, vp, vp, vp]
     lib.b200ba_profile_enable.argtypes = [vp, i32]
     lib.b200ba_profile_get.argtypes = [vp, C.POINTER(dbl), C.POINTER(i64)]
     for name in SYMBOLS:  # a stale library (older build without a newer entry point) must fail here, not at first use

@@ -549,5 +549,25 @@ class BAKernels:
         return c.value
 
 
+def with_noise(poses, intrinsics, points, observations, seed=0, point3d_noise=3e-2, camera_rotation_noise=5e-2,
+               camera_translation_noise=5e-2, camera_intrinsics_noise=10.0, point2d_noise=1.0, move_cameras=False,
+               explicit=None, device=None):
+    """`Dataset.with_noise` (src/dataset/dataset.py:43-63, same keyword names and defaults) on the GPU: returns noisy COPIES
+    (poses (C,3,4) W2C, intrinsics (C,5), points (P,3), observations (N,2)) as NumPy arrays; inputs untouched.
+    `explicit`: dict with any of pts_vec / move_vec / rot_vec / intr_add / obs_vec to replace the generated perturbations."""
+    lib = _require_cuda()
+    dev = torch.device(device if device is not None else "cuda")
+    ex = explicit or {}
+    d = [_dev(np.asarray(a, dtype=np.float64), torch.float64, dev).clone() for a in (poses, intrinsics, points, observations)]
+    e = [(_dev(np.asarray(ex[k], dtype=np.float64), torch.float64, dev) if k in ex else None)
+         for k in ("pts_vec", "move_vec", "rot_vec", "intr_add", "obs_vec")]
+    Cn, P, N = int(d[0].shape[0]), int(d[2].shape[0]), int(d[3].shape[0])
+    with torch.cuda.device(dev):
+        check(lib.b200ba_with_noise(Cn, P, N, _ptr(d[0]), _ptr(d[1]), _ptr(d[2]), _ptr(d[3]), int(seed), float(point3d_noise),
+                                    float(camera_rotation_noise), float(camera_translation_noise), float(camera_intrinsics_noise),
+                                    float(point2d_noise), int(bool(move_cameras)), *[_ptr(t) for t in e], _stream()), "with_noise")
+    return tuple(t.cpu().numpy() for t in d)
+
+
 def launch_count() -> int:
     return int(_lib.load().b200ba_launch_count())

@@ -22,6 +22,7 @@
 #include "ba_ps_tile.cuh"
 #include "ba_dense.cuh"
 #include "pose_kernels.cuh"
+#include "noise_kernels.cuh"
 
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
@@ -76,6 +77,8 @@ struct b200ba_plan {
   int64_t NB = 0;                                                    // rows in B order incl. run padding
   int ring_slots = 0, n_sm = 0;
   int ringx_ok = 0, ringx_D = 0, ringx_slots = 0;  // fused multi-rank camera kernel (ba_cs_ringx.cuh)
+  int32_t* cam_order_x = nullptr;     // its camera order: the SAME on every rank (descending GLOBAL row count)
+  std::vector<int64_t> cam_rows_host; // local rows per camera (padded), kept for that
   size_t ringx_smem = 0;
   size_t ring_smem = 0;
   int32_t *chunk_row = nullptr, *chunk_pt = nullptr;                 // point-side chunks of whole points
@@ -504,11 +507,13 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       order[c] = c;
     }
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rows[a] > rows[b]; });
+    p->cam_rows_host = rows;
     int64_t mx = 0;
     for (int c = 0; c < C; ++c) mx = rows[c] > mx ? rows[c] : mx;
     p->max_cam_rows = (int)mx;
     cudaMemcpyAsync(p->camtab, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     cudaMemcpyAsync(p->cam_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+    p->cam_order_x = p->cam_order;  // single rank; b200ba_plan_set_comm replaces it by the globally consistent order
     // Warp tasks of the split camera passes: cameras in descending size, every camera at least one task (a camera
     // without rows on this rank still has to publish a zero partial sum).  Measured rule (tools/cs_warp_probe.py,
     // one rank's share of Venice-1778 / Final-13682 at 2, 4, 8 ranks): whole cameras as tasks whenever there are
@@ -842,7 +847,7 @@ static int xchg_setup(int rank, int nranks, size_t need, cudaStream_t s) {
   const size_t Ccap = ycap / 8;
   const size_t off_cflag = XF_INTS * sizeof(int) + 2 * ycap * sizeof(double);
   const size_t off_cdata = (off_cflag + (size_t)nranks * Ccap * sizeof(int) + 63) & ~(size_t)63;
-  const size_t bytes = off_cdata + 2 * (size_t)nranks * Ccap * 8 * sizeof(double);
+  const size_t bytes = off_cdata + 2 * (size_t)nranks * Ccap * 8 * 2 * sizeof(double);  // 16 B packets
   int good = 1;
   cudaIpcMemHandle_t mine{};
   if (cudaMalloc((void**)&g_x.base, bytes) != cudaSuccess) { g_x.base = nullptr; good = 0; cudaGetLastError(); }
@@ -917,6 +922,29 @@ extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const 
     p->xchg = g_x.ok && p->use_warp;
     if (p->xchg) if (const char* e = getenv("B200BA_XSIGNAL")) if (!strcmp(e, "kernel")) p->xchg = 2;
     if (getenv("B200BA_VERBOSE")) fprintf(stderr, "[b200ba] rank %d/%d: partial sums over %s\n", rank, nranks, p->xchg ? "peer memory" : "NCCL");
+  }
+  {
+    // The fused multi-rank ring kernel waits, per camera, for the partial sums of the SAME camera from the same-numbered CTA
+    // of every peer: all ranks must walk the cameras in ONE order (a per-rank order by local row count deadlocks: rank A
+    // waits for a camera that rank B reaches only after a camera A has not reached yet).  Order: descending GLOBAL row count.
+    const int C = p->C;
+    long long* d_rows = nullptr;
+    std::vector<long long> h((size_t)C, 0);
+    for (int c = 0; c < C && c < (int)p->cam_rows_host.size(); ++c) h[c] = p->cam_rows_host[c];
+    CK(cudaMalloc((void**)&d_rows, (size_t)C * sizeof(long long)));
+    CK(cudaMemcpy(d_rows, h.data(), (size_t)C * sizeof(long long), cudaMemcpyHostToDevice));
+    CKN(ncclAllReduce(d_rows, d_rows, (size_t)C, ncclInt64, ncclSum, g_comm, nullptr));
+    CK(cudaStreamSynchronize(nullptr));
+    CK(cudaMemcpy(h.data(), d_rows, (size_t)C * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(d_rows);
+    std::vector<int32_t> order(C);
+    for (int c = 0; c < C; ++c) order[c] = c;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return h[a] > h[b]; });
+    int32_t* d_order = nullptr;
+    int rc = dalloc(p, &d_order, (size_t)C);
+    if (rc) return rc;
+    CK(cudaMemcpy(d_order, order.data(), (size_t)C * sizeof(int32_t), cudaMemcpyHostToDevice));
+    p->cam_order_x = d_order;
   }
   return B200BA_OK;
 }
@@ -1076,7 +1104,7 @@ struct Ops {
       const int grid = p->C < p->n_sm ? p->C : p->n_sm;
       const int seq = ++g_x.cseq;
       PLAUNCH(p, PC_MV_CAM, (k_cs_ringx<JT>), grid, RING_T, p->ringx_smem, s, p->C, p->nPB, CS_C | CS_UX | upd_flag | CS_A, p->ringx_slots,
-              p->ringx_D, p->st, p->camtab, p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin, p->cv, p->part2,
+              p->ringx_D, p->st, p->camtab, p->cam_order_x, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin, p->cv, p->part2,
               g_x.peers, g_x.xc, p->rank, p->nranks, seq, timeout_ns);
     } else {
       cs(p, PC_MV_CAM, CS_C | CS_WRITE_Y, -1, s);
@@ -1745,6 +1773,20 @@ extern "C" int b200ba_plan_info(b200ba_plan* p, int* out) {
   for (int k = 0; k < 8; ++k) out[k] = 0;
   out[0] = p->use_tile; out[1] = p->tile_rows; out[2] = p->ntiles; out[3] = p->fused_lin; out[4] = p->nPB; out[5] = p->dense_schur;
   out[6] = p->nchunks; out[7] = p->split | (p->ringx_ok << 1) | (p->ringx_D << 8);
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_with_noise(int C, int P, int64_t N, double* poses, double* intr, double* pts, double* obs, uint64_t seed,
+                                 double point3d_noise, double rot_noise, double trans_noise, double intr_noise, double point2d_noise,
+                                 int move_cameras, const double* pts_vec, const double* move_vec, const double* rot_vec,
+                                 const double* intr_add, const double* obs_vec, void* stream_) {
+  if (C < 0 || P < 0 || N < 0 || (C && (!poses || !intr)) || (P && !pts) || (N && !obs)) FAIL(B200BA_EINVAL, "with_noise: bad args");
+  cudaStream_t s = (cudaStream_t)stream_;
+  if (P) LAUNCH((k_noise_vec<3>), cdiv(P, 256), 256, 0, s, (int64_t)P, pts, seed, 0u, point3d_noise, pts_vec);
+  if (C) LAUNCH(k_noise_cams, cdiv(C, 128), 128, 0, s, C, poses, intr, seed, rot_noise, trans_noise, intr_noise, move_cameras, move_vec,
+                rot_vec, intr_add);
+  if (N) LAUNCH((k_noise_vec<2>), cdiv(N, 256), 256, 0, s, N, obs, seed, 4u, point2d_noise, obs_vec);
+  CK(cudaGetLastError());
   return B200BA_OK;
 }
 

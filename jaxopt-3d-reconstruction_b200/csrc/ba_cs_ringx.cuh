@@ -8,16 +8,20 @@
 // ring kernel).  Here the TMA ring of ba_cs_ring.cuh is kept — rows are read once — and every CTA keeps D cameras in
 // flight:
 //   iteration i   pass C of camera i from its ring slots (slots are NOT released), reduce, and warp 0 PUSHES the partial
-//                 8-vector into every peer's exchange block (plain stores over NVLink, then st.release.sys of a
-//                 per-(source, camera) flag carrying the launch sequence number)
-//                 finish camera i - D: warp 0 waits for that camera's flags (ld.acquire.sys; they have had D cameras'
-//                 worth of streaming time to arrive), adds the R partial vectors IN RANK ORDER (identical bits on every
+//                 8-vector into every peer's exchange block as self-validating 16 B packets (each 32-bit half of a value
+//                 travels with the launch sequence number; plain stores over NVLink, no fence)
+//                 finish camera i - D: warp 0 polls that camera's packets (they have had D cameras' worth of streaming
+//                 time to arrive), adds the R partial vectors IN RANK ORDER (identical bits on every
 //                 rank: the PCG scalars stay in lock-step without further communication), runs the camera-local update,
 //                 and all warps do pass A from the rows still sitting in shared memory; only then the slots go back to
 //                 the producer.
 // Two exchange buffers (parity of the sequence number) suffice for the same reason as in ba_cs_warp.cuh.
 // With nr == 1 (B200BA_FORCE_SPLIT on one GPU) the same pipeline runs without peers — that is how the single-GPU tests
 // cover it.
+// ORDER: the wait for camera c is a wait for the same-numbered CTA of every peer to reach camera c, so all ranks deal the
+// cameras to the CTAs in ONE order (cam_order_x: descending global row count, built in b200ba_plan_set_comm).  The first
+// version used each rank's own order (by local row count): correct on the small test scenes (<= 1 camera per CTA), a
+// circular wait — a hang until the 2 s time-outs — on Venice at 2 ranks.
 #pragma once
 #include "ba_cs_ring.cuh"
 #include "ba_cs_warp.cuh"
@@ -25,8 +29,8 @@
 #define RX_DMAX 8  // cameras in flight per CTA (bounded by the ring: (D + 1) x slots per camera + 1 <= slots)
 
 struct XCam {            // camera-level region of every rank's exchange block (same layout on all ranks)
-  size_t flag_off;       // in ints from the block base: flags[src][Ccap]
-  size_t data_off;       // in doubles from the block base: data[parity][src][Ccap][8]
+  size_t flag_off;       // (unused since the packets validate themselves)
+  size_t data_off;       // in doubles from the block base: packets[parity][src][Ccap][8] of 16 B {seq:lo32, seq:hi32}
   int Ccap;
 };
 
@@ -61,6 +65,9 @@ k_cs_ringx(int C, int nPB, int flags, int nslots, int D, SolverState* __restrict
   uint64_t* bar_cempty = bar_cfull + (RX_DMAX + 3);
   int* s_run0 = reinterpret_cast<int*>(bar_cempty + (RX_DMAX + 3));
   if (st->pcg_done) return;  // identical on every rank: nobody pushes, nobody waits
+  // a peer was lost earlier in this solve (exchange timeout): do not wait again — the PCG is being wound down
+  // (pcg_scalars stops on the status bit) and k_lm_decide rejects the step on every rank
+  const bool lost = (st->status & 8) != 0;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   __shared__ double s_scal[4];
   if (tid == 0) {
@@ -166,18 +173,19 @@ k_cs_ringx(int C, int nPB, int flags, int nslots, int D, SolverState* __restrict
         const double nk = n0 + n1;
         if (lane < 8) s_pend[(i % (RX_DMAX + 1)) * 8 + k] = nk;
         if (nr > 1) {
+          // self-validating 16 B packets {seq : low word, seq : high word} (the LL idea of NCCL): no fence, no separate flag —
+          // a __threadfence_system() here cost ~5 us per camera on the critical path of warp 0 (first version: 133 us
+          // instead of 2 x 27 us at Venice on 2 ranks).  lane = (peer slot, component k): 4 peers per pass
           const int c = rec_cam(i % NCAMX)[0];
-          // lane = (peer slot q, component k): 4 peers per pass
+          const unsigned long long bits = (unsigned long long)__double_as_longlong(nk);
+          const unsigned long long p0 = ((unsigned long long)(unsigned)seq << 32) | (bits & 0xffffffffull);
+          const unsigned long long p1 = ((unsigned long long)(unsigned)seq << 32) | (bits >> 32);
           for (int q0 = 0; q0 < nr; q0 += 4) {
             const int r = q0 + (lane >> 3);
-            if (r < nr && r != rank)
-              px.base[r][xc.data_off + (((size_t)parity * nr + rank) * xc.Ccap + c) * 8 + k] = nk;
-          }
-          __threadfence_system();
-          __syncwarp();
-          if (lane < nr && lane != rank) {
-            int* f = reinterpret_cast<int*>(px.base[lane]) + xc.flag_off + (size_t)rank * xc.Ccap + c;
-            asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f), "r"(seq) : "memory");
+            if (r < nr && r != rank) {
+              double* dst = px.base[r] + xc.data_off + ((((size_t)parity * nr + rank) * xc.Ccap + c) * 8 + k) * 2;
+              asm volatile("st.global.v2.u64 [%0], {%1,%2};" ::"l"(dst), "l"(p0), "l"(p1) : "memory");
+            }
           }
         }
       }
@@ -185,26 +193,26 @@ k_cs_ringx(int C, int nPB, int flags, int nslots, int D, SolverState* __restrict
         // ---- finish camera j = i - D: all partial sums in rank order, camera-local update, m_c
         const int j = i - D, cbj = j % NCAMX;
         const int c = rec_cam(cbj)[0];
-        if (nr > 1) {
-          if (lane < nr && lane != rank) {
-            const int* f = reinterpret_cast<const int*>(px.base[rank]) + xc.flag_off + (size_t)lane * xc.Ccap + c;
-            long long t0 = 0;
-            int spins = 0;
-            while (ld_acquire_sys(f) - seq < 0) {
-              if (++spins == 64) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-              if (spins > 64 && (spins & 63) == 0) {
-                long long t1;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                if (t1 - t0 > timeout_ns) { atomicOr(&st->status, 8); break; }
-              }
+        // every lane (k = lane & 7; the four 8-lane groups do the same work) collects component k of every rank's partial
+        // in rank order; a peer's packet is valid when both words carry this launch's sequence number
+        double nk = 0.0;
+        long long t0 = 0;
+        for (int r = 0; r < nr; ++r) {
+          if (r == rank) { nk += s_pend[(j % (RX_DMAX + 1)) * 8 + k]; continue; }
+          const double* src = px.base[rank] + xc.data_off + ((((size_t)parity * nr + r) * xc.Ccap + c) * 8 + k) * 2;
+          unsigned long long q0, q1;
+          int spins = 0;
+          for (;;) {
+            asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(q0), "=l"(q1) : "l"(src) : "memory");
+            if (((unsigned)(q0 >> 32) == (unsigned)seq && (unsigned)(q1 >> 32) == (unsigned)seq) || lost) break;
+            if (++spins == 256 && t0 == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            if (spins > 256 && (spins & 255) == 0) {
+              long long t1;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+              if (t1 - t0 > timeout_ns) { atomicOr(&st->status, 8); break; }
             }
           }
-          __syncwarp();
-        }
-        double nk = 0.0;
-        for (int r = 0; r < nr; ++r) {
-          if (r == rank) nk += s_pend[(j % (RX_DMAX + 1)) * 8 + k];
-          else nk += ld_relaxed_sys(px.base[rank] + xc.data_off + (((size_t)parity * nr + r) * xc.Ccap + c) * 8 + k);
+          nk += __longlong_as_double((long long)((q1 << 32) | (q0 & 0xffffffffull)));
         }
         const double mu = s_scal[0], alpha = s_scal[1], beta = s_scal[2];
         const double mk = cs_update(flags, k, lane, nk, rec_sv(cbj), mu, alpha, beta, cv + (size_t)CV_STRIDE * c,

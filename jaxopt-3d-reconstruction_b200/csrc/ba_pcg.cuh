@@ -222,7 +222,7 @@ __device__ __forceinline__ void pcg_scalars(int C, int it, SolverState* __restri
   if (threadIdx.x == 0) {
     const double gamma = v3[0], delta = v3[1], rr = v3[2];
     const bool conv = rr <= rtol * rtol * st->rhs2;
-    const bool bad = !(rr == rr) || !(delta == delta);
+    const bool bad = !(rr == rr) || !(delta == delta) || (st->status & 8);  // NaN, or a peer was lost (exchange timeout)
     // the recurrences of pipelined CG lose accuracy before the classical method does: no new minimum of
     // |r|^2 for PCG_STAG iterations = stagnation; the host then verifies / restarts from the true residual
     int since = st->since_best + 1;

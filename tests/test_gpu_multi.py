@@ -39,6 +39,19 @@ def test_cameras_cut_into_many_warp_tasks_multi_rank():
     _run(2, "trafalgar257", {"B200BA_TASK_ROWS": "64"})
 
 
+def test_fused_ring_kernel_needs_one_camera_order_on_all_ranks():
+    """ba_cs_ringx.cuh with pipeline depth 1 and two cameras per CTA (257 cameras, 148 CTAs): every CTA waits for its first
+    camera's peer sums before it pushes its second one.  With per-rank camera orders (the first version) this is a circular
+    wait; the order must be the global one built in b200ba_plan_set_comm."""
+    out = _run(2, "trafalgar257", {"B200BA_RINGX": "1", "B200BA_RINGX_D": "1", "B200BA_XCHG_TIMEOUT_MS": "300"})
+    assert "MULTI_GPU_OK" in out
+
+
+def test_three_launch_exchange_sequence_still_matches():
+    """B200BA_RINGX=0: partial sums | wait + vector step | sigma pass as three launches (round-1 path, the fallback)."""
+    _run(2, "ladybug49", {"B200BA_RINGX": "0"})
+
+
 def test_camera_without_rows_on_one_rank():
     _run(2, "ladybug49_gap", {})
 

@@ -3,10 +3,10 @@
 out=gpurun_out/r2i
 mkdir -p $out
 nvidia-smi --query-gpu=index,name --format=csv > $out/smi.txt
-timeout 600 python -m pytest tests/test_gpu_ba.py -m gpu -q -k "ring or split or few_rows" > $out/pytest_ba.log 2>&1; grep -E "^(FAILED|ERROR)|passed|failed" $out/pytest_ba.log | tail -8
+timeout 300 python -m pytest tests/test_gpu_noise.py -m gpu -q > $out/pytest_noise.log 2>&1; tail -3 $out/pytest_noise.log
 timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q > $out/pytest_multi.log 2>&1; grep -E "^(FAILED|ERROR)|passed|failed|MULTI" $out/pytest_multi.log | tail -12
 for rx in 1 0; do
-  B200BA_RINGX=$rx timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 9 --warmup 3 --no-pose --no-cpu-baseline > $out/bench2_rx$rx.json 2> $out/bench2_rx$rx.err
+  B200BA_RINGX=$rx timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 9 --warmup 3 --no-pose --no-cpu-baseline --no-e2e > $out/bench2_rx$rx.json 2> $out/bench2_rx$rx.err
   echo "bench2 ringx=$rx exit $?"; tail -c 400 $out/bench2_rx$rx.err
   python - $out/bench2_rx$rx.json <<'PY'
 import json,sys
