@@ -57,6 +57,7 @@ static std::atomic<int64_t> g_launches{0};
 
 static inline unsigned cdiv(int64_t a, int64_t b) { return (unsigned)((a + b - 1) / b); }
 
+struct PinnedBlock { SolverState st[2]; double scal[32]; };
 struct b200ba_plan {
   int C = 0, P = 0;
   int64_t N = 0;
@@ -130,6 +131,11 @@ struct b200ba_plan {
   double *part = nullptr, *part2 = nullptr, *partN = nullptr, *scal = nullptr;
   SolverState* st = nullptr;
   SolverState* st_host = nullptr;  // pinned
+  SolverState* st_host2 = nullptr; // pinned: second snapshot buffer of the PCG poll
+  cudaEvent_t poll_ev[2] = {nullptr, nullptr};
+  int pcg_last = 0;                // PCG iterations of the previous solve of this plan (first-chunk prediction)
+  int host_status = 0;             // status bits raised by host-side logic during a solve (merged into the result)
+  struct PinnedBlock* pinned = nullptr;
   double* scal_host = nullptr;     // pinned, 16 doubles
   int nblkN = 0, nblkP = 0;
   // comm
@@ -187,6 +193,15 @@ static cudaError_t pool_malloc(void** q, size_t bytes) {
   return cudaMallocAsync(q, bytes ? bytes : 1, g_alloc_stream);
 }
 static void pool_free(void* q) { if (q) cudaFreeAsync(q, g_alloc_stream); }
+
+static std::vector<PinnedBlock*> g_pinned_free;
+static PinnedBlock* pinned_get() {
+  if (!g_pinned_free.empty()) { PinnedBlock* b = g_pinned_free.back(); g_pinned_free.pop_back(); return b; }
+  PinnedBlock* b = nullptr;
+  if (cudaMallocHost((void**)&b, sizeof(PinnedBlock)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return b;
+}
+static void pinned_put(PinnedBlock* b) { if (b) g_pinned_free.push_back(b); }
 
 template <typename T>
 static int dalloc(b200ba_plan* p, T** ptr, size_t n) {
@@ -406,8 +421,16 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     if (pool_malloc((void**)&q, (size_t)(N ? N : 1) * 3 * p->jsz) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "alloc Jp_ps"); }
     p->allocs.push_back(q); p->Jp_ps = q;
   }
-  if (cudaMallocHost((void**)&p->st_host, sizeof(SolverState)) != cudaSuccess ||
-      cudaMallocHost((void**)&p->scal_host, 32 * sizeof(double)) != cudaSuccess) {
+  // pinned host buffers come from a process-wide free list (a plan is rebuilt per problem; cudaMallocHost costs ~0.5 ms)
+  p->pinned = pinned_get();
+  if (p->pinned) {
+    p->st_host = &p->pinned->st[0];
+    p->st_host2 = &p->pinned->st[1];
+    p->scal_host = p->pinned->scal;
+  }
+  if (!p->pinned ||
+      cudaEventCreateWithFlags(&p->poll_ev[0], cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->poll_ev[1], cudaEventDisableTiming) != cudaSuccess) {
     b200ba_plan_destroy(p);
     FAIL(B200BA_ECUDA, "cudaMallocHost failed");
   }
@@ -779,8 +802,8 @@ extern "C" int b200ba_plan_destroy(b200ba_plan* p) {
   if (p->glm.k3_work) cudaFree(p->glm.k3_work);
   if (p->glm.traj) cudaFree(p->glm.traj);
   if (p->glm.traj_host) cudaFreeHost(p->glm.traj_host);
-  if (p->st_host) cudaFreeHost(p->st_host);
-  if (p->scal_host) cudaFreeHost(p->scal_host);
+  pinned_put(p->pinned);
+  for (int k = 0; k < 2; ++k) if (p->poll_ev[k]) cudaEventDestroy(p->poll_ev[k]);
   for (cudaEvent_t e : p->ev_pool) cudaEventDestroy(e);
   delete p;
   return B200BA_OK;
@@ -1175,8 +1198,28 @@ struct Ops {
     int chunk = fixed_iters > 0 ? fixed_iters : 16;
     for (;;) {
       int done = 0;
+      // Chunks of iterations between polls of the device-side flag.  The chunk sizes are PREDICTED: the first one from the
+      // iteration count of the previous solve of this plan (consecutive LM iterations need similar counts), the following
+      // ones from the geometric decay of |r|^2 observed so far — typically two polls and one or two surplus (no-op)
+      // iterations per solve instead of 16 + 8 + 8 + ... with up to seven.  (Keeping the next chunk queued while waiting
+      // for the previous snapshot was measured and dropped: the 16 surplus launches cost more than the poll bubbles.)
+      double rr_prev = -1.0;
+      int it_prev = 0;
       while (!done && launched <= limit) {
-        const int n = (limit + 1 - launched) < chunk ? (limit + 1 - launched) : chunk;
+        int n = chunk;
+        if (fixed_iters <= 0) {
+          if (launched > 0 && rr_prev < 0.0) { rr_prev = p->st_host->rhs2; it_prev = 0; }  // |r_0|^2 = |rhs|^2
+          if (rr_prev > 0.0 && p->st_host->rr > 0.0 && p->st_host->rr < rr_prev && p->st_host->pcg_iters > it_prev) {
+            const double rate = log(p->st_host->rr / rr_prev) / (double)(p->st_host->pcg_iters - it_prev);  // < 0 per iteration
+            const double target = rt * rt * p->st_host->rhs2;
+            const double need = target > 0.0 ? log(target / p->st_host->rr) / rate : 8.0;
+            n = need < 1.0 ? 2 : need > 30.0 ? 32 : (int)need + 2;
+          } else if (launched == 0 && restarts == 0 && p->pcg_last > 12) {
+            n = p->pcg_last - 4;
+          }
+          if (launched > 0) { rr_prev = p->st_host->rr; it_prev = p->st_host->pcg_iters; }
+        }
+        n = std::min(n, limit + 1 - launched);
         for (int k = 0; k < n; ++k)
           if ((rc = pcg_iteration(p, launched + k, rt, limit, s))) return rc;
         launched += n;
@@ -1187,7 +1230,7 @@ struct Ops {
       if (fixed_iters > 0 || !done) break;
       const int stop = p->st_host->pcg_stop;
       if (stop == 1 || stop == 2 || p->st_host->rhs2 == 0.0) break;  // maxiter / NaN / zero rhs
-      if (restarts >= 6) { p->st_host->status |= 4; break; }
+      if (restarts >= 6) { p->host_status |= 4; break; }  // true residual never reached rtol: reported by lm_solve (B200BA_ST_PCG_MAXITER)
       launched = p->st_host->pcg_iters;
       // verify: y = S x, r = rhs - y, u = Minv r, |r|^2 -> done (true residual small) or restart state
       if ((rc = matvec(p, CV_X, s))) return rc;
@@ -1201,6 +1244,7 @@ struct Ops {
       ++restarts;
       chunk = 8;
     }
+    if (fixed_iters <= 0) p->pcg_last = p->st_host->pcg_iters;
     if (iters_out) *iters_out = p->st_host->pcg_iters;
     return 0;
   }
@@ -1679,6 +1723,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   if (res->mu_trajectory_host) res->mu_trajectory_host[0] = p->st_host->mu;
   int it = 0;
   int status = 0;
+  p->host_status = 0;
   while (opts->maxiter > 0) {
     // ---- update(): solve (J^T J + mu I) v = g through the reduced camera system
     int pcg_iters = 0;
@@ -1720,7 +1765,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     if (opts->verbose)
       fprintf(stderr, "[b200ba] it %d loss %.9e |g| %.3e mu %.3e rho %.3e acc %d pcg %d\n", it, p->st_host->loss, err,
               p->st_host->mu, p->st_host->rho, accepted, pcg_iters);
-    status |= p->st_host->status;
+    status |= p->st_host->status | p->host_status;
     if (status & B200BA_ST_XCHG_TIMEOUT)  // set on EVERY rank by k_lm_decide (the flag travels with the trial scalars); the step was rejected
       FAIL(B200BA_ENCCL, "lm_solve: timed out waiting for a peer's partial sums (peer-memory exchange); parameters hold the last accepted step");
     if (!(it < opts->maxiter && err > opts->tol)) break;  // run(): NaN error also stops (NaN > tol is false)
