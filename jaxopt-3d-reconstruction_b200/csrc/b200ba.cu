@@ -78,6 +78,7 @@ struct b200ba_plan {
   int64_t NB = 0;                                                    // rows in B order incl. run padding
   int ring_slots = 0, n_sm = 0;
   int ringx_ok = 0, ringx_D = 0, ringx_slots = 0;  // fused multi-rank camera kernel (ba_cs_ringx.cuh)
+  int ringx_auto = 0;                              // ... and whether the cost model prefers it for this plan
   int32_t* cam_order_x = nullptr;     // its camera order: the SAME on every rank (descending GLOBAL row count)
   std::vector<int64_t> cam_rows_host; // local rows per camera (padded), kept for that
   size_t ringx_smem = 0;
@@ -686,7 +687,14 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
           p->ringx_ok = 1;
       }
     }
-    if (const char* e = getenv("B200BA_RINGX")) if (!atoi(e)) p->ringx_ok = 0;
+    // Which camera-side scheme for the multi-rank iteration?  MEASURED (profiles/scale_r2_*.json), mv_cam + vector step per PCG
+    // iteration, fused kernel vs three-launch sequence: Venice-1778 at 2 ranks 56.9 vs 66.5 us, at 8 ranks 46.6 vs 39.7 us
+    // (357.7 vs 469.3 LM it/s); Final-13682 at 2 ranks 299 vs 235 us.  The fused kernel walks ONE camera at a time per CTA
+    // (2.4-3.9 us of per-camera latency: two CTA barriers, warp 0's reduce / push / poll of up to 7 peers / update) and only
+    // wins with few, long cameras at 2 ranks — within the run-to-run noise of the whole solve.  Default: the three-launch
+    // sequence; B200BA_RINGX=1 selects the fused kernel (kept tested: single-rank pipeline tests and 2-rank parity tests).
+    p->ringx_auto = 0;
+    if (const char* e = getenv("B200BA_RINGX")) { if (!atoi(e)) p->ringx_ok = 0; else p->ringx_auto = 1; }
     if (const char* e = getenv("B200BA_RINGX_D")) { const int v = atoi(e); if (v >= 1 && v < p->ringx_D) p->ringx_D = v; }
   }
   lap("camera tables, B arrays, smem config");
@@ -1120,7 +1128,7 @@ struct Ops {
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
     if (!p->split) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
-    } else if (p->ringx_ok && (p->nranks == 1 || p->xchg == 1)) {
+    } else if (p->ringx_ok && p->ringx_auto && (p->nranks == 1 || p->xchg == 1)) {
       // multi-rank: ONE launch — partial sums pushed to the peers and summed inside the kernel (ba_cs_ringx.cuh)
       static long long timeout_ns = -1;
       if (timeout_ns < 0) { const char* e = getenv("B200BA_XCHG_TIMEOUT_MS"); timeout_ns = (e && atol(e) > 0 ? atol(e) : 2000) * 1000000LL; }
@@ -1817,7 +1825,7 @@ extern "C" int b200ba_plan_info(b200ba_plan* p, int* out) {
   if (!p || !out) FAIL(B200BA_EINVAL, "null");
   for (int k = 0; k < 8; ++k) out[k] = 0;
   out[0] = p->use_tile; out[1] = p->tile_rows; out[2] = p->ntiles; out[3] = p->fused_lin; out[4] = p->nPB; out[5] = p->dense_schur;
-  out[6] = p->nchunks; out[7] = p->split | (p->ringx_ok << 1) | (p->ringx_D << 8);
+  out[6] = p->nchunks; out[7] = p->split | ((p->ringx_ok && p->ringx_auto) << 1) | (p->ringx_D << 8);
   return B200BA_OK;
 }
 

@@ -92,7 +92,11 @@ struct RingSteps {
       double s0 = 0.0;
 #pragma unroll
       for (int j = 0; j < 8; ++j) s0 += (double)keep[k][j] * m[j];
+#ifdef B200BA_L2HINT
+      asm volatile("st.global.L2::cache_hint.f64 [%0], %1, %2;" ::"l"(sig + pos[k]), "d"(s0), "l"(l2_policy_evict_last()) : "memory");
+#else
       sig[pos[k]] = s0;
+#endif
     }
   }
 };
@@ -167,6 +171,9 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
       }
     };
     int ring = 0, ring_ph = 0;
+#ifdef B200BA_L2HINT
+    const uint64_t pol_first = l2_policy_evict_first();
+#endif
     if (ncam > 0) issue_record(0);
     for (int i = 0; i < ncam; ++i) {
       if (i + 1 < ncam) issue_record(i + 1);
@@ -187,8 +194,13 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
             first_run = min(first_run, r);
             const size_t src = (size_t)beg[r] + (size_t)(lo - pre[r]);
             const size_t dst = (size_t)ring * RING_R + (size_t)(lo - l_lo);
+#ifdef B200BA_L2HINT
+            bulk_g2s_hint(s_rows + 8 * dst, Jc_B + 8 * src, (uint32_t)(hi - lo) * ROWB, bar_full + ring, pol_first);
+            if (flags & CS_C) bulk_g2s_hint(s_omg + dst, omg + src, (uint32_t)(hi - lo) * 8, bar_full + ring, pol_first);
+#else
             bulk_g2s(s_rows + 8 * dst, Jc_B + 8 * src, (uint32_t)(hi - lo) * ROWB, bar_full + ring);
             if (flags & CS_C) bulk_g2s(s_omg + dst, omg + src, (uint32_t)(hi - lo) * 8, bar_full + ring);
+#endif
           }
         }
 #pragma unroll

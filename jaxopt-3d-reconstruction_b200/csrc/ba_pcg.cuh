@@ -325,6 +325,31 @@ k_pcg_verify(int C, SolverState* __restrict__ st, const double* __restrict__ par
 #ifndef PS_SCATTER
 #define PS_SCATTER 2  // omega scatter: 0 = st.global, 1 = st.global.cg (L2 only), 2 = st.global.L1::no_allocate
 #endif
+#ifdef B200BA_L2HINT
+__device__ __forceinline__ double ps_gather_h(const double* p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ void ps_scatter_h(double* p, double v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.f64 [%0], %1, %2;" ::"l"(p), "d"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ float ldg_h(const float* p, uint64_t pol) {
+  float v;
+  asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ double ldg_h(const double* p, uint64_t pol) {
+  double v;
+  asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+  return v;
+}
+__device__ __forceinline__ int ldg_h(const int* p, uint64_t pol) {
+  int v;
+  asm volatile("ld.global.nc.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
+}
+#endif
 __device__ __forceinline__ double ps_gather(const double* p) {
 #if PS_GATHER == 1
   double v;
@@ -383,6 +408,9 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     __syncthreads();
   }
   if (ch >= nchunks) return;
+#ifdef B200BA_L2HINT
+  const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
+#endif
   double acc[2] = {0.0, 0.0};
   if (nrows <= CAP) {
     double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
@@ -397,10 +425,16 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
       dst[j] = 0; lp[j] = 0; s[j] = 0.0;
       b[j][0] = b[j][1] = b[j][2] = (JT)0;
       if (i < nrows) {
+#ifdef B200BA_L2HINT
+        dst[j] = ldg_h(posB + row, pol_first);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) b[j][k] = ldg_h(Jp_A + (size_t)k * N + row, pol_first);
+#else
         dst[j] = __ldg(posB + row);
-        if (!BACKSUB && !PS_OWN) lp[j] = __ldg(pt_A + row) - p0;
 #pragma unroll
         for (int k = 0; k < 3; ++k) b[j][k] = __ldg(Jp_A + (size_t)k * N + row);
+#endif
+        if (!BACKSUB && !PS_OWN) lp[j] = __ldg(pt_A + row) - p0;
       }
     }
     if (tid < npts) {
@@ -413,7 +447,11 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     }
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j)
+#ifdef B200BA_L2HINT
+      if (tid + j * PS_T < nrows) s[j] = ps_gather_h(sig + dst[j], pol_first);
+#else
       if (tid + j * PS_T < nrows) s[j] = ps_gather(sig + dst[j]);
+#endif
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j) {
       const int i = tid + j * PS_T;
@@ -450,7 +488,11 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
 #ifdef PS_DEBUG
           if (q < 0 || q >= npts || dst[j] < 0) { printf("k_ps: ch %d tid %d i %d q %d npts %d nrows %d dst %d\n", ch, tid, i, q, npts, nrows, dst[j]); q = 0; }
 #endif
+#ifdef B200BA_L2HINT
+          ps_scatter_h(omg + dst[j], ps_dot3((double)b[j][0], (double)b[j][1], (double)b[j][2], sz[0][q], sz[1][q], sz[2][q]), pol_last);
+#else
           ps_scatter(omg + dst[j], ps_dot3((double)b[j][0], (double)b[j][1], (double)b[j][2], sz[0][q], sz[1][q], sz[2][q]));
+#endif
         }
       }
     }

@@ -245,6 +245,23 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// L2 eviction-priority hints (opt-in build: -DB200BA_L2HINT): the sigma / omega exchange arrays (80 MB at Venice, written by
+// one kernel of the PCG iteration and read by the other) are stored evict_last and the streamed data (Jacobian rows, indices,
+// the exchange values once consumed) is loaded evict_first, so that the exchange stays in the 126 MB L2 between the kernels.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
 template <int NT>
 __device__ __forceinline__ void named_bar_sync(int id) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(NT) : "memory");
