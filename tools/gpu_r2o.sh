@@ -34,4 +34,5 @@ prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
 for _ in range(2): ba.optimize(x0, prob, None, k3, None)
 PY
 timeout 300 ncu --set full --clock-control none -k regex:"k_dn_factor|k_dn_assemble|k_resjac" -s 6 -c 4 -f -o $out/prof_dense python $out/dense_probe.py > $out/ncu_dense.log 2>&1
+timeout 200 python tools/e2e_breakdown.py > $out/e2e_breakdown.txt 2>&1; cat $out/e2e_breakdown.txt | tail -4
 ls -la $out | head -30
