@@ -113,6 +113,22 @@ int b200ba_schur_solve(b200ba_plan* plan, double rtol, int maxiter, double* vc, 
 int b200ba_cost(b200ba_plan* plan, const double* cam8, const double* cam_const3,
                 const double* pts, double inv_w2, double* cost_host, void* stream);
 
+/* The same trial cost WITHOUT a plan and WITHOUT any allocation, for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  This entry point has NO counterpart in the reference.
+ * cam_idx / pt_idx / obs_xy (N x 2): the observations in the caller's
+ * order, DEVICE arrays like cam8 (C x 8), cam_const3 (C x 3) and pts (P x 3); residual_model as in
+ * b200ba_plan_set_residual_model; cost_dev: ONE double in device memory, written asynchronously on `stream` (0 for N = 0).
+ * Scratch (camera tables + one partial sum per 1,024 rows) is a fixed 4.25 MiB file-scope device array that every GPU
+ * loading the library holds until exit.  LIMITS: C <= 16,384 cameras and N <= 33,554,432 observations; beyond either the
+ * call returns B200BA_EINVAL with the limit in b200ba_last_error() (use b200ba_cost with a plan).  Calls no cudaMalloc /
+ * cudaFree / allocating routine.  All calls share the scratch: calls that OVERLAP on the GPU (different streams without an
+ * ordering event) race; each call overwrites everything it reads, so nothing carries over from the previous call.  An index
+ * outside [0, C) / [0, P) makes the cost NaN instead of faulting.  The sum order differs from b200ba_cost's (caller-order
+ * blocks of 1,024 rows instead of camera runs): the two agree to rounding (~1e-13 relative), not bit for bit. */
+int b200ba_cost_noalloc(int C, int P, int64_t N, const int32_t* cam_idx, const int32_t* pt_idx,
+                        const double* obs_xy, const double* cam8, const double* cam_const3, const double* pts,
+                        double inv_w2, int residual_model, double* cost_dev, void* stream);
+
 /* ---- reprojection-error evaluator: the step after the solve that feeds every metric and plot of the reference
  * (Dataset.compute_reprojection_errors_alt, src/dataset/dataset.py:116-123, which calls
  * Camera.compute_projection_errors_alt, src/dataset/camera.py:78-85, once per camera in a Python loop).

@@ -17,6 +17,7 @@ SYMBOLS = [
     "b200ba_schur_prepare", "b200ba_schur_matvec", "b200ba_schur_solve", "b200ba_cost",
     "b200ba_pose_lm_batched", "b200ba_launch_count", "b200ba_profile_enable", "b200ba_profile_get",
     "b200ba_reprojection_errors", "b200ba_plan_set_residual_model", "b200ba_plan_info", "b200ba_with_noise",
+    "b200ba_cost_noalloc",
 ]
 
 
@@ -75,6 +76,7 @@ def load():
     lib.b200ba_schur_matvec.argtypes = [vp, vp, vp, vp]
     lib.b200ba_schur_solve.argtypes = [vp, dbl, i32, vp, vp, C.POINTER(i32), vp]
     lib.b200ba_cost.argtypes = [vp, vp, vp, vp, dbl, C.POINTER(dbl), vp]
+    lib.b200ba_cost_noalloc.argtypes = [i32, i32, i64, vp, vp, vp, vp, vp, vp, dbl, i32, vp, vp]
     lib.b200ba_plan_set_residual_model.argtypes = [vp, i32]
     lib.b200ba_reprojection_errors.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp, vp]
     lib.b200ba_pose_lm_batched.argtypes = [i32, i32, vp, vp, vp, vp, vp, dbl, i32, i32, dbl, dbl,

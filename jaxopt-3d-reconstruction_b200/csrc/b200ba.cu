@@ -1866,3 +1866,125 @@ extern "C" int b200ba_profile_get(b200ba_plan* p, double* ms_out /*[16]*/, int64
   p->recs.clear();
   return B200BA_OK;
 }
+
+// ---------------------------------------------------------------- trial cost WITHOUT any allocation
+// b200ba_cost_noalloc: 0.5 * sum r^2 at given parameters for callers that cannot call cudaMalloc (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// A plan-free variant of the trial-cost pass (k_resjac<..., false> + k_reduce, which take their
+// camera-run tables and the per-camera partial sums from plan memory): the rows are taken in the CALLER's order, and the
+// two pieces of scratch the pass needs live in ONE file-scope device array of fixed size —
+//   [0, NA_MAX_CAMS * TAB_STRIDE)        the camera tables (rotation, M, intrinsics: built once per call, read by every row)
+//   [NA_MAX_CAMS * TAB_STRIDE, + NA_MAX_PARTS)   one partial sum per NA_ROWS_PER_CTA rows (summed in a fixed order: the
+//                                        result does not depend on the launch geometry)
+// 4.25 MiB that every GPU loading the library holds until exit.  Every call fully overwrites the entries it reads (tables
+// [0, C), partials [0, ceil(N / NA_ROWS_PER_CTA))): nothing has to start at zero and the previous call's contents are never
+// read.  ALL calls share the array: two calls that overlap on the GPU (different streams, or different host threads on
+// different streams) race on it; calls on one stream, or ordered by events, are safe.
+#define NA_MAX_CAMS 16384                // Final-13682 fits
+#define NA_MAX_ROWS (int64_t(1) << 25)   // 33.5 M observations (Final-13682: 28.99 M)
+#define NA_ROWS_PER_CTA 1024
+#define NA_MAX_PARTS (int)(NA_MAX_ROWS / NA_ROWS_PER_CTA)
+#define NA_MAX_DEVICES 64
+static __device__ __align__(256) double g_na_scratch[(size_t)NA_MAX_CAMS * TAB_STRIDE + NA_MAX_PARTS];
+// host side: g_na_scratch is only a stand-in symbol here; the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current
+static double* g_na_ptr[NA_MAX_DEVICES] = {nullptr};
+static std::atomic<int> g_na_ready[NA_MAX_DEVICES];
+
+__global__ void __launch_bounds__(128)
+k_na_tables(int C, const double* __restrict__ cam8, const double* __restrict__ k3, double* __restrict__ tab) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double T[TAB_STRIDE];
+#pragma unroll
+  for (int k = 0; k < TAB_STRIDE; ++k) T[k] = 0.0;
+  build_cam_table(cam8 + 8 * (size_t)c, k3 + 3 * (size_t)c, T);
+#pragma unroll
+  for (int k = 0; k < TAB_STRIDE; ++k) tab[(size_t)c * TAB_STRIDE + k] = T[k];
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(256)
+k_na_cost(int64_t N, int C, int P, const int32_t* __restrict__ cam_idx, const int32_t* __restrict__ pt_idx,
+          const double2* __restrict__ obs, const double* __restrict__ pts, const double* __restrict__ tab, double scale,
+          double* __restrict__ parts) {
+  __shared__ double sm[32];
+  double v[1] = {0.0};
+  const int64_t base = (int64_t)blockIdx.x * NA_ROWS_PER_CTA;
+#pragma unroll
+  for (int k = 0; k < NA_ROWS_PER_CTA / 256; ++k) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    if (i >= N) break;
+    const int c = __ldg(cam_idx + i), p = __ldg(pt_idx + i);
+    if ((unsigned)c >= (unsigned)C || (unsigned)p >= (unsigned)P) {  // an index outside the arrays: poison the sum, do not fault
+      v[0] += __longlong_as_double(0x7ff8000000000000LL);
+      continue;
+    }
+    const double2 o = __ldg(obs + i);
+    const double X = __ldg(pts + 3 * (size_t)p), Y = __ldg(pts + 3 * (size_t)p + 1), Z = __ldg(pts + 3 * (size_t)p + 2);
+    const Proj pr = project(tab + (size_t)c * TAB_STRIDE, X, Y, Z);
+    double ex, ey;
+    const double r = row_residual<MODEL>(pr, o.x, o.y, scale, ex, ey);
+    v[0] += r * r;
+  }
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) parts[blockIdx.x] = v[0];
+}
+
+// 0.5 * sum of the partials, one CTA, fixed order (thread t takes parts t, t + 1024, ...; then the ordered block sum)
+__global__ void __launch_bounds__(1024)
+k_na_final(int nparts, const double* __restrict__ parts, double* __restrict__ cost_out) {
+  __shared__ double sm[32];
+  double v[1] = {0.0};
+  for (int i = threadIdx.x; i < nparts; i += 1024) v[0] += parts[i];
+  block_sum<1>(v, sm);
+  if (threadIdx.x == 0) *cost_out = 0.5 * v[0];
+}
+
+static int na_scratch(double** out) {
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NA_MAX_DEVICES) FAIL(B200BA_EINVAL, "cost_noalloc: device ordinal beyond 63");
+  if (!g_na_ready[dev].load(std::memory_order_acquire)) {
+    double* ptr = nullptr;
+    CK(cudaGetSymbolAddress((void**)&ptr, g_na_scratch));  // with `dev` current: the address of THIS device's copy
+    if (!ptr) FAIL(B200BA_ECUDA, "cost_noalloc: cudaGetSymbolAddress returned a null address");
+    g_na_ptr[dev] = ptr;  // concurrent first calls store the same value
+    g_na_ready[dev].store(1, std::memory_order_release);
+  }
+  *out = g_na_ptr[dev];
+  return B200BA_OK;
+}
+
+extern "C" int b200ba_cost_noalloc(int C, int P, int64_t N, const int32_t* cam_idx, const int32_t* pt_idx,
+                                   const double* obs_xy, const double* cam8, const double* k3, const double* pts,
+                                   double inv_w2, int residual_model, double* cost_dev, void* stream_) {
+  if (C < 0 || P < 0 || N < 0 || !cost_dev) FAIL(B200BA_EINVAL, "cost_noalloc: bad args");
+  if (residual_model != 0 && residual_model != 1) FAIL(B200BA_EINVAL, "cost_noalloc: residual model must be 0 or 1");
+  if (C > NA_MAX_CAMS)
+    FAIL(B200BA_EINVAL, "cost_noalloc: " + std::to_string(C) + " cameras exceed the fixed scratch (max " + std::to_string(NA_MAX_CAMS) +
+                            "); use b200ba_cost with a plan");
+  if (N > NA_MAX_ROWS)
+    FAIL(B200BA_EINVAL, "cost_noalloc: " + std::to_string((long long)N) + " observations exceed the fixed scratch (max " +
+                            std::to_string((long long)NA_MAX_ROWS) + "); use b200ba_cost with a plan");
+  if (N && (!cam_idx || !pt_idx || !obs_xy || !cam8 || !k3 || !pts || !C || !P)) FAIL(B200BA_EINVAL, "cost_noalloc: null data");
+  cudaStream_t s = (cudaStream_t)stream_;
+  double* scratch = nullptr;
+  int rc;
+  if ((rc = na_scratch(&scratch))) return rc;
+  double* tab = scratch;
+  double* parts = scratch + (size_t)NA_MAX_CAMS * TAB_STRIDE;
+  const int nparts = (int)((N + NA_ROWS_PER_CTA - 1) / NA_ROWS_PER_CTA);
+  if (N) {
+    LAUNCH(k_na_tables, cdiv(C, 128), 128, 0, s, C, cam8, k3, tab);
+    if (residual_model)
+      LAUNCH(k_na_cost<1>, nparts, 256, 0, s, N, C, P, cam_idx, pt_idx, reinterpret_cast<const double2*>(obs_xy), pts, tab,
+             sqrt(inv_w2), parts);
+    else
+      LAUNCH(k_na_cost<0>, nparts, 256, 0, s, N, C, P, cam_idx, pt_idx, reinterpret_cast<const double2*>(obs_xy), pts, tab,
+             inv_w2, parts);
+  }
+  LAUNCH(k_na_final, 1, 1024, 0, s, nparts, parts, cost_dev);
+  CK(cudaGetLastError());
+  return B200BA_OK;
+}
