@@ -126,7 +126,7 @@ class LMState:
 class BAProblem:
     """Problem structure resident on the GPU: plan (sorted rows, CSR, workspaces) + observations."""
 
-    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True, residual_model=0):
+    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True, residual_model=0, obs_ready=None):
         lib = _require_cuda()
         self.lib = lib
         self.C, self.P, self.N = int(C_), int(P), int(cam_idx.numel())
@@ -140,6 +140,8 @@ class BAProblem:
             self.plan = plan
             if residual_model:
                 check(lib.b200ba_plan_set_residual_model(plan, int(residual_model)), "set_residual_model")
+            if obs_ready is not None:  # the observations were uploaded on a side stream while the plan was being built
+                torch.cuda.current_stream().wait_event(obs_ready)
             check(lib.b200ba_plan_set_observations(plan, _ptr(obs), _stream()), "set_observations")
             torch.cuda.current_stream().synchronize()
 
@@ -274,7 +276,21 @@ class B200BundleAdjustment:
         dev = self.device
         cam_idx = _dev(cam_idx, torch.int32, dev)
         pt_idx = _dev(pt_idx, torch.int32, dev)
-        obs = _dev(obs, torch.float64, dev)
+        obs_ready = None
+        if (isinstance(obs, torch.Tensor) and obs.device.type == "cpu" and obs.is_pinned() and obs.dtype == torch.float64
+                and (pt_range is not None or self.world == 1) and getattr(self, "residual_model", "scalar") != "vector2"):
+            # pinned host observations (two thirds of the upload): copy them on a side stream while the plan is built from
+            # the index arrays (sorts, run tables); the plan's stream waits for the copy before it permutes them
+            if getattr(self, "_obs_stream", None) is None:
+                self._obs_stream = torch.cuda.Stream(device=dev)
+            main = torch.cuda.current_stream(dev)
+            with torch.cuda.stream(self._obs_stream):
+                obs = obs.contiguous().to(dev, non_blocking=True)
+                obs_ready = torch.cuda.Event()
+                obs_ready.record(self._obs_stream)
+            obs.record_stream(main)
+        else:
+            obs = _dev(obs, torch.float64, dev)
         P = int(points_num)
         lo, hi = 0, P
         if pt_range is not None:
@@ -291,7 +307,7 @@ class B200BundleAdjustment:
             o2 = torch.full((2 * obs.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
             o2[0::2, 0], o2[1::2, 1] = obs[:, 0], obs[:, 1]
             cam_idx, pt_idx, obs = cam_idx.repeat_interleave(2).contiguous(), pt_idx.repeat_interleave(2).contiguous(), o2
-        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32, residual_model=model)
+        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32, residual_model=model, obs_ready=obs_ready)
         prob.pt_lo, prob.pt_hi, prob.P_global = lo, hi, P
         if self.world > 1:
             self._init_comm(prob)

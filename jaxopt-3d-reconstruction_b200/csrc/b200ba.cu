@@ -366,6 +366,53 @@ static int dense_build(b200ba_plan* p, cudaStream_t s) {
   return 0;
 }
 
+// ---- point chunks of the point-side kernels, built on the device (round 1 copied pt_ptr to the host and scanned it there:
+// 2-3 ms per plan at Venice).  The rows are cut into superblocks of CHUNK_SB rows (superblock k = the points whose first
+// row lies in [k, k + 1) x CHUNK_SB: two binary searches); ONE thread walks a superblock's points and cuts greedy chunks of
+// whole points with <= cap rows and <= max_pts points (a point with more rows is a chunk of its own).  Pass 0 counts the
+// chunks of every superblock, an exclusive scan places them, pass 1 writes {first row, first point} of every chunk.
+#define CHUNK_SB 8192
+__global__ void k_chunk_greedy(int P, int64_t N, int nsb, int cap, int max_pts, const int32_t* __restrict__ pt_ptr,
+                               int32_t* __restrict__ count, const int32_t* __restrict__ offset, int32_t* __restrict__ chunk_row,
+                               int32_t* __restrict__ chunk_pt) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nsb) return;
+  auto first_point_at = [&](int64_t row) {  // first point whose first row is >= row
+    int lo = 0, hi = P;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (pt_ptr[mid] < row) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+  };
+  const int s = first_point_at((int64_t)k * CHUNK_SB);
+  const int e = (k == nsb - 1) ? P : first_point_at((int64_t)(k + 1) * CHUNK_SB);
+  int n = 0;
+  const int o = offset ? offset[k] : 0;
+  int first = s, cur = 0;
+  int r = s < e ? pt_ptr[s] : 0;
+  if (s < e) {
+    if (offset) { chunk_row[o] = r; chunk_pt[o] = s; }
+    n = 1;
+  }
+  for (int q = s; q < e; ++q) {
+    const int rn = pt_ptr[q + 1], d = rn - r;
+    if ((cur > 0 && cur + d > cap) || q - first >= max_pts) {
+      if (offset) { chunk_row[o + n] = r; chunk_pt[o + n] = q; }
+      ++n;
+      first = q;
+      cur = 0;
+    }
+    cur += d;
+    r = rn;
+  }
+  if (!offset) count[k] = n;
+  else if (k == nsb - 1) { chunk_row[o + n] = (int32_t)N; chunk_pt[o + n] = P; }  // sentinel
+}
+__global__ void k_chunk_total(int nsb, const int32_t* __restrict__ count, const int32_t* __restrict__ offset, int32_t* __restrict__ total) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *total = nsb ? offset[nsb - 1] + count[nsb - 1] : 0;
+}
+
 static int bits_for(int64_t v) {
   int b = 1;
   while ((1LL << b) <= v && b < 63) ++b;
@@ -590,7 +637,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     }
     p->use_warp = 1;
     if (const char* e = getenv("B200BA_FORCE_SPLIT")) p->split = atoi(e) != 0;  // profiling / tests: multi-rank kernel sequence on one rank
-    if (const char* e = getenv("B200BA_CS_WARP")) p->use_warp = atoi(e);
+    // (the split passes always run on the warp-task kernels: the ring kernel's half modes had shared-memory races and are unreachable)
     const size_t nb_rows = p->NB ? (size_t)p->NB : 1;
     void* q = nullptr;
     int bad_alloc = 0;
@@ -699,38 +746,52 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
   }
   lap("camera tables, B arrays, smem config");
   {
-    // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk)
+    // greedy chunks of whole points with <= cap rows and <= PS_T points (a point with more rows is its own chunk), built on
+    // the device (k_chunk_greedy); the host learns only their number
     const int cap = PS_T * PS_RPT;
-    std::vector<int32_t> hptr((size_t)P + 1), crow, cpt;
-    if ((cudaMemcpyAsync(hptr.data(), p->pt_ptr, ((size_t)P + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s), cudaStreamSynchronize(s)) != cudaSuccess) {
-      b200ba_plan_destroy(p);
-      FAIL(B200BA_ECUDA, "plan_create: pt_ptr readback");
-    }
-    crow.push_back(0);
-    cpt.push_back(0);
-    int cur = 0;
-    for (int q = 0; q < P; ++q) {
-      const int d = hptr[q + 1] - hptr[q];
-      if ((cur > 0 && cur + d > cap) || q - cpt.back() >= PS_T) {
-        crow.push_back(hptr[q]);
-        cpt.push_back(q);
-        cur = 0;
+    const int nsb = N > 0 ? (int)((N - 1) / CHUNK_SB + 1) : 0;
+    std::vector<int32_t> crow, cpt;  // host copies: only the opt-in tiled kernel wants them
+    int nch = 0;
+    if (nsb > 0) {
+      int32_t *cnt = nullptr, *off = nullptr;
+      void* tmp = nullptr;
+      size_t tmp_bytes = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, cnt, off, nsb, s);
+      cudaError_t e = pool_malloc((void**)&cnt, ((size_t)nsb + 1) * sizeof(int32_t));
+      if (e == cudaSuccess) e = pool_malloc((void**)&off, (size_t)nsb * sizeof(int32_t));
+      if (e == cudaSuccess) e = pool_malloc(&tmp, tmp_bytes);
+      if (e == cudaSuccess) {
+        LAUNCH(k_chunk_greedy, cdiv(nsb, 128), 128, 0, s, P, N, nsb, cap, PS_T, p->pt_ptr, cnt, nullptr, nullptr, nullptr);
+        cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, cnt, off, nsb, s);
+        LAUNCH(k_chunk_total, 1, 32, 0, s, nsb, cnt, off, cnt + nsb);
+        e = cudaMemcpyAsync(&nch, cnt + nsb, sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
       }
-      cur += d;
+      if (e == cudaSuccess && (dalloc(p, &p->chunk_row, (size_t)nch + 1) || dalloc(p, &p->chunk_pt, (size_t)nch + 1))) e = cudaErrorMemoryAllocation;
+      if (e == cudaSuccess) {
+        LAUNCH(k_chunk_greedy, cdiv(nsb, 128), 128, 0, s, P, N, nsb, cap, PS_T, p->pt_ptr, cnt, off, p->chunk_row, p->chunk_pt);
+        e = cudaGetLastError();
+      }
+      pool_free(cnt); pool_free(off); pool_free(tmp);
+      if (e != cudaSuccess) {
+        b200ba_plan_destroy(p);
+        FAIL(B200BA_ECUDA, std::string("plan_create: point chunks: ") + cudaGetErrorString(e));
+      }
+    } else {
+      const int32_t z[2] = {(int32_t)N, P};
+      if (dalloc(p, &p->chunk_row, 1) || dalloc(p, &p->chunk_pt, 1)) { b200ba_plan_destroy(p); return B200BA_ECUDA; }
+      cudaMemcpyAsync(p->chunk_row, &z[0], sizeof(int32_t), cudaMemcpyHostToDevice, s);
+      cudaMemcpyAsync(p->chunk_pt, &z[1], sizeof(int32_t), cudaMemcpyHostToDevice, s);
+      cudaStreamSynchronize(s);
     }
-    crow.push_back((int32_t)N);
-    cpt.push_back(P);
-    p->nchunks = (int)crow.size() - 1;
+    p->nchunks = nch;
     size_t mx = (size_t)p->nblkN;
     if ((size_t)p->nblkP > mx) mx = p->nblkP;
     if ((size_t)p->nchunks > mx) mx = p->nchunks;
-    if (dalloc(p, &p->chunk_row, crow.size()) || dalloc(p, &p->chunk_pt, cpt.size()) || dalloc(p, &p->partN, 2 * mx + 16)) {
+    if (dalloc(p, &p->partN, 2 * mx + 16)) {
       b200ba_plan_destroy(p);
       return B200BA_ECUDA;
     }
-    cudaMemcpyAsync(p->chunk_row, crow.data(), crow.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
-    cudaMemcpyAsync(p->chunk_pt, cpt.data(), cpt.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
-    cudaStreamSynchronize(s);
     lap("point chunks");
     // Tiles of the tiled point-side kernel (ba_ps_tile.cuh; opt-in, measured equal to the chunk kernel at best):
     // consecutive chunks up to tile_rows rows; needs every point to fit a tile.
@@ -739,6 +800,10 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int want = 0;
     if (const char* e = getenv("B200BA_PS_TILE")) want = N > 0 && atoi(e) != 0;
     if (want) {
+      crow.resize((size_t)p->nchunks + 1); cpt.resize((size_t)p->nchunks + 1);
+      cudaMemcpyAsync(crow.data(), p->chunk_row, crow.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+      cudaMemcpyAsync(cpt.data(), p->chunk_pt, cpt.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+      cudaStreamSynchronize(s);
       std::vector<int32_t> trow, tpt;
       trow.push_back(0); tpt.push_back(0);
       int cur = 0;
@@ -983,17 +1048,58 @@ extern "C" int b200ba_plan_set_comm(b200ba_plan* p, int rank, int nranks, const 
 // ---------------------------------------------------------------- solver steps
 // lin_scal (device, after the blocks): [0] sum r^2, [1] |g_p|^2 (both rank-local before the
 // all-reduce); scal: [2] max diag V (local), [3] |g_c|^2, [4] max diag U
-__global__ void k_lin_state(SolverState* st, const double* lin_scal, const double* scal, int init,
-                            double damping) {
-  if (threadIdx.x || blockIdx.x) return;
-  st->loss = 0.5 * lin_scal[0];
-  st->grad2 = lin_scal[1] + scal[3];
-  st->maxdiag = fmax(scal[2], scal[4]);
-  if (init) {
-    st->mu = damping * st->maxdiag;
-    st->nu = 2.0;
-    st->accepted = 0;
-    st->status = 0;
+// Scalar tail of the linearisation, ONE single-CTA launch per phase instead of five k_reduce launches, k_cam_scalars and
+// k_lin_state (at the small scenes an LM iteration is a chain of short launches: every launch saved is ~3 us).
+//   phase bit 0 (before the all-reduces): lin_scal[0] = sum r^2 (per-camera partials of k_resjac), lin_scal[1] = |g_p|^2,
+//                scal[2] = max diag V (per-CTA partials of k_point_blocks)
+//   phase bit 1 (after them): scal[3] = |g_c|^2, scal[4] = max diag U over the cameras; then the LM state: loss, |g|^2,
+//                max diag, and at init_state mu = damping * max diag
+// One rank runs both phases in one launch.  Every sum keeps the order of the generic k_reduce (thread t takes elements
+// t, t + 1024, ...; ordered block sum): results are bit-identical to the separate launches.
+__global__ void __launch_bounds__(1024)
+k_lin_reduce(int phase, int C, int nblkP, const double* __restrict__ part, const double* __restrict__ partN,
+             const double* __restrict__ U, const double* __restrict__ gc, double* __restrict__ lin_scal,
+             double* __restrict__ scal, SolverState* __restrict__ st, int init, double damping) {
+  __shared__ double sm[32];
+  if (phase & 1) {
+    const double r2 = cta_sum_strided(part, C, 1, sm);
+    const double gp2 = cta_sum_strided(partN, nblkP, 2, sm);
+    double m = -1.0;
+    for (int i = threadIdx.x; i < nblkP; i += blockDim.x) m = fmax(m, partN[2 * (size_t)i + 1]);
+    m = block_max1(m, sm);
+    if (threadIdx.x == 0) { lin_scal[0] = r2; lin_scal[1] = gp2; scal[2] = m; }
+    __syncthreads();
+  }
+  if (phase & 2) {
+    double v[1] = {0.0};
+    double m = -1.0;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      double g2 = 0.0, md = 0.0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const double g = gc[8 * (size_t)c + k];
+        g2 += g * g;
+        md = fmax(md, U[64 * (size_t)c + 9 * k]);
+      }
+      v[0] += g2;
+      m = fmax(m, md);
+    }
+    block_sum<1>(v, sm);
+    __syncthreads();
+    m = block_max1(m, sm);
+    if (threadIdx.x == 0) {
+      scal[3] = v[0];
+      scal[4] = m;
+      st->loss = 0.5 * lin_scal[0];
+      st->grad2 = lin_scal[1] + v[0];
+      st->maxdiag = fmax(scal[2], m);
+      if (init) {
+        st->mu = damping * st->maxdiag;
+        st->nu = 2.0;
+        st->accepted = 0;
+        st->status = 0;
+      }
+    }
   }
 }
 
@@ -1047,8 +1153,9 @@ static void pts_from4(b200ba_plan* p, const double* pts4, double* pts, cudaStrea
 
 template <typename JT>
 struct Ops {
-  static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
-                       cudaStream_t s) {
+  // residual + Jacobian rows + all blocks + the LM state (init != 0: init_state, mu = damping * max diag)
+  static int linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2, int init,
+                       double damping, cudaStream_t s) {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
     // K0+K1+K2b in one launch: rows, A-order records, and the camera blocks U_c / g_c (ba_kernels.cuh)
@@ -1058,16 +1165,17 @@ struct Ops {
     else
       PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 0, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
               pts4, inv_w2, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 1, 1, p->lin_scal, 0);
     if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec*)p->rec_A,
                   (JT*)p->Jp_ps, p->V, p->gp, p->partN, p->exact_grad);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->nblkP, 2, 1, p->lin_scal + 1, 0);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN + 1, p->nblkP, 2, 1, p->scal + 2, 1);
     int rc;
-    if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
-    if ((rc = allreduce(p, p->scal + 2, 1, ncclMax, s))) return rc;
-    PLAUNCH(p, PC_OTHER, k_cam_scalars, cdiv(C, 128), 128, 0, s, C, p->U, p->gc, p->part);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 3, 2);
+    if (p->nranks > 1) {
+      PLAUNCH(p, PC_OTHER, k_lin_reduce, 1, 1024, 0, s, 1, C, p->nblkP, p->part, p->partN, p->U, p->gc, p->lin_scal, p->scal, p->st, init, damping);
+      if ((rc = allreduce(p, p->U, (size_t)C * 72 + 2, ncclSum, s))) return rc;
+      if ((rc = allreduce(p, p->scal + 2, 1, ncclMax, s))) return rc;
+      PLAUNCH(p, PC_OTHER, k_lin_reduce, 1, 1024, 0, s, 2, C, p->nblkP, p->part, p->partN, p->U, p->gc, p->lin_scal, p->scal, p->st, init, damping);
+    } else {
+      PLAUNCH(p, PC_OTHER, k_lin_reduce, 1, 1024, 0, s, 3, C, p->nblkP, p->part, p->partN, p->U, p->gc, p->lin_scal, p->scal, p->st, init, damping);
+    }
     CK(cudaGetLastError());
     return 0;
   }
@@ -1305,35 +1413,93 @@ struct Ops {
     return 0;
   }
 
-  static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
-                  double* out_dev, cudaStream_t s) {
+  // per-camera sums of r^2 at trial parameters -> part[0, C)
+  static int cost_partials(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2, cudaStream_t s) {
     if (p->residual_model)
       PLAUNCH(p, PC_COST, (k_resjac<JT, 1, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
               sqrt(inv_w2), nullptr, nullptr, p->part, nullptr, nullptr, 0);
     else
       PLAUNCH(p, PC_COST, (k_resjac<JT, 0, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
               inv_w2, nullptr, nullptr, p->part, nullptr, nullptr, 0);
+    return 0;
+  }
+  static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
+                  double* out_dev, cudaStream_t s) {
+    int rc;
+    if ((rc = cost_partials(p, cam8, k3, pts4, inv_w2, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, p->C, 1, 1, out_dev, 0);
     return 0;
   }
 };
 
-// scal[8] = sum r^2 (trial), [9] = v_p.g_p, [10] = |v_p|^2 (rank-local; all-reduced), then add the
-// replicated camera parts -> decide input [8],[11],[12]
-__global__ void k_pack_decide(double* scal) {
-  if (threadIdx.x || blockIdx.x) return;
-  scal[9] += scal[13];   // vg
-  scal[10] += scal[14];  // vv
-}
-// multi-rank: scal[11] = 1 if this rank's peer-memory exchange timed out during the solve of this iteration; summed over
-// the ranks with the trial scalars, so that EVERY rank rejects the step and returns B200BA_ENCCL together
-__global__ void k_status_flag(const SolverState* st, double* scal) {
-  if (threadIdx.x || blockIdx.x) return;
+// ---- trial step, trial cost, gain-ratio decision, conditional copy: the tail of an LM iteration in few launches
+// scal[8] = sum r^2 (trial), [9] = v_p.g_p, [10] = |v_p|^2 (from the back-substitution), [11] = exchange-timeout flag —
+// rank-local, all-reduced as 4 doubles on several ranks; [13], [14] = the replicated camera parts v_c.g_c, |v_c|^2.
+// k_cost_reduce: ONE single-CTA launch for what used to be k_reduce (camera parts) + k_reduce (cost) + k_status_flag
+// (+ k_pack_decide + k_lm_decide on one rank).  Sums keep the order of the generic k_reduce: bit-identical results.
+// part: [0, C) per-camera sums of r^2 (trial-cost kernel); [2C, 4C) per-camera {v.g, |v|^2} (k_trial_cams).
+__global__ void __launch_bounds__(1024)
+k_cost_reduce(int C, const double* __restrict__ part, double* __restrict__ scal, SolverState* __restrict__ st, int decide) {
+  __shared__ double sm[32];
+  const double r2 = cta_sum_strided(part, C, 1, sm);
+  const double vg = cta_sum_strided(part + 2 * (size_t)C, C, 2, sm);
+  const double vv = cta_sum_strided(part + 2 * (size_t)C + 1, C, 2, sm);
+  if (threadIdx.x) return;
+  scal[8] = r2;
+  scal[13] = vg;
+  scal[14] = vv;
+  // multi-rank: 1 if this rank's peer-memory exchange timed out during the solve of this iteration; summed over the ranks
+  // with the trial scalars, so that EVERY rank rejects the step and returns B200BA_ENCCL together
   scal[11] = (st->status & 8) ? 1.0 : 0.0;
+  if (decide) {
+    scal[9] += vg;
+    scal[10] += vv;
+    lm_decide_body(st, scal + 8);
+  }
+}
+// several ranks: after the all-reduce of scal[8..11]
+__global__ void k_lm_decide2(SolverState* __restrict__ st, double* __restrict__ scal) {
+  if (threadIdx.x || blockIdx.x) return;
+  scal[9] += scal[13];
+  scal[10] += scal[14];
+  lm_decide_body(st, scal + 8);
+}
+// accepted step: trial parameters -> parameters, cameras and points in ONE launch; inside the device-resident loop the
+// same launch also sets the condition of the re-linearisation IF node
+__global__ void k_accept_copy2(const SolverState* __restrict__ st, int64_t nc, const double* __restrict__ cam_src,
+                               double* __restrict__ cam_dst, int64_t np, const double* __restrict__ pts_src,
+                               double* __restrict__ pts_dst, int set_cond, cudaGraphConditionalHandle if_h) {
+  const int acc = st->accepted;
+  if (set_cond && blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(if_h, acc ? 1 : 0);
+  if (!acc) return;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nc) cam_dst[i] = cam_src[i];
+  else if (i - nc < np) pts_dst[i - nc] = pts_src[i - nc];
 }
 
 #define DISPATCH(p, fn, ...) ((p)->jac_f32 ? Ops<float>::fn(__VA_ARGS__) : Ops<double>::fn(__VA_ARGS__))
 
+
+// trial parameters, trial cost, gain ratio and damping update (LevenbergMarquardt.update after the solve); cam8: current
+// camera parameters.  5 launches on one rank.
+template <typename JT>
+static int trial_decide(b200ba_plan* p, const double* cam8, const double* k3, double inv_w2, cudaStream_t s) {
+  const int C = p->C, P = p->P;
+  int rc;
+  PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part + 2 * (size_t)C);
+  if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
+  if ((rc = Ops<JT>::cost_partials(p, p->cam_trial, k3, p->pts4_trial, inv_w2, s))) return rc;
+  PLAUNCH(p, PC_OTHER, k_cost_reduce, 1, 1024, 0, s, C, p->part, p->scal, p->st, p->nranks > 1 ? 0 : 1);
+  if (p->nranks > 1) {
+    if ((rc = allreduce(p, p->scal + 8, 4, ncclSum, s))) return rc;
+    PLAUNCH(p, PC_OTHER, k_lm_decide2, 1, 1, 0, s, p->st, p->scal);
+  }
+  return 0;
+}
+static void accept_step(b200ba_plan* p, double* cam8, int set_cond, cudaGraphConditionalHandle if_h, cudaStream_t s) {
+  const int64_t nc = 8 * (int64_t)p->C, np = 4 * (int64_t)p->P;
+  PLAUNCH(p, PC_OTHER, k_accept_copy2, cdiv(nc + np, 256), 256, 0, s, p->st, nc, p->cam_trial, cam8, np, p->pts4_trial, p->pts4, set_cond, if_h);
+}
 
 extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
                                 double inv_w2, double* U, double* gc, double* V, double* gp,
@@ -1342,8 +1508,7 @@ extern "C" int b200ba_linearize(b200ba_plan* p, const double* cam8, const double
   cudaStream_t s = (cudaStream_t)stream_;
   int rc;
   pts_to4(p, pts, p->pts4, s);
-  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
-  PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, 1e-6);
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, 1, 1e-6, s))) return rc;
   if (U) CK(cudaMemcpyAsync(U, p->U, (size_t)p->C * 64 * 8, cudaMemcpyDeviceToDevice, s));
   if (gc) CK(cudaMemcpyAsync(gc, p->gc, (size_t)p->C * 8 * 8, cudaMemcpyDeviceToDevice, s));
   if (V) CK(cudaMemcpyAsync(V, p->V, (size_t)p->P * 6 * 8, cudaMemcpyDeviceToDevice, s));
@@ -1501,10 +1666,6 @@ __global__ void k_g_record0(SolverState* st, cudaGraphConditionalHandle loop_h, 
   traj[2 * (cap + 1)] = st->mu;
   cudaGraphSetConditional(loop_h, maxiter > 0 ? 1 : 0);  // run(): the first update is unconditional
 }
-__global__ void k_g_accept(const SolverState* st, cudaGraphConditionalHandle if_h) {
-  if (threadIdx.x || blockIdx.x) return;
-  cudaGraphSetConditional(if_h, st->accepted ? 1 : 0);
-}
 __global__ void k_g_advance(SolverState* st, cudaGraphConditionalHandle loop_h, int maxiter, double tol, int cap, double* traj) {
   if (threadIdx.x || blockIdx.x) return;
   const int it = st->lm_it + 1;
@@ -1559,7 +1720,7 @@ template <typename JT>
 static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   auto& G = p->glm;
   graph_release(p);
-  const int C = p->C, P = p->P;
+  const int C = p->C;
   const int cap = o->maxiter > 0 ? o->maxiter : 1;
   if (!G.cs) CK(cudaStreamCreateWithFlags(&G.cs, cudaStreamNonBlocking));
   if (!G.cam_work) {
@@ -1590,8 +1751,7 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   // ---- segment A: init_state
   int64_t l0 = g_launches.load();
   GCK(cudaStreamBeginCaptureToGraph(s, G.graph, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
-  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, o->damping_parameter);
+  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, 1, o->damping_parameter, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
   LAUNCH(k_g_record0, 1, 32, 0, s, p->st, loop_h, o->maxiter, G.cap, G.traj);
   GCK(cudaStreamEndCapture(s, nullptr));
   G.launches_init = g_launches.load() - l0;
@@ -1604,16 +1764,8 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   if (!rc) rc = Ops<JT>::dense_solve(p, s);
   if (!rc) rc = Ops<JT>::backsub(p, s);
   if (rc) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
-  LAUNCH(k_trial_cams, cdiv(C, 128), 128, 0, s, C, G.cam_work, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);
-  LAUNCH(k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
-  if (P) LAUNCH(k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
-  if ((rc = Ops<JT>::cost(p, p->cam_trial, G.k3_work, p->pts4_trial, inv_w2, p->scal + 8, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
-  LAUNCH(k_status_flag, 1, 1, 0, s, p->st, p->scal);
-  LAUNCH(k_pack_decide, 1, 1, 0, s, p->scal);
-  LAUNCH(k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
-  LAUNCH(k_g_accept, 1, 32, 0, s, p->st, if_h);
-  LAUNCH(k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, G.cam_work);
-  if (P) LAUNCH(k_accept_copy, cdiv(4 * (int64_t)P, 256), 256, 0, s, p->st, 4 * (int64_t)P, p->pts4_trial, p->pts4);
+  if ((rc = trial_decide<JT>(p, G.cam_work, G.k3_work, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
+  accept_step(p, G.cam_work, 1, if_h, s);
   GCK(cudaStreamEndCapture(s, nullptr));
   G.launches_body = g_launches.load() - l0;
   if ((rc = add_cond_node(body, cudaGraphCondTypeIf, if_h, &inode, &ifbody))) { p->prof = prof; return rc; }
@@ -1625,8 +1777,7 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   // ---- IF(accepted): re-linearise
   l0 = g_launches.load();
   GCK(cudaStreamBeginCaptureToGraph(s, ifbody, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
-  LAUNCH(k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
+  if ((rc = Ops<JT>::linearize(p, G.cam_work, G.k3_work, p->pts4, inv_w2, 0, 0.0, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
   GCK(cudaStreamEndCapture(s, nullptr));
   G.launches_lin = g_launches.load() - l0;
 #undef GCK
@@ -1707,7 +1858,6 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
                                const b200ba_lm_opts* opts, b200ba_lm_result* res, void* stream_) {
   if (!p || !cam8 || !k3 || (p->P && !pts) || !opts || !res) FAIL(B200BA_EINVAL, "lm_solve: null");
   cudaStream_t s = (cudaStream_t)stream_;
-  const int C = p->C, P = p->P;
   int rc;
   res->n_jac_evals = res->n_res_evals = res->n_pcg_iters_total = 0;
   // small scenes (dense reduced-camera path): the whole loop as ONE CUDA graph; B200BA_GRAPH=0 keeps the host-driven loop
@@ -1721,8 +1871,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
   }
   // init_state (points live as 32 B records inside the solve; the caller's P x 3 array is written back at the end)
   pts_to4(p, pts, p->pts4, s);
-  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
-  PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 1, opts->damping_parameter);
+  if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, 1, opts->damping_parameter, s))) return rc;
   if ((rc = read_state(p, s))) return rc;
   res->n_jac_evals++;
   double err = sqrt(p->st_host->grad2);
@@ -1744,22 +1893,13 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
     }
     res->n_pcg_iters_total += pcg_iters;
     if ((rc = DISPATCH(p, backsub, p, s))) return rc;
-    PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->part, C, 2, 2, p->scal + 13, 0);
-    if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
-    if ((rc = DISPATCH(p, cost, p, p->cam_trial, k3, p->pts4_trial, inv_w2, p->scal + 8, s))) return rc;
+    if ((rc = p->jac_f32 ? trial_decide<float>(p, cam8, k3, inv_w2, s) : trial_decide<double>(p, cam8, k3, inv_w2, s))) return rc;
     res->n_res_evals++;
-    PLAUNCH(p, PC_OTHER, k_status_flag, 1, 1, 0, s, p->st, p->scal);
-    if ((rc = allreduce(p, p->scal + 8, 4, ncclSum, s))) return rc;
-    PLAUNCH(p, PC_OTHER, k_pack_decide, 1, 1, 0, s, p->scal);
-    PLAUNCH(p, PC_OTHER, k_lm_decide, 1, 1, 0, s, p->st, p->scal + 8);
-    PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(8 * (int64_t)C, 256), 256, 0, s, p->st, 8 * (int64_t)C, p->cam_trial, cam8);
-    if (P) PLAUNCH(p, PC_OTHER, k_accept_copy, cdiv(4 * (int64_t)P, 256), 256, 0, s, p->st, 4 * (int64_t)P, p->pts4_trial, p->pts4);
+    accept_step(p, cam8, 0, cudaGraphConditionalHandle{}, s);
     if ((rc = read_state(p, s))) return rc;
     const int accepted = p->st_host->accepted;
     if (accepted) {
-      if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, s))) return rc;
-      PLAUNCH(p, PC_OTHER, k_lin_state, 1, 1, 0, s, p->st, p->lin_scal, p->scal, 0, 0.0);
+      if ((rc = DISPATCH(p, linearize, p, cam8, k3, p->pts4, inv_w2, 0, 0.0, s))) return rc;
       if ((rc = read_state(p, s))) return rc;
       res->n_jac_evals++;
       err = sqrt(p->st_host->grad2);

@@ -624,8 +624,7 @@ k_reduce(const double* __restrict__ in, int n, int stride, int nout, double* __r
 // scal: [0] loss_trial*2 (sum r^2), [1] vg (cams+points), [2] vv.  Gain ratio and damping update
 // exactly as jaxopt's update / update_state_using_gain_ratio, with a select
 // instead of the arithmetic blend.
-__global__ void k_lm_decide(SolverState* __restrict__ st, const double* __restrict__ scal) {
-  if (threadIdx.x || blockIdx.x) return;
+__device__ __forceinline__ void lm_decide_body(SolverState* __restrict__ st, const double* __restrict__ scal) {
   if (scal[3] > 0.0) {  // a rank's peer-memory exchange timed out (k_status_flag, summed over the ranks): the step was built
     st->status |= 8;    // from incomplete sums -> reject on every rank, nothing is copied, the host returns B200BA_ENCCL
     st->accepted = 0;
@@ -652,6 +651,10 @@ __global__ void k_lm_decide(SolverState* __restrict__ st, const double* __restri
     st->mu = mu * st->nu;
     st->nu = 2.0 * st->nu;
   }
+}
+__global__ void k_lm_decide(SolverState* __restrict__ st, const double* __restrict__ scal) {
+  if (threadIdx.x || blockIdx.x) return;
+  lm_decide_body(st, scal);
 }
 
 __global__ void k_accept_copy(const SolverState* __restrict__ st, int64_t n, const double* __restrict__ src,

@@ -138,7 +138,7 @@ def test_device_resident_lm_loop_equals_host_driven_loop(monkeypatch, shape):
     np.testing.assert_array_equal(sa.accepted, sb.accepted)
     np.testing.assert_array_equal(pa, pb)
     assert sa.n_jac_evals == sb.n_jac_evals and sa.n_res_evals == sb.n_res_evals
-    assert la - lb == 1 + 2 * sa.iter_num   # the same kernels, plus the graph's bookkeeping: 1 at init, 2 per iteration (IF / WHILE conditions)
+    assert la - lb == 1 + sa.iter_num   # the same kernels, plus the graph's bookkeeping: 1 at init, 1 per iteration (the WHILE condition; the IF condition rides on the accept copy)
 
 
 def test_device_resident_lm_loop_respects_maxiter(monkeypatch):
