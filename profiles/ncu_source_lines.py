@@ -17,7 +17,8 @@ for r in rows:
         cur["hdr"] = r; continue
     if cur is not None and r:
         cur["rows"].append(r)
-b = blocks[0]
+sub = os.environ.get('NCU_NAME_SUB')  # pick among template instantiations: substring of the demangled name
+b = [x for x in blocks if not sub or sub in x['name']][0]
 h = b["hdr"]
 isrc, isamp, iex = h.index("Source"), h.index("Warp Stall Sampling (All Samples)"), h.index("Instructions Executed")
 # line table
