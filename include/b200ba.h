@@ -56,6 +56,19 @@ int b200ba_plan_set_comm(b200ba_plan* plan, int rank, int nranks, const char* un
  * facade's default for this large-residual model). */
 int b200ba_plan_set_residual_model(b200ba_plan* plan, int model);
 
+/* The same 2-vector model under the ROBUSTIFIER the reference's COLMAP comparator selects
+ * (BundleAdjustmentOptions::CreateLossFunction, colmap/src/optim/bundle_adjustment.cc:53-68): ceres::CauchyLoss(a),
+ * rho(s) = b log(1 + s/b), or ceres::SoftLOneLoss(a), rho(s) = 2b (sqrt(1 + s/b) - 1), b = a^2, s = |projection - observation|^2 in
+ * pixels^2.  Applied as Ceres applies a loss (Triggs' correction of the residual block and its Jacobian, Corrector in Ceres'
+ * corrector.cc; both losses have rho'' < 0, where the correction is a scaling of the block and its rows by sqrt(rho'(s))); the LM
+ * loss becomes Ceres' cost 0.5 sum rho(s) / w^2.  Row contract (differs from model 1): list every observation as an ADJACENT pair
+ * of rows (x component, then y component) in plan_create (N even) and pass the FULL observation (x, y) on both rows.
+ * loss_scale: a, in pixels, > 0.  Ceres itself is an external dependency of the reference (find_package, no sources): the
+ * oracle restates its published algorithm (oracle/ba_oracle.py: ceres_rho, ceres_corrector); GPU parity tests/test_gpu_vector2.py. */
+#define B200BA_ROBUST_CAUCHY 1
+#define B200BA_ROBUST_SOFT_L1 2
+int b200ba_plan_set_robust_loss(b200ba_plan* plan, int loss, double loss_scale);
+
 /* ---- K1: residual + analytic Jacobian rows (BundleAdjustment.get_residuals,
  * bundle_adjustment.py:52-74 with reproject_point :17-21, plus the Jacobian jaxopt obtains by
  * jvp/vjp).  Outputs in the caller's ORIGINAL row order.  cam8: C x 8 = [w(3), t(3), fx, fy];

@@ -17,7 +17,7 @@ SYMBOLS = [
     "b200ba_schur_prepare", "b200ba_schur_matvec", "b200ba_schur_solve", "b200ba_cost",
     "b200ba_pose_lm_batched", "b200ba_launch_count", "b200ba_profile_enable", "b200ba_profile_get",
     "b200ba_reprojection_errors", "b200ba_plan_set_residual_model", "b200ba_plan_info", "b200ba_with_noise",
-    "b200ba_cost_noalloc",
+    "b200ba_cost_noalloc", "b200ba_plan_set_robust_loss",
 ]
 
 
@@ -78,6 +78,7 @@ def load():
     lib.b200ba_cost.argtypes = [vp, vp, vp, vp, dbl, C.POINTER(dbl), vp]
     lib.b200ba_cost_noalloc.argtypes = [i32, i32, i64, vp, vp, vp, vp, vp, vp, dbl, i32, vp, vp]
     lib.b200ba_plan_set_residual_model.argtypes = [vp, i32]
+    lib.b200ba_plan_set_robust_loss.argtypes = [vp, i32, dbl]
     lib.b200ba_reprojection_errors.argtypes = [vp, vp, vp, vp, i32, dbl, vp, vp, vp]
     lib.b200ba_pose_lm_batched.argtypes = [i32, i32, vp, vp, vp, vp, vp, dbl, i32, i32, dbl, dbl,
                                            vp, vp, vp, vp, vp, vp]

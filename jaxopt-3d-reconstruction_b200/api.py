@@ -126,7 +126,7 @@ class LMState:
 class BAProblem:
     """Problem structure resident on the GPU: plan (sorted rows, CSR, workspaces) + observations."""
 
-    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True, residual_model=0, obs_ready=None):
+    def __init__(self, C_, P, cam_idx, pt_idx, obs, device, jac_f32=True, residual_model=0, obs_ready=None, robust=None):
         lib = _require_cuda()
         self.lib = lib
         self.C, self.P, self.N = int(C_), int(P), int(cam_idx.numel())
@@ -140,6 +140,8 @@ class BAProblem:
             self.plan = plan
             if residual_model:
                 check(lib.b200ba_plan_set_residual_model(plan, int(residual_model)), "set_residual_model")
+            if robust is not None:  # (loss, scale): rows in (x, y) pairs with the full observation on both
+                check(lib.b200ba_plan_set_robust_loss(plan, {"cauchy": 1, "soft_l1": 2}[robust[0]], float(robust[1])), "set_robust_loss")
             if obs_ready is not None:  # the observations were uploaded on a side stream while the plan was being built
                 torch.cuda.current_stream().wait_event(obs_ready)
             check(lib.b200ba_plan_set_observations(plan, _ptr(obs), _stream()), "set_observations")
@@ -194,10 +196,20 @@ class B200BundleAdjustment:
 
     def __init__(self, cam_num, avg_cam_width, device=None, tol=1e-6, maxiter=100,
                  damping_parameter=1e-6, pcg_rtol=None, pcg_maxiter=1000, jac_f32=None,
-                 verbose=False, process_group=None, distributed=None, residual_model="scalar"):
+                 verbose=False, process_group=None, distributed=None, residual_model="scalar", robust_loss=None,
+                 loss_scale=1.0):
+        """residual_model: 'scalar' (the reference) or 'vector2' (the COLMAP comparator's 2-vector cost).  robust_loss (vector2
+        only): None = TrivialLoss, 'cauchy' / 'soft_l1' = ceres::CauchyLoss / SoftLOneLoss(loss_scale [pixels]) as
+        `BundleAdjustmentOptions.CreateLossFunction` selects them (colmap/src/optim/bundle_adjustment.cc:53-68)."""
         if residual_model not in ("scalar", "vector2"):
             raise ValueError("residual_model must be 'scalar' (the reference) or 'vector2' (the COLMAP comparator's cost)")
+        if robust_loss not in (None, "trivial", "cauchy", "soft_l1"):
+            raise ValueError("robust_loss must be None / 'trivial', 'cauchy' or 'soft_l1'")
+        if robust_loss in ("cauchy", "soft_l1") and residual_model != "vector2":
+            raise ValueError("robust losses belong to residual_model='vector2' (the reference's own cost has no robustifier)")
         self.residual_model = residual_model
+        self.robust_loss = None if robust_loss == "trivial" else robust_loss
+        self.loss_scale = float(loss_scale)
         if jac_f32 is None:
             # stored Jacobian rows: fp32 (fp64 accumulation) for the reference's small-residual scalar model; the 2-vector
             # model is a LARGE-residual problem whose last iterations stall on fp32 storage noise (measured: 21 LM
@@ -300,14 +312,19 @@ class B200BundleAdjustment:
             lo, hi = int(bounds[self.rank]), int(bounds[self.rank + 1])
             keep = (pt_idx >= lo) & (pt_idx < hi)
             cam_idx, pt_idx, obs = cam_idx[keep].contiguous(), (pt_idx[keep] - lo).contiguous(), obs[keep].contiguous()
-        model = 0
+        model, robust = 0, None
         if getattr(self, "residual_model", "scalar") == "vector2":
             # 2-vector model: the same pipeline over 2N rows, (x, NaN) / (NaN, y) mark the component
             model = 1
-            o2 = torch.full((2 * obs.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
-            o2[0::2, 0], o2[1::2, 1] = obs[:, 0], obs[:, 1]
+            if self.robust_loss is None:
+                o2 = torch.full((2 * obs.shape[0], 2), float("nan"), dtype=torch.float64, device=dev)
+                o2[0::2, 0], o2[1::2, 1] = obs[:, 0], obs[:, 1]
+            else:  # robust models: adjacent (x, y) row pairs, both with the full observation
+                o2 = obs.repeat_interleave(2, dim=0).contiguous()
+                robust = (self.robust_loss, self.loss_scale)
             cam_idx, pt_idx, obs = cam_idx.repeat_interleave(2).contiguous(), pt_idx.repeat_interleave(2).contiguous(), o2
-        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32, residual_model=model, obs_ready=obs_ready)
+        prob = BAProblem(self.cam_num, hi - lo, cam_idx, pt_idx, obs, dev, self.jac_f32, residual_model=model, obs_ready=obs_ready,
+                         robust=robust)
         prob.pt_lo, prob.pt_hi, prob.P_global = lo, hi, P
         if self.world > 1:
             self._init_comm(prob)

@@ -63,6 +63,7 @@ struct b200ba_plan {
   int64_t N = 0;
   int jac_f32 = 0;
   int residual_model = 0;  // 0: the reference's scalar squared error per observation; 1: 2-vector model over 2N rows (k_resjac<JT, 1, .>)
+  double loss_scale = 1.0;  // models 2 / 3 (2-vector model under Ceres' Cauchy / soft-L1 loss): the loss scale a, in pixels
   size_t jsz = 8;
   // structure (device).  A order = rows sorted by (point, camera); B order = (point block, camera, point)
   int32_t *cam_ps = nullptr, *pt_ps = nullptr, *order_ps = nullptr;  // A rows
@@ -107,6 +108,7 @@ struct b200ba_plan {
     cudaGraph_t graph = nullptr;
     double inv_w2 = 0, tol = 0, damping = 0;
     int maxiter = -1, model = -1;
+    double loss_scale = 0.0;
     int64_t launches_init = 0, launches_body = 0, launches_lin = 0;
     cudaStream_t cs = nullptr;                  // capture stream
     double *cam_work = nullptr, *k3_work = nullptr;
@@ -684,10 +686,12 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     p->fused_lin = 1;
     if (const char* e = getenv("B200BA_EXACT_GRAD")) p->exact_grad = atoi(e) != 0;
-    if (cudaFuncSetAttribute(k_resjac<float, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
-        cudaFuncSetAttribute(k_resjac<float, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
-        cudaFuncSetAttribute(k_resjac<double, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess ||
-        cudaFuncSetAttribute(k_resjac<double, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) != cudaSuccess) {
+    bool rj_ok = true;
+#define RJ_ATTR(JT, M) rj_ok = rj_ok && cudaFuncSetAttribute(k_resjac<JT, M, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RJ_TILE_BYTES) == cudaSuccess
+    RJ_ATTR(float, 0); RJ_ATTR(float, 1); RJ_ATTR(float, 2); RJ_ATTR(float, 3);
+    RJ_ATTR(double, 0); RJ_ATTR(double, 1); RJ_ATTR(double, 2); RJ_ATTR(double, 3);
+#undef RJ_ATTR
+    if (!rj_ok) {
       b200ba_plan_destroy(p);
       FAIL(B200BA_ECUDA, "plan_create: shared-memory configuration of the residual/Jacobian kernel");
     }
@@ -1159,12 +1163,17 @@ struct Ops {
     const int C = p->C, P = p->P;
     const int64_t N = p->N;
     // K0+K1+K2b in one launch: rows, A-order records, and the camera blocks U_c / g_c (ba_kernels.cuh)
-    if (p->residual_model)
-      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 1, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-              pts4, sqrt(inv_w2), (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad);
-    else
-      PLAUNCH(p, PC_RESJAC, (k_resjac<JT, 0, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA,
-              pts4, inv_w2, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad);
+    const double rho_b = p->loss_scale * p->loss_scale * inv_w2;
+#define RJ_LIN(M, SC)                                                                                                          \
+  PLAUNCH(p, PC_RESJAC, (k_resjac<JT, M, true>), C, RJ_THREADS, RJ_TILE_BYTES, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, \
+          p->posA, pts4, SC, (JT*)p->Jc_B, (RowRec*)p->rec_A, p->part, p->U, p->gc, p->exact_grad, rho_b)
+    switch (p->residual_model) {
+      case 0: RJ_LIN(0, inv_w2); break;
+      case 1: RJ_LIN(1, sqrt(inv_w2)); break;
+      case 2: RJ_LIN(2, sqrt(inv_w2)); break;
+      default: RJ_LIN(3, sqrt(inv_w2)); break;
+    }
+#undef RJ_LIN
     if (P) PLAUNCH(p, PC_PT_BLOCKS, (k_point_blocks<JT>), p->nblkP, 256, 0, s, P, (size_t)N, p->pt_ptr, (const RowRec*)p->rec_A,
                   (JT*)p->Jp_ps, p->V, p->gp, p->partN, p->exact_grad);
     int rc;
@@ -1415,12 +1424,17 @@ struct Ops {
 
   // per-camera sums of r^2 at trial parameters -> part[0, C)
   static int cost_partials(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2, cudaStream_t s) {
-    if (p->residual_model)
-      PLAUNCH(p, PC_COST, (k_resjac<JT, 1, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
-              sqrt(inv_w2), nullptr, nullptr, p->part, nullptr, nullptr, 0);
-    else
-      PLAUNCH(p, PC_COST, (k_resjac<JT, 0, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4,
-              inv_w2, nullptr, nullptr, p->part, nullptr, nullptr, 0);
+    const double rho_b = p->loss_scale * p->loss_scale * inv_w2;
+#define RJ_COST(M, SC)                                                                                                        \
+  PLAUNCH(p, PC_COST, (k_resjac<JT, M, false>), p->C, RJ_THREADS, 0, s, p->nPB, p->camtab, cam8, k3, p->pt_B, p->obs_B, p->posA, pts4, \
+          SC, nullptr, nullptr, p->part, nullptr, nullptr, 0, rho_b)
+    switch (p->residual_model) {
+      case 0: RJ_COST(0, inv_w2); break;
+      case 1: RJ_COST(1, sqrt(inv_w2)); break;
+      case 2: RJ_COST(2, sqrt(inv_w2)); break;
+      default: RJ_COST(3, sqrt(inv_w2)); break;
+    }
+#undef RJ_COST
     return 0;
   }
   static int cost(b200ba_plan* p, const double* cam8, const double* k3, const double* pts4, double inv_w2,
@@ -1615,6 +1629,16 @@ extern "C" int b200ba_plan_set_residual_model(b200ba_plan* p, int model) {
   return B200BA_OK;
 }
 
+extern "C" int b200ba_plan_set_robust_loss(b200ba_plan* p, int loss, double loss_scale) {
+  if (!p) FAIL(B200BA_EINVAL, "null plan");
+  if (loss != B200BA_ROBUST_CAUCHY && loss != B200BA_ROBUST_SOFT_L1) FAIL(B200BA_EINVAL, "set_robust_loss: loss must be 1 (Cauchy) or 2 (soft L1)");
+  if (!(loss_scale > 0.0)) FAIL(B200BA_EINVAL, "set_robust_loss: loss_scale must be > 0");
+  if (p->N & 1) FAIL(B200BA_EINVAL, "set_robust_loss: the robust models take rows in (x, y) pairs: N must be even");
+  p->residual_model = 1 + loss;  // k_resjac<JT, 2 | 3, .>
+  p->loss_scale = loss_scale;
+  return B200BA_OK;
+}
+
 extern "C" int b200ba_reprojection_errors(b200ba_plan* p, const double* cam8, const double* k3, const double* pts,
                                           int loss, double loss_scale, double* err_rows, double* cam_sum, void* stream_) {
   if (!p || !cam8 || !k3 || (p->P && !pts)) FAIL(B200BA_EINVAL, "reprojection_errors: null");
@@ -1784,7 +1808,7 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   p->prof = prof;
   cudaError_t e = cudaGraphInstantiate(&G.exec, G.graph, 0);
   if (e != cudaSuccess) { cudaGetLastError(); graph_release(p); FAIL(B200BA_ECUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
-  G.inv_w2 = inv_w2; G.tol = o->tol; G.damping = o->damping_parameter; G.maxiter = o->maxiter; G.model = p->residual_model;
+  G.inv_w2 = inv_w2; G.tol = o->tol; G.damping = o->damping_parameter; G.maxiter = o->maxiter; G.model = p->residual_model; G.loss_scale = p->loss_scale;
   return 0;
 }
 
@@ -1796,7 +1820,7 @@ static int lm_solve_graph(b200ba_plan* p, double* cam8, const double* k3, double
   auto& G = p->glm;
   if (G.failed) return -1;
   if (!G.exec || G.inv_w2 != inv_w2 || G.tol != o->tol || G.damping != o->damping_parameter || G.maxiter != o->maxiter ||
-      G.model != p->residual_model) {
+      G.model != p->residual_model || G.loss_scale != p->loss_scale) {
     CK(cudaStreamSynchronize(s));  // the capture stream is a different one: nothing of this plan may still be running
     const int64_t l0 = g_launches.load();
     const int rc = graph_build<JT>(p, inv_w2, o);

@@ -140,6 +140,34 @@ template <> __device__ __forceinline__ void strow_cvt<float>(float* p, const dou
 }
 template <> __device__ __forceinline__ void strow_cvt<double>(double* p, const double* a) { strow(p, a); }
 
+// MODEL 2 / 3: the 2-vector model under ceres::CauchyLoss(a) / ceres::SoftLOneLoss(a), the robustifiers the reference's
+// COLMAP comparator selects (colmap/src/optim/bundle_adjustment.cc:53-68), applied the way Ceres applies them: Triggs'
+// correction of the residual block and its Jacobian (Corrector, corrector.cc).  Both losses have rho'' < 0, where the
+// corrector reduces to scaling the block r = (dx, dy)/w and its Jacobian rows by sqrt(rho'(s)), s = |r|^2; the LM loss is
+// Ceres' cost 0.5 sum rho(s).  Row contract: every observation as an ADJACENT pair of rows (x component, then y), both with
+// the full observation; the stable sorts and the 4-aligned run starts of the plan keep the pair on an (even, odd) B position,
+// so the component is the parity of the row's B position.  rho_b = (a / w)^2.  cterm: the row's share of 2 x cost.
+template <int MODEL>
+__device__ __forceinline__ double robust_residual(const Proj& pr, double ox, double oy, double inv_w, double rho_b, int comp,
+                                                  double& ex, double& ey, double& cterm) {
+  const double dx = (pr.u - ox) * inv_w, dy = (pr.v - oy) * inv_w;
+  const double s = dx * dx + dy * dy;
+  const double q = s / rho_b;
+  double rho, rho1;
+  if (MODEL == 2) {
+    rho = rho_b * log1p(q);        // b log(1 + s/b)
+    rho1 = 1.0 / (1.0 + q);
+  } else {
+    const double t = sqrt(1.0 + q);
+    rho = 2.0 * s / (t + 1.0);     // 2b (sqrt(1 + s/b) - 1)
+    rho1 = 1.0 / t;
+  }
+  const double sq = sqrt(rho1);
+  cterm = 0.5 * rho;
+  ex = comp ? 0.0 : sq * inv_w;
+  ey = comp ? sq * inv_w : 0.0;
+  return sq * (comp ? dy : dx);
+}
 template <int MODEL>
 __device__ __forceinline__ double row_residual(const Proj& pr, double ox, double oy, double scale, double& ex, double& ey) {
   if (MODEL == 1) return v2_residual(pr, ox, oy, scale, ex, ey);
@@ -162,7 +190,7 @@ __global__ void __launch_bounds__(RJ_THREADS, WITH_JAC ? 3 : 4)
 k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__ cam8, const double* __restrict__ k3,
          const int32_t* __restrict__ pt_B, const double2* __restrict__ obs_B, const int32_t* __restrict__ posA,
          const double* __restrict__ pts4, double scale, JT* __restrict__ Jc_B, RowRec* __restrict__ rec_A,
-         double* __restrict__ cost_part, double* __restrict__ U, double* __restrict__ gc, int exact_grad) {
+         double* __restrict__ cost_part, double* __restrict__ U, double* __restrict__ gc, int exact_grad, double rho_b) {
   extern __shared__ __align__(128) unsigned char rj_stash_raw[];
   JT* stash = reinterpret_cast<JT*>(rj_stash_raw);
   constexpr int TILE = RJ_TILE_BYTES / (8 * (int)sizeof(JT));
@@ -197,9 +225,15 @@ k_resjac(int nPB, const int32_t* __restrict__ camtab, const double* __restrict__
       const double X = X4[0], Y = X4[1], Z = X4[2];
       const double2 o = __ldg(obs_B + j);
       const Proj pr = project(T, X, Y, Z);
-      double ex, ey;
-      const double r = row_residual<MODEL>(pr, o.x, o.y, scale, ex, ey);
-      v[0] += r * r;
+      double ex, ey, r;
+      if (MODEL >= 2) {
+        double ct;
+        r = robust_residual<MODEL>(pr, o.x, o.y, scale, rho_b, (int)(j & 1), ex, ey, ct);
+        v[0] += ct;
+      } else {
+        r = row_residual<MODEL>(pr, o.x, o.y, scale, ex, ey);
+        v[0] += r * r;
+      }
       if (WITH_JAC) {
         double a[8], b[3];
         jac_row(T, pr, X, Y, Z, ex, ey, a, b);

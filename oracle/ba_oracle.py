@@ -172,6 +172,80 @@ def ba_eval(x, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=True, model="sc
     return r, dxdy, a, b
 
 
+# ----------------------------------------------------------------------------- robustified 2-vector model
+# The reference's COLMAP comparator wraps every 2-vector residual block in a Ceres loss function chosen at
+# colmap/src/optim/bundle_adjustment.cc:53-68 (TrivialLoss / SoftLOneLoss(scale) / CauchyLoss(scale)) and Ceres applies it
+# by Triggs' correction of the residual and its Jacobian.  Ceres Solver is an EXTERNAL dependency of the reference's colmap
+# tree (colmap/CMakeLists.txt:91 `find_package(Ceres REQUIRED)`, no version pinned, sources not under /root/reference), so
+# what follows restates its PUBLISHED algorithm (include/ceres/loss_function.h: CauchyLoss / SoftLOneLoss::Evaluate;
+# internal/ceres/corrector.cc: Corrector::Corrector, CorrectResiduals, CorrectJacobian).  Parity against Ceres itself is
+# UNPINNED; the restatement is anchored by `tests/test_oracle_cpu.py` (gradient of 0.5 sum rho(s) by finite differences
+# equals J'^T r' of the corrected rows; a = infinity reproduces the plain vector2 model).
+def expand_vector2_pairs(cam_idx, pt_idx, obs):
+    """Row contract of the robust residual models (b200ba_plan_set_robust_loss): every observation as an ADJACENT pair of
+    rows (x component, then y component), both carrying the full observation (x, y)."""
+    obs = np.asarray(obs, dtype=np.float64).reshape(-1, 2)
+    return np.repeat(np.asarray(cam_idx), 2), np.repeat(np.asarray(pt_idx), 2), np.repeat(obs, 2, axis=0)
+
+
+def ceres_rho(s, loss, b):
+    """rho(s), rho'(s), rho''(s) of ceres::CauchyLoss(a) / ceres::SoftLOneLoss(a), b = a^2 (loss_function.h)."""
+    s = np.asarray(s, dtype=np.float64)
+    c = 1.0 / b
+    tot = 1.0 + s * c
+    if loss in ("cauchy", "ceres_cauchy", 1):
+        inv = 1.0 / tot
+        return b * np.log1p(s * c), inv, -c * inv * inv  # log1p: Ceres' b log(1 + s/b) without the cancellation at s << b
+    if loss in ("soft_l1", "ceres_soft_l1", 2):
+        tmp = np.sqrt(tot)
+        r1 = 1.0 / tmp
+        return 2.0 * s / (tmp + 1.0), r1, -(c * r1) / (2.0 * tot)  # = Ceres' 2b (sqrt(1 + s/b) - 1), cancellation-free
+    raise ValueError(f"unknown robust loss {loss!r}")
+
+
+def ceres_corrector(s, rho1, rho2):
+    """Corrector::Corrector (corrector.cc): (sqrt_rho1, residual_scaling, alpha_sq_norm) per residual block."""
+    sqrt_rho1 = np.sqrt(rho1)
+    simple = (s == 0.0) | (rho2 <= 0.0)
+    D = 1.0 + 2.0 * s * rho2 / rho1
+    alpha = 1.0 - np.sqrt(np.where(simple, 1.0, D))
+    res_scale = np.where(simple, sqrt_rho1, sqrt_rho1 / (1.0 - alpha))
+    alpha_sq = np.where(simple, 0.0, alpha / np.where(s == 0.0, 1.0, s))
+    return sqrt_rho1, res_scale, alpha_sq
+
+
+def ba_eval_robust(x, C, cam_idx, pt_idx, obs_pairs, cx_cy_skew, w2, loss, loss_scale, want_jac=True):
+    """Corrected rows of the robustified 2-vector model: rows in pairs from `expand_vector2_pairs`.  Residual blocks are
+    r = (projection - observation) / w (so that avg_cam_width is shared with the other models: a pixel scale `loss_scale`
+    becomes b = (loss_scale / w)^2).  Returns r' (2N,), cterm (2N,: rho(s)/2 on each row of the pair, so that the LM loss
+    0.5 * sum(cterm) = 0.5 * sum_obs rho(s), Ceres' cost), a' (2N,8), b' (2N,3)."""
+    obs_pairs = np.asarray(obs_pairs, dtype=np.float64)
+    n2 = len(obs_pairs)
+    o2 = obs_pairs.copy()
+    o2[0::2, 1] = np.nan  # even row = x component, odd row = y component
+    o2[1::2, 0] = np.nan
+    r, _, a, b = ba_eval(x, C, cam_idx, pt_idx, o2, cx_cy_skew, w2, want_jac=want_jac, model="vector2")
+    rx, ry = r[0::2], r[1::2]
+    s = rx * rx + ry * ry
+    bb = float(loss_scale) ** 2 / w2
+    rho, rho1, rho2 = ceres_rho(s, loss, bb)
+    sq, rs, asq = ceres_corrector(s, rho1, rho2)
+    rc = np.empty(n2)
+    rc[0::2], rc[1::2] = rs * rx, rs * ry
+    cterm = np.repeat(0.5 * rho, 2)
+    if not want_jac:
+        return rc, cterm, None, None
+    # CorrectJacobian: J' = sqrt_rho1 (J - alpha_sq_norm r r^T J) on the 2 x n block
+    def corr(Jm):
+        Jx, Jy = Jm[0::2], Jm[1::2]
+        rtJ = rx[:, None] * Jx + ry[:, None] * Jy
+        out = np.empty_like(Jm)
+        out[0::2] = sq[:, None] * (Jx - (asq * rx)[:, None] * rtJ)
+        out[1::2] = sq[:, None] * (Jy - (asq * ry)[:, None] * rtJ)
+        return out
+    return rc, cterm, corr(a), corr(b)
+
+
 def ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx):
     """Scatter rows into the reference's column order [C*6 | C*2 | P*3] -> CSR (N, 8C+3P)."""
     N = a.shape[0]
@@ -310,7 +384,7 @@ class LMResult:
 
 
 def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6, maxiter=100,
-             damping_parameter=1e-6, solver="exact", round_jac_f32=False, cg_tol=1e-5, model="scalar") -> LMResult:
+             damping_parameter=1e-6, solver="exact", round_jac_f32=False, cg_tol=1e-5, model="scalar", robust=None) -> LMResult:
     """jaxopt 0.7 LevenbergMarquardt.run as the reference configures it
     (bundle_adjustment.py:83-91: tol=1e-6, maxiter=100, default solver, 'grad-l2-norm' stop).
 
@@ -319,6 +393,8 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
                           normal equations, rel. tol 1e-5, maxiter 10n (`cg_tol` to tighten it)
     round_jac_f32: emulate fp32 storage of Jacobian rows (design study; gradient stays exact).
     model: 'scalar' (the reference) or 'vector2' (rows from expand_vector2: the COLMAP comparator's residual).
+    robust: None or (loss, scale) with model='vector2' and rows from expand_vector2_pairs: Ceres' CauchyLoss / SoftLOneLoss
+            applied by its corrector (ba_eval_robust); the LM loss is 0.5 * sum rho(s).
     Accept/reject uses a select instead of jaxopt's arithmetic blend."""
     cam_idx = np.asarray(cam_idx, dtype=np.int64)
     pt_idx = np.asarray(pt_idx, dtype=np.int64)
@@ -326,8 +402,21 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
     x = np.array(x0, dtype=np.float64)
     tr = LMTrace()
 
+    if robust is not None and model != "vector2":
+        raise ValueError("robust losses belong to the vector2 model")
+
+    def residual(xx, want_jac):
+        """rows r, a, b and the loss 0.5 * sum of the rows' cost terms"""
+        if robust is None:
+            r, _, a, b = ba_eval(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=want_jac, model=model)
+            return r, a, b, 0.5 * float(r @ r)
+        r, ct, a, b = ba_eval_robust(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, robust[0], robust[1], want_jac=want_jac)
+        return r, a, b, 0.5 * float(ct.sum())
+
+    cur = {}
+
     def evaluate(xx):
-        r, _, a, b = ba_eval(xx, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, model=model)
+        r, a, b, cur["loss"] = residual(xx, True)
         J = ba_jacobian_sparse(a, b, C, P, cam_idx, pt_idx)
         g = J.T @ r
         if round_jac_f32:
@@ -342,7 +431,7 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
     diag = np.asarray(J.multiply(J).sum(axis=0)).reshape(-1)
     mu = damping_parameter * float(diag.max())
     nu = 2.0
-    loss = 0.5 * float(r @ r)
+    loss = cur["loss"]
     err = float(np.linalg.norm(g))
     it = 0
     tr.loss.append(loss)
@@ -360,9 +449,8 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
             raise ValueError(solver)
         delta = -v
         x_next = x + delta
-        r_next, _, _, _ = ba_eval(x_next, C, cam_idx, pt_idx, obs, cx_cy_skew, w2, want_jac=False, model=model)
+        _, _, _, loss_next = residual(x_next, False)
         tr.n_eval_res += 1
-        loss_next = 0.5 * float(r_next @ r_next)
         rho = (loss - loss_next) / (0.5 * float(delta @ (mu * delta - g)))
         ok = bool(rho > 0.0)
         if ok:
@@ -374,7 +462,7 @@ def lm_solve(x0, C, P, cam_idx, pt_idx, obs, cx_cy_skew, avg_cam_width, tol=1e-6
             mu = mu * nu
             nu = 2.0 * nu
         it += 1
-        loss = 0.5 * float(r @ r)
+        loss = cur["loss"]
         err = float(np.linalg.norm(g))
         tr.loss.append(loss)
         tr.grad_l2.append(err)

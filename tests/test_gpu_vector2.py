@@ -62,3 +62,62 @@ def test_vector2_fp32_rows_reach_the_same_minimum_more_slowly():
     assert st.loss == pytest.approx(ref.loss, rel=2e-5) and st.loss <= ref.loss * (1 + 1e-9)   # it keeps descending a little
     rms = bo.rms_reprojection_px(x, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
     assert rms == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3), rel=1e-4)
+
+
+# ---------------------------------------------------------------- robustified solve (ceres::CauchyLoss / SoftLOneLoss)
+@pytest.mark.parametrize("loss", ["cauchy", "soft_l1"])
+@pytest.mark.parametrize("shape,scale", [("tiny", 1.0), ("small", 2.0)])
+def test_robust_rows(shape, loss, scale):
+    """Corrected rows (Triggs / Ceres corrector) and Ceres' cost 0.5 sum rho(s) against the oracle's restatement."""
+    sc = b200ba.synth.make_ba_scene(shape, seed=0)
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, jac_f32=False, residual_model="vector2", robust_loss=loss, loss_scale=scale)
+    x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+    prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+    assert prob.N == 2 * sc.N
+    xd = torch.from_numpy(x0).cuda()
+    cam8 = torch.cat([xd[:6 * sc.C].view(sc.C, 6), xd[6 * sc.C:8 * sc.C].view(sc.C, 2)], 1).contiguous()
+    r, Jc, Jp, cost = b200ba.BAKernels(prob, sc.avg_cam_width).residual_jacobian(cam8, torch.from_numpy(k3).cuda(), xd[8 * sc.C:].view(-1, 3).contiguous())
+    c2, p2, o2 = bo.expand_vector2_pairs(sc.cam_idx, sc.pt_idx, sc.obs)
+    ro, ct, a, b = bo.ba_eval_robust(x0, sc.C, c2, p2, o2, k3, sc.avg_cam_width ** 2, loss, scale)
+    np.testing.assert_allclose(r.cpu().numpy(), ro, rtol=1e-9, atol=1e-15)
+    np.testing.assert_allclose(Jc.cpu().numpy(), a, rtol=1e-9, atol=1e-12 * np.abs(a).max())
+    np.testing.assert_allclose(Jp.cpu().numpy(), b, rtol=1e-9, atol=1e-12 * np.abs(b).max())
+    assert cost == pytest.approx(0.5 * float(ct.sum()), rel=1e-12)
+    # the robustifier does something at this scale: the corrected residuals are visibly smaller than the plain ones
+    rp, _, _, _ = bo.ba_eval(x0, sc.C, *bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs), k3, sc.avg_cam_width ** 2, want_jac=False, model="vector2")
+    assert float(ro @ ro) < 0.9 * float(rp @ rp)
+
+
+@pytest.mark.parametrize("loss", ["cauchy", "soft_l1"])
+def test_robust_lm_trajectory(loss):
+    """The robustified LM solve (dense path and PCG path) against the oracle's LM on the corrected rows, cost = 0.5 sum rho."""
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    c2, p2, o2 = bo.expand_vector2_pairs(sc.cam_idx, sc.pt_idx, sc.obs)
+    ref = None
+    for dense in ("1", "0"):
+        import os
+        os.environ["B200BA_DENSE"] = dense
+        try:
+            ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, residual_model="vector2", robust_loss=loss, loss_scale=2.0, maxiter=30)
+            x0, k3 = ba.prepare_params(sc.poses0, sc.intrinsics0, sc.points0)
+            x, st = ba.optimize(x0, ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P), cx_cy_skew=k3)
+        finally:
+            os.environ.pop("B200BA_DENSE", None)
+        if ref is None:
+            ref = bo.lm_solve(x0, sc.C, sc.P, c2, p2, o2, k3, sc.avg_cam_width, model="vector2", robust=(loss, 2.0), maxiter=30)
+        assert st.iter_num == ref.iter_num
+        np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+        np.testing.assert_array_equal(st.accepted.astype(bool), np.array(ref.trace.accepted))
+        rms = bo.rms_reprojection_px(x, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3)
+        assert rms == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3), rel=1e-4)
+
+
+def test_robust_loss_argument_errors():
+    sc = b200ba.synth.make_ba_scene("tiny", seed=0)
+    with pytest.raises(ValueError):
+        b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, robust_loss="cauchy")           # scalar model has no robustifier
+    with pytest.raises(ValueError):
+        b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, residual_model="vector2", robust_loss="huber")
+    ba = b200ba.B200BundleAdjustment(sc.C, sc.avg_cam_width, residual_model="vector2", robust_loss="cauchy", loss_scale=0.0)
+    with pytest.raises(b200ba.B200BAError):
+        ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)

@@ -288,6 +288,64 @@ def test_ceres_style_losses_of_the_colmap_cost():
     np.testing.assert_allclose(l1, 8.0 * (np.sqrt(1 + s / 4.0) - 1), rtol=1e-13)   # 2 b (sqrt(1 + s/b) - 1), b = 4
 
 
+@pytest.mark.parametrize("loss", ["cauchy", "soft_l1"])
+def test_robust_corrector_restates_ceres(loss):
+    """SURVEY.md §8 f4, the robustified solve: Ceres' loss functions and corrector as restated in oracle/ba_oracle.py
+    (`ceres_rho`, `ceres_corrector`, `ba_eval_robust`).  Ceres is not under /root/reference (external dependency), so the
+    restatement is anchored on what must hold: J'^T r' of the corrected rows is the gradient of the cost 0.5 sum rho(s)
+    (torch.autograd through the literal projection chain), the per-observation cost equals the evaluator's loss codes 2 / 3,
+    a huge scale reproduces the plain vector2 rows, and the general corrector branch (rho'' > 0) agrees with its defining
+    equations."""
+    sc = b200ba.synth.make_ba_scene("tiny", seed=2)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    w, a_scale = sc.avg_cam_width, 1.5
+    c2, p2, o2 = bo.expand_vector2_pairs(sc.cam_idx, sc.pt_idx, sc.obs)
+    r, ct, a, b = bo.ba_eval_robust(x0, sc.C, c2, p2, o2, k3, w * w, loss, a_scale)
+    J = bo.ba_jacobian_sparse(a, b, sc.C, sc.P, c2.astype(np.int64), p2.astype(np.int64))
+    ci, pi, ob, kk = torch.tensor(sc.cam_idx.astype(np.int64)), torch.tensor(sc.pt_idx.astype(np.int64)), torch.tensor(sc.obs), torch.tensor(k3)
+    bb = a_scale ** 2 / (w * w)
+
+    def cost(p):
+        C = sc.C
+        cam, ff, X = p[:6 * C].reshape(-1, 6), p[6 * C:8 * C].reshape(-1, 2), p[8 * C:].reshape(-1, 3)
+        KE = torch.stack([rl.parse_intrinsics(ff[c], kk[c]) @ rl.parse_cam_pose(cam[c]) for c in range(C)])
+        q = torch.einsum("nij,nj->ni", KE[ci][:, :, :3], X[pi]) + KE[ci][:, :, 3]
+        s = (((q[:, :2] / q[:, 2:3] - ob) / w) ** 2).sum(1)
+        rho = bb * torch.log(1 + s / bb) if loss == "cauchy" else 2 * bb * (torch.sqrt(1 + s / bb) - 1)
+        return 0.5 * rho.sum()
+
+    xt = torch.tensor(x0, requires_grad=True)
+    c = cost(xt)
+    c.backward()
+    assert 0.5 * float(ct.sum()) == pytest.approx(float(c.detach()), rel=1e-12)
+    g = J.T @ r
+    np.testing.assert_allclose(g, xt.grad.numpy(), rtol=1e-8, atol=1e-12 * np.abs(g).max())
+    # per-observation cost = the evaluator's Ceres loss codes (pixels^2) / w^2
+    e, _, _ = bo.reprojection_errors(x0, sc.C, sc.cam_idx, sc.pt_idx, sc.obs, k3, "ceres_" + loss, a_scale)
+    np.testing.assert_allclose(2.0 * ct[0::2], e / (w * w), rtol=1e-12)
+    # scale -> infinity: TrivialLoss, i.e. the plain vector2 rows
+    r0, _, a0, b0 = bo.ba_eval(x0, sc.C, *bo.expand_vector2(sc.cam_idx, sc.pt_idx, sc.obs), k3, w * w, model="vector2")
+    r1, ct1, a1, b1 = bo.ba_eval_robust(x0, sc.C, c2, p2, o2, k3, w * w, loss, 1e7)
+    np.testing.assert_allclose(r1, r0, rtol=1e-9)
+    np.testing.assert_allclose(a1, a0, rtol=1e-9, atol=1e-18)
+    assert 0.5 * float(ct1.sum()) == pytest.approx(0.5 * float(r0 @ r0), rel=1e-9)
+    # corrector, general branch: residual_scaling = sqrt(rho') / (1 - alpha) with alpha the root of 0.5 alpha^2 - alpha - (rho''/rho') s = 0
+    s = np.array([0.0, 0.3, 2.0])
+    rho1, rho2 = np.array([1.0, 0.8, 0.5]), np.array([0.1, 0.2, -0.3])
+    sq, rs, asq = bo.ceres_corrector(s, rho1, rho2)
+    np.testing.assert_allclose(sq, np.sqrt(rho1))
+    alpha = asq * s
+    np.testing.assert_allclose(0.5 * alpha[1] ** 2 - alpha[1] - rho2[1] / rho1[1] * s[1], 0.0, atol=1e-15)
+    np.testing.assert_allclose(rs[1], sq[1] / (1 - alpha[1]))
+    assert asq[0] == 0.0 and rs[0] == sq[0] and asq[2] == 0.0 and rs[2] == sq[2]   # s = 0 or rho'' <= 0: plain scaling
+    # the robustified LM run decreases Ceres' cost monotonically over the accepted steps
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    c2, p2, o2 = bo.expand_vector2_pairs(sc.cam_idx, sc.pt_idx, sc.obs)
+    res = bo.lm_solve(x0, sc.C, sc.P, c2, p2, o2, k3, sc.avg_cam_width, model="vector2", robust=(loss, 2.0), maxiter=12)
+    assert np.all(np.diff(res.trace.loss)[np.array(res.trace.accepted)] < 0) and res.trace.loss[-1] < 1e-2 * res.trace.loss[0]
+
+
 def test_vector2_residual_model_vs_autodiff_of_the_projection():
     """the 2-vector residual (projection - observation)/w of COLMAP's BundleAdjustmentCostFunction
     (colmap/src/base/cost_functions.h:44-86) as 2N rows (`expand_vector2`).  Residuals and Jacobian against torch.autograd
