@@ -41,7 +41,7 @@ UNIT = "LM iterations/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=14)
+    ap.add_argument("--steps", type=int, default=18)  # Venice-1778 from the benchmark start: 9 LM iterations per solve -> two whole solves
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="venice1778")
@@ -382,9 +382,14 @@ def ba_workload(D, b200ba, args, workload, steps, warmup, want_e2e, want_kernels
         # ---- end to end through the public API with HOST buffers (H2D of this rank's rows + parameters, D2H of parameters).
         # One untimed warm-up solve through the same API first: the first plan built next to the resident one grows the
         # stream-ordered memory pool (a one-off of tens of ms that is not part of the steady state).
-        pr = ba.build_problem_sparse(h_cam, h_pt, h_obs, sc.P, pt_range=pt_range)
-        ba.optimize(h_x0, pr, None, h_k3, None)
-        pr.close()
+        # Two warm-up solves, their results held exactly like the timed loop holds them: the result comes back in a pinned
+        # host buffer, and with the previous result still referenced the caching host allocator needs TWO blocks before it
+        # stops calling cudaHostAlloc (12 ms for Venice's 24 MB) — steady state from the third solve on.
+        params = None
+        for _ in range(2):
+            pr = ba.build_problem_sparse(h_cam, h_pt, h_obs, sc.P, pt_range=pt_range)
+            params, st = ba.optimize(h_x0, pr, None, h_k3, None)
+            pr.close()
         D.barrier()
         t0 = time.perf_counter()
         its, h2d, d2h, nsolves, trajs = 0, 0, 0, 0, []
@@ -403,7 +408,7 @@ def ba_workload(D, b200ba, args, workload, steps, warmup, want_e2e, want_kernels
         t_e2e = D.max_over_ranks((time.perf_counter() - t0) * 1e3) * 1e-3
         out["e2e"] = {"value": its / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d / max(its, 1)),
                       "d2h_bytes_per_step": int(d2h / max(its, 1)), "solves": nsolves, "lm_iterations": its,
-                      "includes": "after one untimed warm-up solve: H2D of this rank's index/observation rows and the parameters "
+                      "includes": "after two untimed warm-up solves (memory pools and the pinned result buffers warm): H2D of this rank's index/observation rows and the parameters "
                                   "from pinned memory, plan build (GPU sorts + workspace allocation), LM solve, all-reduce of the "
                                   "point ranges (N > 1), D2H of the optimised parameters"}
         out["e2e_params"], out["e2e_trajs"] = params, trajs

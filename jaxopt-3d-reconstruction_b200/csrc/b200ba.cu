@@ -178,6 +178,33 @@ enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, 
     if ((p)->prof) { i1_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); (p)->recs.push_back({(cls), i0_, i1_}); } \
   } while (0)
 
+// The same with programmatic dependent launch allowed (common.cuh: griddep_wait / griddep_launch): for the two kernels of a
+// PCG iteration, whose prologues then overlap the tail of the kernel before.  B200BA_PDL=0 launches them normally.
+// MEASURED at Venice-1778 (gpurun_out/r3b, LM it/s of the whole solve): no PDL 165.9; camera-side ring kernel allowed to start
+// early (mask 2) 168.4; point-side kernel allowed to start early (mask 1) 116.4; both (mask 3) 120.0 — the ring kernel's CTAs
+// arrive during the last wave of the point kernel and have their barriers set up when it ends; the 11 000 CTAs of the point
+// kernel gain nothing from being resident early and lose a third of the solve (every CTA pays for griddepcontrol.wait).
+// Default: mask 2.  B200BA_PDL=0 launches everything normally.
+static int pdl_mask() {  // bit 0: the point-side kernel may start early, bit 1: the camera-side ring kernel may
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("B200BA_PDL"); on = e ? atoi(e) : 2; }
+  return on;
+}
+#define PLAUNCH_PDL(bit, p, cls, kern, grid, block, smem, st, ...)                          \
+  do {                                                                                   \
+    size_t i0_ = 0, i1_ = 0;                                                             \
+    if ((p)->prof) { i0_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); }      \
+    cudaLaunchConfig_t cfg_ = {};                                                        \
+    cfg_.gridDim = dim3(grid); cfg_.blockDim = dim3(block); cfg_.dynamicSmemBytes = (smem); cfg_.stream = (st); \
+    cudaLaunchAttribute at_[1];                                                          \
+    at_[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                      \
+    at_[0].val.programmaticStreamSerializationAllowed = 1;                               \
+    cfg_.attrs = at_; cfg_.numAttrs = (pdl_mask() & (bit)) ? 1 : 0;                                \
+    cudaLaunchKernelEx(&cfg_, kern, __VA_ARGS__);                                        \
+    ++g_launches;                                                                        \
+    if ((p)->prof) { i1_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); (p)->recs.push_back({(cls), i0_, i1_}); } \
+  } while (0)
+
 // Stream-ordered allocation from the device's default memory pool (release threshold = never): after the first
 // plan a new plan's ~40 workspaces are carved out of memory the pool already holds (a plan is rebuilt per problem).
 static cudaStream_t g_alloc_stream = nullptr;
@@ -1221,8 +1248,9 @@ struct Ops {
     }
     if (p->ring_slots && (fused || half1 || half2)) {
       const int grid = p->C < p->n_sm * RING_MINB ? p->C : p->n_sm * RING_MINB;
-      PLAUNCH(p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, p->camtab,
-              p->cam_order, (const JT*)p->Jc_B, p->omg, p->sig, p->U, p->Minv, vin_slot, p->y, p->cv, p->part2);
+      PLAUNCH_PDL(2, p, cls, (k_cs_ring<JT>), grid, RING_T, p->ring_smem, s, p->C, p->nPB, flags, p->ring_slots, p->st, (const int32_t*)p->camtab,
+                  (const int32_t*)p->cam_order, (const JT*)p->Jc_B, (const double*)p->omg, p->sig, (const double*)p->U, (const double*)p->Minv,
+                  vin_slot, p->y, p->cv, p->part2);
       return;
     }
     const size_t smem = (flags & CS_C) && (flags & CS_A) ? p->stash_bytes : 0;
@@ -1237,9 +1265,10 @@ struct Ops {
               (const JT*)p->Jp_ps, p->Vinv, p->sig, p->omg, nullptr, nullptr, nullptr, p->tile_ctr);
       return;
     }
-    PLAUNCH(p, PC_MV_PT, (k_ps<JT, false>), p->nchunks > 0 ? p->nchunks : 1, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, it,
-            do_scalars, rtol, maxiter, p->st, p->part2, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB,
-            (const JT*)p->Jp_ps, p->Vinv, (size_t)p->P, p->sig, p->omg, nullptr, nullptr, nullptr);
+    PLAUNCH_PDL(1, p, PC_MV_PT, (k_ps<JT, false>), p->nchunks > 0 ? p->nchunks : 1, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, it,
+                do_scalars, rtol, maxiter, p->st, (const double*)p->part2, (const int32_t*)p->chunk_row, (const int32_t*)p->chunk_pt,
+                (const int32_t*)p->pt_ptr, (const int32_t*)p->pt_ps, (const int32_t*)p->posB, (const JT*)p->Jp_ps, (const double*)p->Vinv,
+                (size_t)p->P, (const double*)p->sig, p->omg, (const double*)nullptr, (double*)nullptr, (double*)nullptr);
   }
   // matvec tail + vector update + next matvec head; multi-rank: partial sums are all-reduced in between
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {

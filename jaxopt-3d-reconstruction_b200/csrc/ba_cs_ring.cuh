@@ -129,18 +129,21 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   uint64_t* bar_cfull = bar_empty + nslots;
   uint64_t* bar_cempty = bar_cfull + RING_NCAM;
   int* s_run0 = reinterpret_cast<int*>(bar_cempty + RING_NCAM);  // first run of the chunk held by each slot
-  if (st->pcg_done) return;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  // PCG scalars once into shared memory: kept as plain `st->x` the compiler re-loads them from GLOBAL memory at
-  // their use inside every camera's serial update (register pressure) — two dependent round trips per camera,
-  // 68 -> 64 us for the whole kernel at Venice
-  __shared__ double s_scal[4];
+  // PDL: the CTA may become resident while the point-side kernel before it drains; the barrier set-up needs nothing from it
   if (tid == 0) {
-    s_scal[0] = st->mu; s_scal[1] = st->alpha; s_scal[2] = st->beta;
     for (int i = 0; i < nslots; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, RING_CW); }
     for (int i = 0; i < RING_NCAM; ++i) { mbar_init(bar_cfull + i, 1); mbar_init(bar_cempty + i, RING_CW); }
     mbar_fence_init();
   }
+  griddep_launch();
+  griddep_wait();
+  if (st->pcg_done) return;
+  // PCG scalars once into shared memory: kept as plain `st->x` the compiler re-loads them from GLOBAL memory at
+  // their use inside every camera's serial update (register pressure) — two dependent round trips per camera,
+  // 68 -> 64 us for the whole kernel at Venice
+  __shared__ double s_scal[4];
+  if (tid == 0) { s_scal[0] = st->mu; s_scal[1] = st->alpha; s_scal[2] = st->beta; }
   __syncthreads();
   const int nb = (nPB + 3) & ~3, tab_stride = nb + ((nPB + 4) & ~3);
   constexpr uint32_t ROWB = 8 * sizeof(JT);

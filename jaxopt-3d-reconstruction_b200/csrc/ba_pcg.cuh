@@ -316,6 +316,9 @@ k_pcg_verify(int C, SolverState* __restrict__ st, const double* __restrict__ par
 #ifndef PS_RPT
 #define PS_RPT 4
 #endif
+#ifndef PS_PRELOAD
+#define PS_PRELOAD 0  // 1: row positions / point parts / point blocks are loaded BEFORE the wait for the preceding kernel (PDL) — measured slower (70.5 vs 67.7 us at Venice) and an early-started point kernel costs 30 % of the whole solve, see b200ba.cu pdl_mask()
+#endif
 #ifndef PS_OWN
 #define PS_OWN 1  // row -> local point through a shared-memory byte/short map written by the point lanes (no pt_A load)
 #endif
@@ -401,6 +404,14 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     r0 = __ldg(chunk_row + ch); nrows = __ldg(chunk_row + ch + 1) - r0;
     p0 = __ldg(chunk_pt + ch); npts = __ldg(chunk_pt + ch + 1) - p0;
   }
+#ifdef B200BA_L2HINT
+  const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
+#endif
+  // PDL: everything up to griddep_wait() reads only what is constant during a solve (row positions, point parts of the
+  // rows, point blocks) — it runs while the preceding camera-side kernel is still draining its last cameras
+  griddep_launch();
+#if !PS_PRELOAD
+  griddep_wait();
   // CTA-uniform early exit: block 0 of this very launch may set the flag while other CTAs are starting
   if (!BACKSUB && !(do_scalars & 2) && __syncthreads_or(tid == 0 ? st->pcg_done : 0)) return;
   if (!BACKSUB && (do_scalars & 1) && ch == 0) {
@@ -408,22 +419,23 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
     __syncthreads();
   }
   if (ch >= nchunks) return;
-#ifdef B200BA_L2HINT
-  const uint64_t pol_first = l2_policy_evict_first(), pol_last = l2_policy_evict_last();
 #endif
-  double acc[2] = {0.0, 0.0};
-  if (nrows <= CAP) {
-    double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
-    int beg = 0, end = 0;
-    JT b[PS_RPT][3];
-    int dst[PS_RPT], lp[PS_RPT];
-    double s[PS_RPT];
+  const bool small = ch < nchunks && nrows <= CAP;
+  double vi[6] = {0, 0, 0, 0, 0, 0}, g0 = 0, g1 = 0, g2 = 0;
+  int beg = 0, end = 0;
+  JT b[PS_RPT][3];
+  int dst[PS_RPT], lp[PS_RPT];
+  double s[PS_RPT];
+#pragma unroll
+  for (int j = 0; j < PS_RPT; ++j) {
+    dst[j] = 0; lp[j] = 0; s[j] = 0.0;
+    b[j][0] = b[j][1] = b[j][2] = (JT)0;
+  }
+  if (small) {
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j) {
       const int i = tid + j * PS_T;
       const size_t row = (size_t)r0 + i;
-      dst[j] = 0; lp[j] = 0; s[j] = 0.0;
-      b[j][0] = b[j][1] = b[j][2] = (JT)0;
       if (i < nrows) {
 #ifdef B200BA_L2HINT
         dst[j] = ldg_h(posB + row, pol_first);
@@ -445,6 +457,19 @@ k_ps(size_t N, int nchunks, int C, int it, int do_scalars, double rtol, int maxi
       for (int k = 0; k < 6; ++k) vi[k] = __ldg(Vinv + (size_t)k * Pst + p);
       if (BACKSUB) { g0 = gp[3 * (size_t)p]; g1 = gp[3 * (size_t)p + 1]; g2 = gp[3 * (size_t)p + 2]; }
     }
+  }
+#if PS_PRELOAD
+  griddep_wait();
+  // CTA-uniform early exit: block 0 of this very launch may set the flag while other CTAs are starting
+  if (!BACKSUB && !(do_scalars & 2) && __syncthreads_or(tid == 0 ? st->pcg_done : 0)) return;
+  if (!BACKSUB && (do_scalars & 1) && ch == 0) {
+    pcg_scalars(C, it, st, cpart, rtol, maxiter, sred);
+    __syncthreads();
+  }
+  if (ch >= nchunks) return;
+#endif
+  double acc[2] = {0.0, 0.0};
+  if (nrows <= CAP) {
 #pragma unroll
     for (int j = 0; j < PS_RPT; ++j)
 #ifdef B200BA_L2HINT

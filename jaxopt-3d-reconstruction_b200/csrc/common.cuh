@@ -25,6 +25,12 @@ struct SolverState {
 };
 
 #ifndef B200BA_HOST_MATH
+// Programmatic dependent launch (PDL): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may become
+// resident while its predecessor in the stream is still draining, once every CTA of the predecessor has executed
+// griddep_launch(); it must not touch anything the predecessor writes before griddep_wait() (= predecessor complete and
+// its memory visible).  Both are no-ops in an ordinary launch.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
