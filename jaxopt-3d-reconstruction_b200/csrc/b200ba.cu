@@ -19,6 +19,7 @@
 #include "ba_cs_ring.cuh"
 #include "ba_cs_warp.cuh"
 #include "ba_cs_ringx.cuh"
+#include "ba_cs_warpx.cuh"
 #include "ba_ps_tile.cuh"
 #include "ba_dense.cuh"
 #include "pose_kernels.cuh"
@@ -80,6 +81,7 @@ struct b200ba_plan {
   int ring_slots = 0, n_sm = 0;
   int ringx_ok = 0, ringx_D = 0, ringx_slots = 0;  // fused multi-rank camera kernel (ba_cs_ringx.cuh)
   int ringx_auto = 0;                              // ... and whether the cost model prefers it for this plan
+  int warpx = 0, warpx_grid = 0;                   // warp-per-camera fused multi-rank kernel (ba_cs_warpx.cuh)
   int32_t* cam_order_x = nullptr;     // its camera order: the SAME on every rank (descending GLOBAL row count)
   std::vector<int64_t> cam_rows_host; // local rows per camera (padded), kept for that
   size_t ringx_smem = 0;
@@ -165,9 +167,9 @@ enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, 
 // k_cs_warp with the plan's unroll (see ba_cs_warp.cuh)
 #define CW_LAUNCH(p, cls, grid, st, ...)                                                                   \
   do {                                                                                                     \
-    if ((p)->cw_u == 3) PLAUNCH(p, cls, (k_cs_warp<JT, 3>), grid, CW_T, 0, st, __VA_ARGS__);               \
-    else if ((p)->cw_u == 6) PLAUNCH(p, cls, (k_cs_warp<JT, 6>), grid, CW_T, 0, st, __VA_ARGS__);          \
-    else PLAUNCH(p, cls, (k_cs_warp<JT, 4>), grid, CW_T, 0, st, __VA_ARGS__);                              \
+    if ((p)->cw_u == 3) PLAUNCH_PDL(4, p, cls, (k_cs_warp<JT, 3>), grid, CW_T, 0, st, __VA_ARGS__);        \
+    else if ((p)->cw_u == 6) PLAUNCH_PDL(4, p, cls, (k_cs_warp<JT, 6>), grid, CW_T, 0, st, __VA_ARGS__);   \
+    else PLAUNCH_PDL(4, p, cls, (k_cs_warp<JT, 4>), grid, CW_T, 0, st, __VA_ARGS__);                       \
   } while (0)
 #define PLAUNCH(p, cls, kern, grid, block, smem, st, ...)                                \
   do {                                                                                   \
@@ -184,11 +186,13 @@ enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, 
 // early (mask 2) 168.4; point-side kernel allowed to start early (mask 1) 116.4; both (mask 3) 120.0 — the ring kernel's CTAs
 // arrive during the last wave of the point kernel and have their barriers set up when it ends; the 11 000 CTAs of the point
 // kernel gain nothing from being resident early and lose a third of the solve (every CTA pays for griddepcontrol.wait).
-// Default: mask 2.  B200BA_PDL=0 launches everything normally.
-static int pdl_mask() {  // bit 0: the point-side kernel may start early, bit 1: the camera-side ring kernel may
-  static int on = -1;
-  if (on < 0) { const char* e = getenv("B200BA_PDL"); on = e ? atoi(e) : 2; }
-  return on;
+// Multi-rank sequence (k_ps | k_cs_warp | k_cs_vec | k_cs_warp), 2 ranks (gpurun_out/r3e): Venice 229.8 (none) / 230.1 (mask 14) /
+// 233.5 (mask 15); Final-13682 49.7 / 49.85 / 50.1 — there the point kernel may start early too.
+// Default: mask 2 on one rank, 15 on the split path.  B200BA_PDL=0 launches everything normally.
+static int pdl_mask(const b200ba_plan* p) {  // may start early: bit 0 the point-side kernel, bit 1 the ring kernel, bit 2 k_cs_warp, bit 3 k_cs_vec
+  static int env = -2;
+  if (env == -2) { const char* e = getenv("B200BA_PDL"); env = e ? atoi(e) : -1; }
+  return env >= 0 ? env : (p->split ? 15 : 2);
 }
 #define PLAUNCH_PDL(bit, p, cls, kern, grid, block, smem, st, ...)                          \
   do {                                                                                   \
@@ -199,7 +203,7 @@ static int pdl_mask() {  // bit 0: the point-side kernel may start early, bit 1:
     cudaLaunchAttribute at_[1];                                                          \
     at_[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                      \
     at_[0].val.programmaticStreamSerializationAllowed = 1;                               \
-    cfg_.attrs = at_; cfg_.numAttrs = (pdl_mask() & (bit)) ? 1 : 0;                                \
+    cfg_.attrs = at_; cfg_.numAttrs = (pdl_mask(p) & (bit)) ? 1 : 0;                                \
     cudaLaunchKernelEx(&cfg_, kern, __VA_ARGS__);                                        \
     ++g_launches;                                                                        \
     if ((p)->prof) { i1_ = (p)->ev_used; cudaEventRecord((p)->get_event(), (st)); (p)->recs.push_back({(cls), i0_, i1_}); } \
@@ -523,7 +527,7 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     int32_t *vals = nullptr, *permBA = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
-    pool_malloc((void**)&bad, sizeof(int));
+    if (pool_malloc((void**)&bad, sizeof(int)) != cudaSuccess) { b200ba_plan_destroy(p); FAIL(B200BA_ECUDA, "plan_create: out of device memory (index check)"); }
     cudaMemsetAsync(bad, 0, sizeof(int), s);
     LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, cam_idx, C, bad);
     LAUNCH(k_check_range, cdiv(N, 256), 256, 0, s, N, pt_idx, P, bad);
@@ -532,12 +536,18 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     cudaStreamSynchronize(s);
     pool_free(bad);
     if (bad_h) { b200ba_plan_destroy(p); FAIL(B200BA_EINVAL, "plan_create: index out of range"); }
-    pool_malloc((void**)&keys, N * sizeof(int64_t)); pool_malloc((void**)&keys2, N * sizeof(int64_t));
-    pool_malloc((void**)&vals, N * sizeof(int32_t)); pool_malloc((void**)&permBA, N * sizeof(int32_t));
     const int nb = bits_for((int64_t)P * C + C);
     const int nbB = bits_for((int64_t)nruns + 1);
+    int32_t* runptr_u = nullptr;
     cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
-    pool_malloc((void**)&tmp, tmp_bytes);
+    if (pool_malloc((void**)&keys, N * sizeof(int64_t)) != cudaSuccess || pool_malloc((void**)&keys2, N * sizeof(int64_t)) != cudaSuccess ||
+        pool_malloc((void**)&vals, N * sizeof(int32_t)) != cudaSuccess || pool_malloc((void**)&permBA, N * sizeof(int32_t)) != cudaSuccess ||
+        pool_malloc((void**)&tmp, tmp_bytes) != cudaSuccess || pool_malloc((void**)&runptr_u, (nruns + 1) * sizeof(int32_t)) != cudaSuccess) {
+      cudaGetLastError();
+      pool_free(keys); pool_free(keys2); pool_free(vals); pool_free(permBA); pool_free(tmp); pool_free(runptr_u);
+      b200ba_plan_destroy(p);
+      FAIL(B200BA_ECUDA, "plan_create: out of device memory (sort workspaces)");
+    }
     // A order
     LAUNCH(k_make_keys, cdiv(N, 256), 256, 0, s, N, cam_idx, pt_idx, (int64_t)C, 0, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, p->order_ps, (int)N, 0, nb, s);
@@ -546,8 +556,6 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     LAUNCH(k_segment_ptr, cdiv(P + 1, 256), 256, 0, s, P, N, p->pt_ps, p->pt_ptr);
     lap("A order sort");
     // B order: stable sort of the A rows by (point block, camera) keeps the point order inside a run
-    int32_t* runptr_u = nullptr;
-    pool_malloc((void**)&runptr_u, (nruns + 1) * sizeof(int32_t));
     LAUNCH(k_make_keys_B, cdiv(N, 256), 256, 0, s, N, C, p->block_rows, p->cam_ps, p->pt_ps, p->pt_ptr, keys, vals);
     cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, permBA, (int)N, 0, nbB, s);
     LAUNCH(k_segment_ptr64, cdiv((int64_t)nruns + 1, 256), 256, 0, s, (int64_t)nruns, N, keys2, runptr_u);
@@ -567,8 +575,8 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
       if (acc >= (1LL << 31)) e = cudaErrorInvalidValue;
     }
     int32_t* run_start = nullptr;
+    if (e == cudaSuccess) e = pool_malloc((void**)&run_start, (nruns + 1) * sizeof(int32_t));
     if (e == cudaSuccess) {
-      pool_malloc((void**)&run_start, (nruns + 1) * sizeof(int32_t));
       cudaMemcpyAsync(run_start, hstart.data(), (nruns + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, s);
       LAUNCH(k_posB, cdiv(N, 256), 256, 0, s, N, permBA, keys2, runptr_u, run_start, p->posB);
       e = cudaStreamSynchronize(s);
@@ -774,6 +782,33 @@ extern "C" int b200ba_plan_create(int C, int P, int64_t N, const int32_t* cam_id
     p->ringx_auto = 0;
     if (const char* e = getenv("B200BA_RINGX")) { if (!atoi(e)) p->ringx_ok = 0; else p->ringx_auto = 1; }
     if (const char* e = getenv("B200BA_RINGX_D")) { const int v = atoi(e); if (v >= 1 && v < p->ringx_D) p->ringx_D = v; }
+    // warp-per-camera fused kernel: cooperative grid of at most one resident wave (identical on identical GPUs)
+    {
+      int occ = 0, n_sm = 148;
+      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0);
+      cudaError_t e = cudaErrorUnknown;
+      if (p->jac_f32) {
+        if (p->cw_u == 3) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<float, 3>, CW_T, 0);
+        else if (p->cw_u == 6) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<float, 6>, CW_T, 0);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<float, 4>, CW_T, 0);
+      } else {
+        if (p->cw_u == 3) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<double, 3>, CW_T, 0);
+        else if (p->cw_u == 6) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<double, 6>, CW_T, 0);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_cs_warpx<double, 4>, CW_T, 0);
+      }
+      int coop = 0;
+      cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, 0);
+      p->warpx = 0;
+      if (e == cudaSuccess && occ >= 1 && coop && p->nPB <= MAXPB) {
+        p->warpx_grid = std::min((int)cdiv(C, CW_T / 32), occ * n_sm);
+        // MEASURED (gpurun_out/r3f-r3h, LM it/s, three-launch sequence -> this kernel): Venice-1778 2 ranks 237-242 -> 260-263,
+        // 8 ranks 528 -> 578; Final-13682 2 ranks 50.3 -> 48.1-49.7, 8 ranks 142 -> 131.  It wins where every camera has a
+        // resident warp of its own (one wave, rows of pass C still in L2 for pass A) and loses where a warp walks several
+        // cameras.  -1: decided in b200ba_plan_set_comm (several ranks only); B200BA_WARPX=0/1 overrides.
+        p->warpx = C <= p->warpx_grid * (CW_T / 32) ? -1 : 0;
+        if (const char* ev = getenv("B200BA_WARPX")) p->warpx = atoi(ev) != 0;
+      } else cudaGetLastError();
+    }
   }
   lap("camera tables, B arrays, smem config");
   {
@@ -1236,7 +1271,7 @@ struct Ops {
                 p->xseq_last, p->wcount + p->C);
       int vs = vin_slot;
       if (flags & (CS_READ_Y | CS_UX | upd)) {
-        PLAUNCH(p, PC_PCG_VEC, k_cs_vec, (int)cdiv(p->C, CV_T / 8), CV_T, 0, s, p->C, flags & ~(CS_A | CS_C), p->st, p->U, p->Minv,
+        PLAUNCH_PDL(8, p, PC_PCG_VEC, k_cs_vec, (int)cdiv(p->C, CV_T / 8), CV_T, 0, s, p->C, flags & ~(CS_A | CS_C), p->st, p->U, p->Minv,
                 vin_slot, p->y, p->cv, p->part2, g_x.peers, p->rank, (p->xchg && (flags & CS_READ_Y)) ? p->nranks : 1, p->xseq_last,
                 (size_t)XF_INTS / 2 + (size_t)(p->xseq_last & 1) * g_x.ycap);
         if (upd) vs = CV_M;
@@ -1274,6 +1309,22 @@ struct Ops {
   static int cs_step(b200ba_plan* p, int upd_flag, int vin, cudaStream_t s) {
     if (!p->split) {
       cs(p, PC_MV_CAM, CS_C | CS_UX | upd_flag | CS_A, vin, s);
+    } else if ((p->warpx > 0 && (p->nranks == 1 || p->xchg == 1)) || (p->warpx < 0 && p->nranks > 1 && p->xchg == 1)) {
+      // multi-rank: ONE cooperative launch, a warp per camera (ba_cs_warpx.cuh)
+      static long long timeout_ns = -1;
+      if (timeout_ns < 0) { const char* e = getenv("B200BA_XCHG_TIMEOUT_MS"); timeout_ns = (e && atol(e) > 0 ? atol(e) : 2000) * 1000000LL; }
+      int Ci = p->C, nPBi = p->nPB, fl = CS_C | CS_UX | upd_flag | CS_A, vi = vin, rk = p->rank, nr = p->nranks, seq = ++g_x.cseq;
+      const int32_t* tab = p->camtab;
+      const int32_t* ord = p->cam_order_x;
+      const JT* rows = (const JT*)p->Jc_B;
+      const double *om = p->omg, *Uc = p->U, *Mi = p->Minv;
+      static int pipe = -1;  // software pipeline over a warp's cameras (B200BA_WARPX_PIPE=0: finish every camera at once)
+      if (pipe < 0) { const char* e = getenv("B200BA_WARPX_PIPE"); pipe = e ? (atoi(e) != 0) : 1; }
+      void* args[] = {&Ci, &nPBi, &fl, &p->st, &tab, &ord, &rows, &om, &p->sig, &Uc, &Mi, &vi, &p->cv, &p->part2,
+                      &g_x.peers, &g_x.xc, &rk, &nr, &seq, &timeout_ns, &pipe};
+      const void* fn = p->cw_u == 3 ? (const void*)k_cs_warpx<JT, 3> : p->cw_u == 6 ? (const void*)k_cs_warpx<JT, 6> : (const void*)k_cs_warpx<JT, 4>;
+      int rc = coop_launch(p, PC_MV_CAM, fn, p->warpx_grid, CW_T, args, s);
+      if (rc) return rc;
     } else if (p->ringx_ok && p->ringx_auto && (p->nranks == 1 || p->xchg == 1)) {
       // multi-rank: ONE launch — partial sums pushed to the peers and summed inside the kernel (ba_cs_ringx.cuh)
       static long long timeout_ns = -1;
@@ -2018,7 +2069,7 @@ extern "C" int b200ba_plan_info(b200ba_plan* p, int* out) {
   if (!p || !out) FAIL(B200BA_EINVAL, "null");
   for (int k = 0; k < 8; ++k) out[k] = 0;
   out[0] = p->use_tile; out[1] = p->tile_rows; out[2] = p->ntiles; out[3] = p->fused_lin; out[4] = p->nPB; out[5] = p->dense_schur;
-  out[6] = p->nchunks; out[7] = p->split | ((p->ringx_ok && p->ringx_auto) << 1) | (p->ringx_D << 8);
+  out[6] = p->nchunks; out[7] = p->split | ((p->ringx_ok && p->ringx_auto) << 1) | ((p->warpx > 0 || (p->warpx < 0 && p->nranks > 1 && p->xchg == 1)) << 2) | (p->ringx_D << 8);
   return B200BA_OK;
 }
 

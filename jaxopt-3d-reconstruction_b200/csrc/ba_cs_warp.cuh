@@ -240,6 +240,8 @@ k_cs_warp(int ntasks, int nPB, int flags, const SolverState* __restrict__ st, co
           double* __restrict__ wpart, int* __restrict__ wcount, XPeers px, int rank, int nr, int seq, int* __restrict__ xctr) {
   const int lane = threadIdx.x & 31;
   const int t = blockIdx.x * (CW_T / 32) + (threadIdx.x >> 5);
+  griddep_launch();  // PDL (common.cuh): the next kernel of the iteration may become resident while this one drains
+  griddep_wait();    // omega / the camera records / the finished flag come from the kernels before
   const bool work = ((flags & CS_IGNORE_DONE) || !st->pcg_done) && t < ntasks;  // warp-uniform
   if (work) k_cs_warp_task<JT, CW_U>(t, lane, nPB, flags, camtab, wtask, Jc_B, omg, sig, cv, vin_slot, y, wpart, wcount);
   // multi-rank: tell the peers that this rank's partial sums of iteration seq are complete (also when the solve is
@@ -262,11 +264,16 @@ k_cs_vec(int C, int flags, SolverState* __restrict__ st, const double* __restric
   const bool upd = flags & (CS_INIT | CS_ITER);
   double* rec = cv + (size_t)CV_STRIDE * cc + k;
   double v[CV_SLOTS], u8[8] = {0, 0, 0, 0, 0, 0, 0, 0}, m8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  // PDL: U / Minv are constant during a solve and may be loaded while the kernel before drains.  The camera records are
+  // NOT: with every kernel of the iteration allowed to start early, "the launch that wrote them has completed" only holds
+  // after this kernel's own wait
+  griddep_launch();
+  if (flags & CS_UX) load8<double>(U + 64 * cc + 8 * k, u8);
+  if (upd) load8<double>(Minv + 64 * cc + 8 * k, m8);
+  griddep_wait();
 #pragma unroll
   for (int sl = 0; sl < CV_SLOTS; ++sl) v[sl] = rec[8 * sl];
   const double vk = vin_slot >= 0 ? rec[8 * vin_slot] : 0.0;
-  if (flags & CS_UX) load8<double>(U + 64 * cc + 8 * k, u8);
-  if (upd) load8<double>(Minv + 64 * cc + 8 * k, m8);
   double nk = ((flags & CS_READ_Y) && nr <= 1) ? y[8 * cc + k] : 0.0;
   const int done = (flags & CS_IGNORE_DONE) ? 0 : st->pcg_done;  // set by an earlier launch: uniform over grid and ranks
   const double mu = st->mu, alpha = st->alpha, beta = st->beta;

@@ -244,6 +244,29 @@ def test_fused_multi_rank_ring_kernel_on_one_rank(monkeypatch, ringx_d):
 
 
 @pytest.mark.parametrize("cw_u", ["3", "4", "6"])
+@pytest.mark.parametrize("shape", ["ladybug49", "trafalgar257"])
+def test_warp_per_camera_fused_multi_rank_kernel_on_one_rank(monkeypatch, shape, cw_u):
+    """ba_cs_warpx.cuh (one cooperative launch per PCG iteration on several ranks: a persistent warp per camera does pass C,
+    the packet exchange, the camera-local update and pass A) forced onto one rank: same trajectory as the single-rank ring
+    kernel, all three unroll instantiations; trafalgar257 has more cameras than one CTA wave of warps on a small grid."""
+    sc, ba, x0, k3 = _setup(shape, jac_f32=True)
+    out = []
+    for split in ("0", "1"):
+        monkeypatch.setenv("B200BA_FORCE_SPLIT", split)
+        monkeypatch.setenv("B200BA_WARPX", "1")
+        monkeypatch.setenv("B200BA_CW_U", cw_u)
+        prob = ba.build_problem_sparse(sc.cam_idx, sc.pt_idx, sc.obs, sc.P)
+        info = (__import__("ctypes").c_int * 8)()
+        prob.lib.b200ba_plan_info(prob.plan, info)
+        assert (info[7] & 1) == int(split) and (info[7] & 4)
+        out.append(ba.optimize(x0, prob, None, k3, None))
+    (pa, sa), (pb, sb) = out
+    assert sa.iter_num == sb.iter_num and sa.pcg_iters.sum() > 0
+    np.testing.assert_allclose(sa.loss_trajectory, sb.loss_trajectory, rtol=2e-6)
+    np.testing.assert_allclose(pa, pb, rtol=0, atol=1e-6 * np.abs(pa).max())
+
+
+@pytest.mark.parametrize("cw_u", ["3", "4", "6"])
 @pytest.mark.parametrize("task_rows", ["64", "100000"])
 def test_split_camera_passes_match_the_fused_iteration(monkeypatch, task_rows, cw_u):
     """The multi-rank kernel sequence (warp-task partial sums | all-reduce point | camera-local vector step |

@@ -23,7 +23,8 @@ def _run(nproc, shape, env_extra):
 
 @pytest.mark.parametrize("shape", ["small", "ladybug49"])
 def test_point_sharded_solve_matches_single_gpu(shape):
-    """Default path: per-iteration partial sums over peer memory (CUDA IPC), the rest over NCCL."""
+    """Default path: per-iteration partial sums over peer memory (CUDA IPC; at these sizes the warp-per-camera fused kernel,
+    ba_cs_warpx.cuh), the rest over NCCL."""
     out = _run(2, shape, {"B200BA_VERBOSE": "1"})
     assert "partial sums over peer memory" in out, out[-2000:]
 
@@ -36,20 +37,29 @@ def test_nccl_exchange_fallback_matches_single_gpu():
 
 def test_cameras_cut_into_many_warp_tasks_multi_rank():
     """64-row tasks: every camera's partial sum is assembled by the last-arriver path on every rank."""
-    _run(2, "trafalgar257", {"B200BA_TASK_ROWS": "64"})
+    _run(2, "trafalgar257", {"B200BA_TASK_ROWS": "64", "B200BA_WARPX": "0"})
 
 
 def test_fused_ring_kernel_needs_one_camera_order_on_all_ranks():
     """ba_cs_ringx.cuh with pipeline depth 1 and two cameras per CTA (257 cameras, 148 CTAs): every CTA waits for its first
     camera's peer sums before it pushes its second one.  With per-rank camera orders (the first version) this is a circular
     wait; the order must be the global one built in b200ba_plan_set_comm."""
-    out = _run(2, "trafalgar257", {"B200BA_RINGX": "1", "B200BA_RINGX_D": "1", "B200BA_XCHG_TIMEOUT_MS": "300"})
+    out = _run(2, "trafalgar257", {"B200BA_RINGX": "1", "B200BA_RINGX_D": "1", "B200BA_XCHG_TIMEOUT_MS": "300", "B200BA_WARPX": "0"})
+    assert "MULTI_GPU_OK" in out
+
+
+@pytest.mark.parametrize("shape", ["ladybug49", "trafalgar257", "ladybug49_gap"])
+def test_warp_per_camera_fused_kernel(shape):
+    """ba_cs_warpx.cuh: one cooperative launch per PCG iteration; a warp per camera pushes its partial sums to the peers as
+    self-validating packets, polls theirs, updates and does pass A.  A short time-out turns a protocol error into a failure
+    instead of a 2 s stall per camera."""
+    out = _run(2, shape, {"B200BA_WARPX": "1", "B200BA_XCHG_TIMEOUT_MS": "500"})
     assert "MULTI_GPU_OK" in out
 
 
 def test_three_launch_exchange_sequence_still_matches():
     """B200BA_RINGX=0: partial sums | wait + vector step | sigma pass as three launches (round-1 path, the fallback)."""
-    _run(2, "ladybug49", {"B200BA_RINGX": "0"})
+    _run(2, "ladybug49", {"B200BA_RINGX": "0", "B200BA_WARPX": "0"})
 
 
 def test_camera_without_rows_on_one_rank():
