@@ -86,6 +86,22 @@ def test_shard_points_partitions_and_balances(world):
     assert max(cnt) - min(cnt) <= 0.02 * sc.N / world + 64
 
 
+def test_robust_loss_arguments_are_validated_on_the_host():
+    """`robust_loss` belongs to the 2-vector model (the reference's own cost has no robustifier); unknown names are refused
+    before anything touches a device."""
+    with pytest.raises(ValueError):
+        b200ba.B200BundleAdjustment(3, 1000.0, device="cpu", robust_loss="cauchy")
+    with pytest.raises(ValueError):
+        b200ba.B200BundleAdjustment(3, 1000.0, device="cpu", residual_model="vector2", robust_loss="huber")
+    with pytest.raises(ValueError):
+        b200ba.B200BundleAdjustment(3, 1000.0, device="cpu", residual_model="vector3")
+    ba = b200ba.B200BundleAdjustment(3, 1000.0, device="cpu", residual_model="vector2", robust_loss="soft_l1", loss_scale=2)
+    assert ba.robust_loss == "soft_l1" and ba.loss_scale == 2.0 and ba.jac_f32 is False
+    assert b200ba.B200BundleAdjustment(3, 1000.0, device="cpu", residual_model="vector2", robust_loss="trivial").robust_loss is None
+    hdr = open(os.path.join(ROOT, "include", "b200ba.h")).read()
+    assert "B200BA_ROBUST_CAUCHY 1" in hdr and "B200BA_ROBUST_SOFT_L1 2" in hdr  # the codes api.py passes
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
