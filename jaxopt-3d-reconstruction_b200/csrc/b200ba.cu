@@ -1464,10 +1464,9 @@ struct Ops {
   // cooperative launch), two triangular sweeps; the solution lands in slot X of the camera records.
   static int dense_solve(b200ba_plan* p, cudaStream_t s) {
     const int C = p->C, T = p->dn_T, npad = p->dn_npad;
-    PLAUNCH(p, PC_DN_ASM, k_dn_next_epoch, 1, 32, 0, s, p->st);
     PLAUNCH(p, PC_DN_ASM, (k_dn_assemble<JT>), dim3(cdiv(C, DN_ASM_T / 32), C), DN_ASM_T, 0, s, C, npad, (size_t)p->N, (size_t)p->P,
             &p->st->mu, p->dn_blk_ptr, p->dn_pairs, p->posB, p->pt_ps, (const JT*)p->Jc_B, (const JT*)p->Jp_ps, p->Vinv, p->U, p->Sd,
-            p->dn_S);
+            p->dn_S, p->st);
     int* tflags = p->dn_flags;
     int* yflag = p->dn_flags + (size_t)T * T;
     int* xflag = yflag + T;
@@ -1477,34 +1476,35 @@ struct Ops {
       int rc = coop_launch(p, PC_DN_CHOL, (const void*)k_dn_factor, p->dn_grid, DN_T, args, s);
       if (rc) return rc;
     }
-    PLAUNCH(p, PC_DN_SOLVE, k_dn_load_rhs, cdiv(npad, 256), 256, 0, s, 8 * C, npad, p->rhs, p->dn_vec);
     {
       const double* Lc = p->dn_S;
-      void* args[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &yflag};
+      const double* rh = p->rhs;
+      int n8 = 8 * C;
+      void* args[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &yflag, &n8, &rh, &p->cv};
       int rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<false>, p->dn_grid_v, DN_T, args, s);
       if (rc) return rc;
-      void* args2[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &xflag};
+      void* args2[] = {&Ti, &np_, &p->st, &Lc, &p->dn_vec, &xflag, &n8, &rh, &p->cv};
       rc = coop_launch(p, PC_DN_SOLVE, (const void*)k_dn_trsv<true>, p->dn_grid_v, DN_T, args2, s);
       if (rc) return rc;
     }
-    PLAUNCH(p, PC_DN_SOLVE, k_dn_store_x, cdiv(8 * (int64_t)C, 256), 256, 0, s, C, p->dn_vec, p->cv);
     CK(cudaGetLastError());
     return 0;
   }
 
-  static int backsub(b200ba_plan* p, cudaStream_t s) {
+  // reduce = false: leave the per-chunk partials {v_p.g_p, |v_p|^2} in partN for k_cost_reduce (the LM loop)
+  static int backsub(b200ba_plan* p, cudaStream_t s, bool reduce = true) {
     cs(p, PC_BACKSUB, CS_A | CS_IGNORE_DONE, CV_X, s);
     if (p->N && p->use_tile) {
       PLAUNCH(p, PC_BACKSUB, (k_ps_tile<JT, true>), p->tile_grid, PT_T, (size_t)p->tile_rows * sizeof(double), s, (size_t)p->N, (size_t)p->P,
               p->ntiles, p->C, 0, 0, 0.0, 0, p->st, nullptr, p->tile_row, p->tile_pt, p->pt_ptr, p->gpos, p->lpos,
               (const JT*)p->Jp_ps, p->Vinv, p->sig, nullptr, p->gp, p->vp, p->partN, p->tile_ctr);
-      PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->ntiles, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+      if (reduce) PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->ntiles, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
       return 0;
     }
     if (p->N) PLAUNCH(p, PC_BACKSUB, (k_ps<JT, true>), p->nchunks, PS_T, 0, s, (size_t)p->N, p->nchunks, p->C, 0, 0, 0.0, 0, p->st,
                       nullptr, p->chunk_row, p->chunk_pt, p->pt_ptr, p->pt_ps, p->posB, (const JT*)p->Jp_ps, p->Vinv, (size_t)p->P, p->sig,
                       nullptr, p->gp, p->vp, p->partN);
-    PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
+    if (reduce) PLAUNCH(p, PC_OTHER, k_reduce, 1, 1024, 0, s, p->partN, p->N ? p->nchunks : 0, 2, 2, p->scal + 9, 0);  // [9]=vg_p [10]=vv_p
     return 0;
   }
 
@@ -1539,8 +1539,13 @@ struct Ops {
 // (+ k_pack_decide + k_lm_decide on one rank).  Sums keep the order of the generic k_reduce: bit-identical results.
 // part: [0, C) per-camera sums of r^2 (trial-cost kernel); [2C, 4C) per-camera {v.g, |v|^2} (k_trial_cams).
 __global__ void __launch_bounds__(1024)
-k_cost_reduce(int C, const double* __restrict__ part, double* __restrict__ scal, SolverState* __restrict__ st, int decide) {
+k_cost_reduce(int C, const double* __restrict__ part, double* __restrict__ scal, SolverState* __restrict__ st, int decide,
+              const double* __restrict__ partN, int nred) {
   __shared__ double sm[32];
+  // [9] = v_p.g_p, [10] = |v_p|^2 from the per-chunk partials of the back-substitution (was a k_reduce launch of its own)
+  const double vgp = cta_sum_strided(partN, nred, 2, sm);
+  const double vvp = cta_sum_strided(partN + 1, nred, 2, sm);
+  if (threadIdx.x == 0) { scal[9] = vgp; scal[10] = vvp; }
   const double r2 = cta_sum_strided(part, C, 1, sm);
   const double vg = cta_sum_strided(part + 2 * (size_t)C, C, 2, sm);
   const double vv = cta_sum_strided(part + 2 * (size_t)C + 1, C, 2, sm);
@@ -1581,15 +1586,17 @@ __global__ void k_accept_copy2(const SolverState* __restrict__ st, int64_t nc, c
 
 
 // trial parameters, trial cost, gain ratio and damping update (LevenbergMarquardt.update after the solve); cam8: current
-// camera parameters.  5 launches on one rank.
+// camera parameters.  4 launches on one rank; expects the back-substitution's partials in partN (backsub(p, s, false)).
 template <typename JT>
 static int trial_decide(b200ba_plan* p, const double* cam8, const double* k3, double inv_w2, cudaStream_t s) {
   const int C = p->C, P = p->P;
   int rc;
-  PLAUNCH(p, PC_OTHER, k_trial_cams, cdiv(C, 128), 128, 0, s, C, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc, p->cam_trial, p->part + 2 * (size_t)C);
-  if (P) PLAUNCH(p, PC_OTHER, k_trial_pts, cdiv(4 * (int64_t)P, 256), 256, 0, s, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
+  const int cam_blocks = (int)cdiv(C, 256);
+  PLAUNCH(p, PC_OTHER, k_trial, cam_blocks + cdiv(4 * (int64_t)P, 256), 256, 0, s, C, cam_blocks, cam8, p->cv + 8 * CV_X, CV_STRIDE, p->gc,
+          p->cam_trial, p->part + 2 * (size_t)C, 4 * (int64_t)P, p->pts4, p->vp, p->pts4_trial);
   if ((rc = Ops<JT>::cost_partials(p, p->cam_trial, k3, p->pts4_trial, inv_w2, s))) return rc;
-  PLAUNCH(p, PC_OTHER, k_cost_reduce, 1, 1024, 0, s, C, p->part, p->scal, p->st, p->nranks > 1 ? 0 : 1);
+  const int nred = !p->N ? 0 : p->use_tile ? p->ntiles : p->nchunks;  // partials written by backsub(..., false)
+  PLAUNCH(p, PC_OTHER, k_cost_reduce, 1, 1024, 0, s, C, p->part, p->scal, p->st, p->nranks > 1 ? 0 : 1, p->partN, nred);
   if (p->nranks > 1) {
     if ((rc = allreduce(p, p->scal + 8, 4, ncclSum, s))) return rc;
     PLAUNCH(p, PC_OTHER, k_lm_decide2, 1, 1, 0, s, p->st, p->scal);
@@ -1872,7 +1879,7 @@ static int graph_build(b200ba_plan* p, double inv_w2, const b200ba_lm_opts* o) {
   GCK(cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
   rc = Ops<JT>::prepare_blocks(p, s);
   if (!rc) rc = Ops<JT>::dense_solve(p, s);
-  if (!rc) rc = Ops<JT>::backsub(p, s);
+  if (!rc) rc = Ops<JT>::backsub(p, s, false);
   if (rc) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
   if ((rc = trial_decide<JT>(p, G.cam_work, G.k3_work, inv_w2, s))) { cudaStreamEndCapture(s, nullptr); p->prof = prof; return rc; }
   accept_step(p, G.cam_work, 1, if_h, s);
@@ -2019,7 +2026,7 @@ extern "C" int b200ba_lm_solve(b200ba_plan* p, double* cam8, const double* k3, d
       if ((rc = DISPATCH(p, pcg_solve, p, forcing_rtol(opts, err), opts->pcg_maxiter, opts->fixed_pcg_iters, &pcg_iters, s))) return rc;
     }
     res->n_pcg_iters_total += pcg_iters;
-    if ((rc = DISPATCH(p, backsub, p, s))) return rc;
+    if ((rc = DISPATCH(p, backsub, p, s, false))) return rc;
     if ((rc = p->jac_f32 ? trial_decide<float>(p, cam8, k3, inv_w2, s) : trial_decide<double>(p, cam8, k3, inv_w2, s))) return rc;
     res->n_res_evals++;
     accept_step(p, cam8, 0, cudaGraphConditionalHandle{}, s);

@@ -85,9 +85,12 @@ __global__ void __launch_bounds__(DN_ASM_T)
 k_dn_assemble(int C, int npad, size_t N, size_t Pst, const double* __restrict__ mu_ptr, const int32_t* __restrict__ blk_ptr,
               const int2* __restrict__ pairs, const int32_t* __restrict__ posB, const int32_t* __restrict__ pt_ps,
               const JT* __restrict__ Jc_B, const JT* __restrict__ Jp_ps, const double* __restrict__ Vinv,
-              const double* __restrict__ U, const double* __restrict__ Sd, double* __restrict__ S) {
+              const double* __restrict__ U, const double* __restrict__ Sd, double* __restrict__ S, SolverState* __restrict__ st) {
   const int c = blockIdx.y;
   const int d = blockIdx.x * (DN_ASM_T / 32) + (threadIdx.x >> 5);
+  // next epoch of the tile / block-row flags of the factorisation and the sweeps (they read it at their start, after this
+  // launch): one thread of the grid; was a launch of its own
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) st->dn_epoch += 1;
   if (d > c) return;  // warp-uniform
   const int lane = threadIdx.x & 31, k = lane & 7, sg = lane >> 3;
   const int64_t gq = (int64_t)c * C + d;
@@ -279,7 +282,8 @@ k_dn_factor(int T, int npad, double* __restrict__ S, int* __restrict__ flags, So
 // in processing order.  vec: in/out (npad doubles); vflag[T]: block row published (epoch).
 template <bool BACKWARD>
 __global__ void __launch_bounds__(DN_T)
-k_dn_trsv(int T, int npad, const SolverState* __restrict__ st, const double* __restrict__ L, double* __restrict__ vec, int* __restrict__ vflag) {
+k_dn_trsv(int T, int npad, const SolverState* __restrict__ st, const double* __restrict__ L, double* __restrict__ vec, int* __restrict__ vflag,
+          int n, const double* __restrict__ rhs, double* __restrict__ cv) {
   const int epoch = st->dn_epoch;
   __shared__ double Ls[DN_NB * (DN_NB + 1)];
   __shared__ double xs[DN_NB];
@@ -325,7 +329,10 @@ k_dn_trsv(int T, int npad, const SolverState* __restrict__ st, const double* __r
     if (tid < DN_NB) {
       // lane = row of the block: b_r - (the four partial sums of this row, fixed order), then substitution by shuffles.
       // forward: lower-triangular solve in ascending order; backward: Ls holds L_jj^T (upper): descending order
-      double v = __ldcg(vec + DN_NB * j + lane) - (((part[4 * lane] + part[4 * lane + 1]) + part[4 * lane + 2]) + part[4 * lane + 3]);
+      // forward sweep: the right-hand side comes straight from the reduced rhs (C x 8, zero beyond n); backward: y from vec
+      const int e0 = DN_NB * j + lane;
+      const double b0 = BACKWARD ? __ldcg(vec + e0) : (e0 < n ? rhs[e0] : 0.0);
+      double v = b0 - (((part[4 * lane] + part[4 * lane + 1]) + part[4 * lane + 2]) + part[4 * lane + 3]);
 #pragma unroll
       for (int cc0 = 0; cc0 < DN_NB; ++cc0) {
         const int cc = BACKWARD ? DN_NB - 1 - cc0 : cc0;
@@ -334,23 +341,11 @@ k_dn_trsv(int T, int npad, const SolverState* __restrict__ st, const double* __r
         else if (BACKWARD ? lane < cc : lane > cc) v -= Ls[lane * (DN_NB + 1) + cc] * xc;
       }
       vec[DN_NB * j + lane] = v;
+      if (BACKWARD && e0 < n) cv[(size_t)CV_STRIDE * (e0 >> 3) + 8 * CV_X + (e0 & 7)] = v;  // the solution -> slot X of the camera records
       __threadfence();
       __syncwarp();
       if (lane == 0) dn_st_release(vflag + j, epoch);
     }
     __syncthreads();
   }
-}
-
-__global__ void k_dn_next_epoch(SolverState* st) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) st->dn_epoch += 1;
-}
-// rhs (C x 8) -> dense vector (padded with zeros);  solution -> slot X of the camera records
-__global__ void k_dn_load_rhs(int n, int npad, const double* __restrict__ rhs, double* __restrict__ vec) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < npad) vec[e] = e < n ? rhs[e] : 0.0;
-}
-__global__ void k_dn_store_x(int C, const double* __restrict__ vec, double* __restrict__ cv) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < 8 * C) cv[(size_t)CV_STRIDE * (e >> 3) + 8 * CV_X + (e & 7)] = vec[e];
 }

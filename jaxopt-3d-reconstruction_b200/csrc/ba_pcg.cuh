@@ -628,6 +628,31 @@ __global__ void k_trial_pts(int64_t n4, const double* __restrict__ pts4, const d
   if (i < n4) pts4_trial[i] = (i & 3) == 3 ? 0.0 : pts4[i] - vp[3 * (i >> 2) + (i & 3)];
 }
 
+// trial cameras and trial points in ONE launch: the first cam_blocks CTAs do k_trial_cams' work, the rest k_trial_pts'
+__global__ void __launch_bounds__(256)
+k_trial(int C, int cam_blocks, const double* __restrict__ cam8, const double* __restrict__ vc, int vc_stride,
+        const double* __restrict__ gc, double* __restrict__ cam8_trial, double* __restrict__ part, int64_t n4,
+        const double* __restrict__ pts4, const double* __restrict__ vp, double* __restrict__ pts4_trial) {
+  if ((int)blockIdx.x < cam_blocks) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double vg = 0.0, vv = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const size_t o = 8 * (size_t)c + k;
+      const double v = vc[(size_t)vc_stride * c + k];
+      cam8_trial[o] = cam8[o] - v;
+      vg += v * gc[o];
+      vv += v * v;
+    }
+    part[2 * c] = vg;
+    part[2 * c + 1] = vv;
+    return;
+  }
+  const int64_t i = (int64_t)(blockIdx.x - cam_blocks) * blockDim.x + threadIdx.x;
+  if (i < n4) pts4_trial[i] = (i & 3) == 3 ? 0.0 : pts4[i] - vp[3 * (i >> 2) + (i & 3)];
+}
+
 // generic ordered reduction: out[k] = sum_i in[i*stride + k], k < nout (single CTA)
 __global__ void __launch_bounds__(1024)
 k_reduce(const double* __restrict__ in, int n, int stride, int nout, double* __restrict__ out, int is_max_mask) {
