@@ -210,6 +210,34 @@ __device__ __forceinline__ double v2_residual(const Proj& pr, double ox, double 
   return (xrow ? pr.u - ox : pr.v - oy) * inv_w;
 }
 
+// MODEL 2 / 3: the 2-vector model under ceres::CauchyLoss(a) / ceres::SoftLOneLoss(a), the robustifiers the reference's
+// COLMAP comparator selects (colmap/src/optim/bundle_adjustment.cc:53-68), applied the way Ceres applies them: Triggs'
+// correction of the residual block and its Jacobian (Corrector, corrector.cc).  Both losses have rho'' < 0, where the
+// corrector reduces to scaling the block r = (dx, dy)/w and its Jacobian rows by sqrt(rho'(s)), s = |r|^2; the LM loss is
+// Ceres' cost 0.5 sum rho(s).  Row contract: every observation as an ADJACENT pair of rows (x component, then y), both with
+// the full observation; the stable sorts and the 4-aligned run starts of the plan keep the pair on an (even, odd) B position,
+// so the component is the parity of the row's B position.  rho_b = (a / w)^2.  cterm: the row's share of 2 x cost.
+template <int MODEL>
+__device__ __forceinline__ double robust_residual(const Proj& pr, double ox, double oy, double inv_w, double rho_b, int comp,
+                                                  double& ex, double& ey, double& cterm) {
+  const double dx = (pr.u - ox) * inv_w, dy = (pr.v - oy) * inv_w;
+  const double s = dx * dx + dy * dy;
+  const double q = s / rho_b;
+  double rho, rho1;
+  if (MODEL == 2) {
+    rho = rho_b * log1p(q);        // b log(1 + s/b)
+    rho1 = 1.0 / (1.0 + q);
+  } else {
+    const double t = sqrt(1.0 + q);
+    rho = 2.0 * s / (t + 1.0);     // 2b (sqrt(1 + s/b) - 1)
+    rho1 = 1.0 / t;
+  }
+  const double sq = sqrt(rho1);
+  cterm = 0.5 * rho;
+  ex = comp ? 0.0 : sq * inv_w;
+  ey = comp ? sq * inv_w : 0.0;
+  return sq * (comp ? dy : dx);
+}
 // Per-observation value of the reprojection-error evaluator (k_reproj_err): LOSS 0 TRIVIAL_LOSS, 1 CAUCHY_LOSS
 // (src/dataset/loss_functions.py:7-17, applied per coordinate), 2 / 3 ceres::CauchyLoss / SoftLOneLoss of |r|^2 with b = a^2
 // (colmap/src/optim/bundle_adjustment.cc:53-68).

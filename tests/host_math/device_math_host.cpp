@@ -50,6 +50,15 @@ void hm_ba_row_v2(const double* T, const double* X, const double* obs, double in
   *r = v2_residual(pr, obs[0], obs[1], inv_w, ex, ey);
   jac_row(T, pr, X[0], X[1], X[2], ex, ey, a, b);
 }
+// row of the robustified 2-vector model exactly as k_resjac<JT, 2 | 3, .> forms it (loss 1 = Cauchy, 2 = soft L1; comp 0 = x row, 1 = y row)
+void hm_ba_row_robust(const double* T, const double* X, const double* obs, double inv_w, double rho_b, int loss, int comp,
+                      double* r, double* cterm, double* a, double* b) {
+  const Proj pr = project(T, X[0], X[1], X[2]);
+  double ex, ey;
+  *r = loss == 1 ? robust_residual<2>(pr, obs[0], obs[1], inv_w, rho_b, comp, ex, ey, *cterm)
+                 : robust_residual<3>(pr, obs[0], obs[1], inv_w, rho_b, comp, ex, ey, *cterm);
+  jac_row(T, pr, X[0], X[1], X[2], ex, ey, a, b);
+}
 double hm_reproj_loss(int loss, double dx, double dy, double b) {
   switch (loss) {
     case 0: return reproj_loss<0>(dx, dy, b);

@@ -32,6 +32,7 @@ def hm(tmp_path_factory):
     lib.hm_ba_row.argtypes = [dp, dp, dp, C.c_double, dp, dp, dp, dp]
     lib.hm_pose_row.argtypes = [dp, dp, dp, C.c_double, C.c_double, C.c_int, dp, dp]
     lib.hm_ba_row_v2.argtypes = [dp, dp, dp, C.c_double, dp, dp, dp]
+    lib.hm_ba_row_robust.argtypes = [dp, dp, dp, C.c_double, C.c_double, C.c_int, C.c_int, dp, dp, dp, dp]
     lib.hm_reproj_loss.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double]
     lib.hm_reproj_loss.restype = C.c_double
     lib.hm_chol8_solve.argtypes = [dp, dp]
@@ -123,5 +124,29 @@ def test_vector2_rows_of_the_cuda_source_vs_oracle(hm):
                         _p(r[i:i + 1]), _p(a[i]), _p(b[i]))
     assert np.isfinite(r).all() and np.isfinite(a).all() and np.isfinite(b).all()
     np.testing.assert_allclose(r, ro, rtol=1e-9, atol=1e-15)
+    np.testing.assert_allclose(a, ao, rtol=1e-9, atol=1e-12 * np.abs(ao).max())
+    np.testing.assert_allclose(b, bo_, rtol=1e-9, atol=1e-12 * np.abs(bo_).max())
+
+
+@pytest.mark.parametrize("loss,code", [("cauchy", 1), ("soft_l1", 2)])
+def test_robust_rows_of_the_cuda_source_vs_oracle(hm, loss, code):
+    """`robust_residual<2 | 3>` (common.cuh: the 2-vector model under Ceres' Cauchy / soft-L1 loss as k_resjac<JT, 2 | 3, .>
+    evaluates it) against the oracle's restatement of Ceres' loss functions + corrector (`ba_eval_robust`): corrected residuals,
+    the rows' cost terms and the corrected Jacobian rows, on the paired-row contract (component = parity of the row)."""
+    sc = b200ba.synth.make_ba_scene("small", seed=0)
+    x0, k3 = bo.pack_params(sc.poses0, sc.intrinsics0, sc.points0)
+    C_ = sc.C
+    cam8 = np.concatenate([x0[:6 * C_].reshape(C_, 6), x0[6 * C_:8 * C_].reshape(C_, 2)], axis=1)
+    T = _tables(hm, cam8, k3)
+    c2, p2, o2 = bo.expand_vector2_pairs(sc.cam_idx, sc.pt_idx, sc.obs)
+    w, scale = sc.avg_cam_width, 2.0
+    ro, cto, ao, bo_ = bo.ba_eval_robust(x0, C_, c2, p2, o2, k3, w * w, loss, scale)
+    n = len(c2)
+    r, ct, a, b = np.zeros(n), np.zeros(n), np.zeros((n, 8)), np.zeros((n, 3))
+    for i in range(n):
+        hm.hm_ba_row_robust(_p(T[c2[i]]), _p(np.ascontiguousarray(sc.points0[p2[i]])), _p(np.ascontiguousarray(o2[i])), 1.0 / w,
+                            (scale / w) ** 2, code, i & 1, _p(r[i:i + 1]), _p(ct[i:i + 1]), _p(a[i]), _p(b[i]))
+    np.testing.assert_allclose(r, ro, rtol=1e-9, atol=1e-15)
+    np.testing.assert_allclose(ct, cto, rtol=1e-12)
     np.testing.assert_allclose(a, ao, rtol=1e-9, atol=1e-12 * np.abs(ao).max())
     np.testing.assert_allclose(b, bo_, rtol=1e-9, atol=1e-12 * np.abs(bo_).max())
