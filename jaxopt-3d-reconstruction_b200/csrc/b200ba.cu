@@ -81,6 +81,7 @@ struct b200ba_plan {
   int ring_slots = 0, n_sm = 0;
   int ringx_ok = 0, ringx_D = 0, ringx_slots = 0;  // fused multi-rank camera kernel (ba_cs_ringx.cuh)
   int ringx_auto = 0;                              // ... and whether the cost model prefers it for this plan
+  int dn_grid_v_env = 0;
   int warpx = 0, warpx_grid = 0;                   // warp-per-camera fused multi-rank kernel (ba_cs_warpx.cuh)
   int32_t* cam_order_x = nullptr;     // its camera order: the SAME on every rank (descending GLOBAL row count)
   std::vector<int64_t> cam_rows_host; // local rows per camera (padded), kept for that
@@ -394,7 +395,10 @@ static int dense_build(b200ba_plan* p, cudaStream_t s) {
   if (!coop || per_sm < 1) return 0;
   const int ntl = p->dn_T * (p->dn_T + 1) / 2;
   p->dn_grid = std::min(ntl, std::min(per_sm, 4) * n_sm);
+  if (const char* e = getenv("B200BA_DN_GRID")) { const int v = atoi(e); if (v >= 1 && v < p->dn_grid) p->dn_grid = v; }  // experiments: fewer CTAs = fewer flag hand-overs
+  if (const char* e = getenv("B200BA_DN_GRID_V")) { const int v = atoi(e); if (v >= 1) p->dn_grid_v_env = v; }
   p->dn_grid_v = std::min(p->dn_T, n_sm);
+  if (p->dn_grid_v_env > 0 && p->dn_grid_v_env < p->dn_grid_v) p->dn_grid_v = p->dn_grid_v_env;
   p->dense_schur = 1;
   return 0;
 }
