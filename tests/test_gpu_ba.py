@@ -311,6 +311,35 @@ def test_camera_with_very_few_rows(monkeypatch, split):
     np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
 
 
+@pytest.mark.parametrize("jac_f32", [False, True])
+def test_point_with_more_rows_than_a_chunk_holds(jac_f32):
+    """One point with 603 observations (its three cameras see it 201 times each: duplicates are legal rows) — more than the
+    512 rows of a point chunk: a chunk of its own from the device-side chunk builder, the CTA-wide branch of the point-side
+    kernel in the matvec and in the back-substitution, a 603-row run in the point-block kernels.  PCG path against the exact
+    oracle on the same rows."""
+    sc, ba, x0, k3 = _setup("ladybug49", jac_f32=jac_f32)
+    rows0 = np.flatnonzero(sc.pt_idx == 0)
+    rng = np.random.default_rng(0)
+    rep = np.repeat(rows0, 600 // len(rows0) + 1)[:600]
+    cam_idx = np.concatenate([sc.cam_idx, sc.cam_idx[rep]]).astype(np.int32)
+    pt_idx = np.concatenate([sc.pt_idx, sc.pt_idx[rep]]).astype(np.int32)
+    obs = np.concatenate([sc.obs, sc.obs[rep] + rng.normal(0.0, 0.5, (len(rep), 2))])
+    perm = rng.permutation(len(cam_idx))
+    cam_idx, pt_idx, obs = cam_idx[perm], pt_idx[perm], np.ascontiguousarray(obs[perm])
+    assert np.bincount(pt_idx, minlength=sc.P)[0] > 512
+    prob = ba.build_problem_sparse(cam_idx, pt_idx, obs, sc.P)
+    info = (__import__("ctypes").c_int * 8)()
+    prob.lib.b200ba_plan_info(prob.plan, info)
+    assert not info[5]  # PCG path (the fixture switches the dense path off)
+    params, st = ba.optimize(x0, prob, None, k3, None)
+    ref = bo.lm_solve(x0, sc.C, sc.P, cam_idx, pt_idx, obs, k3, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num and st.pcg_iters.sum() > 0
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    np.testing.assert_array_equal(st.accepted.astype(bool), np.array(ref.trace.accepted))
+    rms = bo.rms_reprojection_px(params, sc.C, cam_idx, pt_idx, obs, k3)
+    assert rms == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, cam_idx, pt_idx, obs, k3), rel=1e-4)
+
+
 def test_schur_matvec_matches_dense_schur_complement():
     """b200ba_schur_matvec (camera head -> point kernel -> camera tail) against S formed densely by the oracle's
     formulas: S = U + mu I - W (V + mu I)^-1 W^T."""
