@@ -340,6 +340,23 @@ def test_point_with_more_rows_than_a_chunk_holds(jac_f32):
     assert rms == pytest.approx(bo.rms_reprojection_px(ref.params, sc.C, cam_idx, pt_idx, obs, k3), rel=1e-4)
 
 
+@pytest.mark.parametrize("dense", ["0", "1"])
+def test_points_without_observations_stay_put(monkeypatch, dense):
+    """Three points (the first, one in the middle, the last) lose all their observations: empty A runs, V_p = 0 so that
+    (V_p + mu I)^-1 = I / mu and g_p = 0.  Both solver paths follow the exact oracle and leave those points untouched."""
+    monkeypatch.setenv("B200BA_DENSE", dense)
+    sc, ba, x0, k3 = _setup("small", jac_f32=True)
+    gone = [0, 7, sc.P - 1]
+    keep = ~np.isin(sc.pt_idx, gone)
+    ci, pi, ob = sc.cam_idx[keep], sc.pt_idx[keep], np.ascontiguousarray(sc.obs[keep])
+    params, st = ba.optimize(x0, ba.build_problem_sparse(ci, pi, ob, sc.P), None, k3, None)
+    ref = bo.lm_solve(x0, sc.C, sc.P, ci, pi, ob, k3, sc.avg_cam_width)
+    assert st.iter_num == ref.iter_num
+    np.testing.assert_allclose(st.loss_trajectory, np.array(ref.trace.loss), rtol=1e-5)
+    np.testing.assert_array_equal(params[8 * sc.C:].reshape(-1, 3)[gone], sc.points0[gone])
+    assert np.isfinite(params).all()
+
+
 def test_schur_matvec_matches_dense_schur_complement():
     """b200ba_schur_matvec (camera head -> point kernel -> camera tail) against S formed densely by the oracle's
     formulas: S = U + mu I - W (V + mu I)^-1 W^T."""
