@@ -187,6 +187,8 @@ enum { PC_RESJAC = 0, PC_PT_BLOCKS, PC_CAM_BLOCKS, PC_PT_PREPARE, PC_CAM_SCHUR, 
 // early (mask 2) 168.4; point-side kernel allowed to start early (mask 1) 116.4; both (mask 3) 120.0 — the ring kernel's CTAs
 // arrive during the last wave of the point kernel and have their barriers set up when it ends; the 11 000 CTAs of the point
 // kernel gain nothing from being resident early and lose a third of the solve (every CTA pays for griddepcontrol.wait).
+// With the ring kernel's trigger moved to the start of every CTA's LAST camera (RING_TRIGGER_LATE, gpurun_out/r3r) the early
+// point kernel only waits a few microseconds and still loses 2 % (165.6 vs 169.3): it stays off.
 // Multi-rank sequence (k_ps | k_cs_warp | k_cs_vec | k_cs_warp), 2 ranks (gpurun_out/r3e): Venice 229.8 (none) / 230.1 (mask 14) /
 // 233.5 (mask 15); Final-13682 49.7 / 49.85 / 50.1 — there the point kernel may start early too.
 // Default: mask 2 on one rank, 15 on the split path.  B200BA_PDL=0 launches everything normally.

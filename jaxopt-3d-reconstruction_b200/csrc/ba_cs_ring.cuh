@@ -20,6 +20,9 @@
 #ifndef RING_MAXREG
 #define RING_MAXREG 128            // 13 warps -> at most 4 on one SM sub-partition: 4 x 32 x 128 = its 16 K registers
 #endif
+#ifndef RING_TRIGGER_LATE
+#define RING_TRIGGER_LATE 1  // PDL trigger of the following kernel: 0 at the start of the launch, 1 when a CTA starts its last camera
+#endif
 #ifndef RING_MINB
 #define RING_MINB 1                // CTAs per SM (2: two half-size CTAs interleave their per-camera reduce/update bubbles)
 #endif
@@ -136,7 +139,12 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
     for (int i = 0; i < RING_NCAM; ++i) { mbar_init(bar_cfull + i, 1); mbar_init(bar_cempty + i, RING_CW); }
     mbar_fence_init();
   }
+#if RING_TRIGGER_LATE
+  // the point-side kernel that follows may be scheduled once EVERY CTA has started its last camera (trigger below): its CTAs
+  // fill the SMs that fall idle during the last round of cameras instead of being resident through the whole launch
+#else
   griddep_launch();
+#endif
   griddep_wait();
   if (st->pcg_done) return;
   // PCG scalars once into shared memory: kept as plain `st->x` the compiler re-loads them from GLOBAL memory at
@@ -223,7 +231,13 @@ k_cs_ring(int C, int nPB, int flags, int nslots, SolverState* __restrict__ st, c
   // to the producer as soon as pass C has read it: the ring is pure prefetch depth (~2 cameras ahead) and
   // HBM streaming never waits for the serial reduce / update / pass-A phases of a camera.
   int ring = 0, ring_ph = 0;
+#if RING_TRIGGER_LATE
+  if (ncam == 0) griddep_launch();
+#endif
   for (int i = 0; i < ncam; ++i) {
+#if RING_TRIGGER_LATE
+    if (i == ncam - 1) griddep_launch();
+#endif
     const int cb = i % RING_NCAM, ph = (i / RING_NCAM) & 1;
     mbar_wait(bar_cfull + cb, ph);
     const RingCam& B = s_cam[cb];
